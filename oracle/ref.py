@@ -1,0 +1,191 @@
+"""TEST INFRASTRUCTURE — ctypes driver for the REAL reference built by oracle/build_ref.sh.
+
+Only tests/, tools that generate golden fixtures, __graft_entry__.smoke() and
+bench.py's CPU arm may import this.  The product never does.
+
+Every call below lands in the reference's own code (see oracle/ref_shims/ref_hooks.cpp
+for the file:line of each function reached).
+"""
+import ctypes as C
+import os
+import tempfile
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "liblajolla_ref.so")
+REFERENCE_DIR = os.environ.get("GDPT_REFERENCE_DIR", "/root/reference")
+DEFAULT_SEED = 0x31E241F862A1FB5E  # src/pcg.h:33
+
+_lib = None
+
+
+def available():
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not available():
+            raise RuntimeError("oracle/_ref/liblajolla_ref.so missing: run oracle/build_ref.sh where /root/reference exists")
+        L = C.CDLL(LIB_PATH)
+        dp = C.POINTER(C.c_double)
+        ip = C.POINTER(C.c_int)
+        L.gdpt_ref_init.argtypes = [C.c_int]
+        L.gdpt_ref_load.restype = C.c_void_p
+        L.gdpt_ref_load.argtypes = [C.c_char_p]
+        L.gdpt_ref_free.argtypes = [C.c_void_p]
+        L.gdpt_ref_info.argtypes = [C.c_void_p, ip]
+        L.gdpt_ref_set_options.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.gdpt_ref_render.argtypes = [C.c_void_p, dp, dp, dp, dp]
+        L.gdpt_ref_render_path.argtypes = [C.c_void_p, dp]
+        L.gdpt_ref_fourier_solve.argtypes = [C.c_int, C.c_int, dp, dp, dp, C.c_double, dp]
+        L.gdpt_ref_grad_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, dp]
+        L.gdpt_ref_render_pixelseed.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp, dp]
+        L.gdpt_ref_sample_primary.argtypes = [C.c_void_p, C.c_int, dp, dp]
+        L.gdpt_ref_intersect.argtypes = [C.c_void_p, C.c_int, dp, dp, ip, dp]
+        L.gdpt_ref_bsdf.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp, dp, dp]
+        L.gdpt_ref_export.argtypes = [C.c_void_p, C.c_char_p]
+        _lib = L
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double)) if a is not None else None
+
+
+_threads = None
+
+
+def init(threads=None):
+    global _threads
+    threads = threads or os.cpu_count() or 1
+    if _threads != threads:
+        if _threads is None:
+            import atexit
+            atexit.register(lib().gdpt_ref_shutdown)  # worker threads must be joined before static destructors run
+        lib().gdpt_ref_init(threads)
+        _threads = threads
+    return threads
+
+
+def make_variant(xml_path, out_dir=None, **subs):
+    """Write a variant of a reference scene XML next to symlinks of its assets.
+
+    subs: integrator='gradpath', width=, height=, spp=, max_depth=, extra_xml= (text
+    spliced before </scene>).  The reference tree is never modified.
+    """
+    import re
+    src_dir = os.path.dirname(os.path.abspath(xml_path))
+    out_dir = out_dir or tempfile.mkdtemp(prefix="gdpt_scene_")
+    os.makedirs(out_dir, exist_ok=True)
+    for e in os.listdir(src_dir):
+        d = os.path.join(out_dir, e)
+        if not os.path.lexists(d) and not e.endswith(".xml"):
+            os.symlink(os.path.join(src_dir, e), d)
+    txt = open(xml_path).read()
+    if "integrator" in subs:
+        txt = re.sub(r'<integrator\s+type="[^"]*"', '<integrator type="%s"' % subs["integrator"], txt, count=1)
+    if "max_depth" in subs:
+        if re.search(r'name="maxDepth"', txt):
+            txt = re.sub(r'(name="maxDepth"\s+value=")[^"]*"', r'\g<1>%d"' % subs["max_depth"], txt)
+        else:
+            txt = re.sub(r'(<integrator[^>]*)/>', r'\1>\n<integer name="maxDepth" value="%d"/></integrator>' % subs["max_depth"], txt, count=1)
+    for key, name in (("width", "width"), ("height", "height"), ("spp", "sampleCount")):
+        if key in subs:
+            txt = re.sub(r'(name="%s"\s+value=")[^"]*"' % name, r'\g<1>%d"' % subs[key], txt)
+    if subs.get("extra_xml"):
+        txt = txt.replace("</scene>", subs["extra_xml"] + "\n</scene>")
+    out = os.path.join(out_dir, subs.get("name", "variant") + ".xml")
+    with open(out, "w") as f:
+        f.write(txt)
+    return out
+
+
+class RefScene:
+    def __init__(self, xml_path, threads=None):
+        init(threads)
+        self.h = lib().gdpt_ref_load(os.path.abspath(xml_path).encode())
+        if not self.h:
+            raise RuntimeError("reference failed to parse " + xml_path)
+        self.refresh()
+
+    def refresh(self):
+        info = (C.c_int * 8)()
+        lib().gdpt_ref_info(self.h, info)
+        (self.width, self.height, self.spp, self.max_depth, self.rr_depth,
+         self.integrator, self.nshapes, self.nmats) = list(info)
+
+    def set_options(self, spp=-2, max_depth=-2, rr_depth=-2):
+        lib().gdpt_ref_set_options(self.h, spp, max_depth, rr_depth)
+        self.refresh()
+
+    def close(self):
+        if self.h:
+            lib().gdpt_ref_free(self.h)
+            self.h = None
+
+    def _img(self):
+        return np.zeros((self.height, self.width, 3), dtype=np.float64)
+
+    def render(self):
+        """Reference render() with GradPath. Returns dict(primal, dx, dy, poisson) = c, cx, cy, out."""
+        c, cx, cy, out = self._img(), self._img(), self._img(), self._img()
+        lib().gdpt_ref_render(self.h, _dp(c), _dp(cx), _dp(cy), _dp(out))
+        return dict(primal=c, dx=cx, dy=cy, poisson=out)
+
+    def render_path(self):
+        out = self._img()
+        lib().gdpt_ref_render_path(self.h, _dp(out))
+        return out
+
+    def grad_sample(self, x, y, stream, seed=DEFAULT_SEED):
+        rec = np.zeros(23)
+        lib().gdpt_ref_grad_sample(self.h, x, y, stream, seed, _dp(rec))
+        return rec
+
+    def render_pixelseed(self, spp, seed=DEFAULT_SEED, sample0=0, y0=0, y1=None):
+        """Pixel-seeded accumulation (stream = sample*W*H + y*W + x). Returns c, cx0, cy0, cx1, cy1."""
+        y1 = self.height if y1 is None else y1
+        bufs = [self._img() for _ in range(5)]
+        lib().gdpt_ref_render_pixelseed(self.h, seed, spp, sample0, y0, y1, *[_dp(b) for b in bufs])
+        return bufs
+
+    def sample_primary(self, screen_pos):
+        sp = np.ascontiguousarray(screen_pos, dtype=np.float64).reshape(-1, 2)
+        rays = np.zeros((sp.shape[0], 6))
+        lib().gdpt_ref_sample_primary(self.h, sp.shape[0], _dp(sp), _dp(rays))
+        return rays
+
+    def intersect(self, rays, rdiff=None):
+        rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 8)
+        n = rays.shape[0]
+        ids = np.zeros((n, 3), dtype=np.int32)
+        vtx = np.zeros((n, 24))
+        rd = np.ascontiguousarray(rdiff, dtype=np.float64) if rdiff is not None else None
+        lib().gdpt_ref_intersect(self.h, n, _dp(rays), _dp(rd), ids.ctypes.data_as(C.POINTER(C.c_int)), _dp(vtx))
+        return ids, vtx
+
+    def bsdf(self, mat_id, vtx, dirs, rnd):
+        vtx = np.ascontiguousarray(vtx, dtype=np.float64).reshape(-1, 15)
+        dirs = np.ascontiguousarray(dirs, dtype=np.float64).reshape(-1, 6)
+        rnd = np.ascontiguousarray(rnd, dtype=np.float64).reshape(-1, 3)
+        out = np.zeros((vtx.shape[0], 10))
+        lib().gdpt_ref_bsdf(self.h, mat_id, vtx.shape[0], _dp(vtx), _dp(dirs), _dp(rnd), _dp(out))
+        return out
+
+    def export(self, path):
+        if lib().gdpt_ref_export(self.h, os.path.abspath(path).encode()) != 0:
+            raise RuntimeError("export failed: " + path)
+        return path
+
+
+def fourier_solve(u, gx, gy, alpha=0.04):
+    u = np.ascontiguousarray(u, dtype=np.float64)
+    gx = np.ascontiguousarray(gx, dtype=np.float64)
+    gy = np.ascontiguousarray(gy, dtype=np.float64)
+    h, w, _ = u.shape
+    out = np.zeros_like(u)
+    lib().gdpt_ref_fourier_solve(w, h, _dp(u), _dp(gx), _dp(gy), alpha, _dp(out))
+    return out
