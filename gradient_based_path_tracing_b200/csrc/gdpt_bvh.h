@@ -1,0 +1,50 @@
+// 4-wide BVH over all triangles and spheres of a scene — the replacement for Embree's
+// rtcCommitScene (/root/reference/src/scene.cpp:19-34) and the data the traversal kernel
+// (gdpt_trace.cuh) walks.  Geometry is rounded to float exactly as the reference hands it
+// to Embree (src/shapes/triangle_mesh.inl:11-14, src/shapes/sphere.inl:1-10).
+//
+// Node (128 B, one L2/L1 line, 8 x 16-byte vector loads):
+//   float4 lox, loy, loz, hix, hiy, hiz   bounds of the 4 children, SoA over children
+//   int4   child                           >=0: node index; <0: leaf, first primitive = ~child
+//   int4   count                           primitives in the leaf (0 = empty slot / inner node)
+// Primitive (48 B, 3 x 16-byte loads): v0.xyz | prim_id,  e1.xyz | shape_id,  e2.xyz | kind
+//   kind 0 = triangle (e1 = v1-v0, e2 = v2-v0), kind 1 = sphere (data in DScene::spheres)
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace gdpt {
+
+struct BvhNode {
+    float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
+    int child[4];
+    int count[4];
+};
+static_assert(sizeof(BvhNode) == 128, "node must be one 128-byte line");
+
+struct BvhPrim {
+    float v0[3]; int prim_id;
+    float e1[3]; int shape_id;
+    float e2[3]; int kind;
+};
+static_assert(sizeof(BvhPrim) == 48, "primitive record must be 48 bytes");
+
+struct HostShape {
+    int kind;                 // 0 sphere, 1 mesh
+    const double *positions;  // mesh: [nverts][3]
+    const int *indices;       // mesh: [ntris][3]
+    int nverts, ntris;
+    double sphere[4];
+};
+
+struct Bvh {
+    std::vector<BvhNode> nodes;
+    std::vector<BvhPrim> prims;
+    float lo[3], hi[3];       // float scene bounds (what rtcGetSceneBounds reports)
+    int max_depth = 0;
+};
+
+// Binned-SAH binary build collapsed to 4-wide. Deterministic.
+void build_bvh(const std::vector<HostShape> &shapes, Bvh &out);
+
+} // namespace gdpt
