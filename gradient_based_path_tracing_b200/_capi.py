@@ -1,0 +1,105 @@
+"""ctypes binding of libgdpt.so (include/gdpt.h).  No compute happens in Python and there is
+no fallback: if the CUDA library is missing, importing anything that needs it raises."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgdpt.so")
+
+PRECISION_F64 = 0
+PRECISION_F32 = 1
+DEFAULT_SEED = 0x31E241F862A1FB5E
+
+dp = C.POINTER(C.c_double)
+ip = C.POINTER(C.c_int32)
+
+
+class GdptImage(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("channels", C.c_int32),
+                ("data", dp), ("palette", dp), ("palette_size", C.c_int32), ("index", C.POINTER(C.c_uint8))]
+
+
+class GdptSceneDesc(C.Structure):
+    _fields_ = [
+        ("sample_to_cam", C.c_double * 16), ("cam_to_world", C.c_double * 16),
+        ("width", C.c_int32), ("height", C.c_int32), ("filter_kind", C.c_int32), ("filter_param", C.c_double),
+        ("n_shapes", C.c_int32), ("shapes", ip), ("shape_offsets", C.POINTER(C.c_int64)), ("spheres", dp),
+        ("n_positions", C.c_int64), ("n_triangles", C.c_int64), ("n_normals", C.c_int64), ("n_uvs", C.c_int64),
+        ("positions", dp), ("indices", ip), ("normals", dp), ("uvs", dp),
+        ("n_materials", C.c_int32), ("materials", dp), ("n_textures", C.c_int32), ("textures", dp),
+        ("n_images3", C.c_int32), ("n_images1", C.c_int32), ("images3", C.POINTER(GdptImage)), ("images1", C.POINTER(GdptImage)),
+        ("n_lights", C.c_int32), ("lights", dp),
+        ("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("samples_per_pixel", C.c_int32),
+    ]
+
+
+class GdptRenderParams(C.Structure):
+    _fields_ = [("spp", C.c_int32), ("sample0", C.c_int32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32),
+                ("seed", C.c_uint64), ("data_cost", C.c_double), ("precision", C.c_int32),
+                ("y0", C.c_int32), ("y1", C.c_int32), ("wave_samples", C.c_int32)]
+
+
+class GdptImages(C.Structure):
+    _fields_ = [("primal", dp), ("dx", dp), ("dy", dp), ("poisson", dp)]
+
+
+class GdptStats(C.Structure):
+    _fields_ = [("ms_total", C.c_double), ("ms_trace", C.c_double), ("ms_shade", C.c_double), ("ms_poisson", C.c_double),
+                ("ms_copy", C.c_double), ("kernel_launches", C.c_int64), ("rays_traced", C.c_int64), ("paths", C.c_int64),
+                ("bounce_iterations", C.c_int64)]
+
+
+# every symbol include/gdpt.h declares
+EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_destroy", "gdpt_scene_bounds", "gdpt_render",
+           "gdpt_render_accumulate_device", "gdpt_merge_device", "gdpt_poisson", "gdpt_poisson_device", "gdpt_get_stats",
+           "gdpt_synchronize", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill"]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libgdpt.so is not built (run __graft_entry__.build()); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        L.gdpt_last_error.restype = C.c_char_p
+        L.gdpt_create.argtypes = [C.POINTER(GdptSceneDesc), C.c_int, C.POINTER(vp)]
+        L.gdpt_destroy.argtypes = [vp]
+        L.gdpt_destroy.restype = None
+        L.gdpt_scene_bounds.argtypes = [vp, dp]
+        L.gdpt_render.argtypes = [vp, C.POINTER(GdptRenderParams), C.POINTER(GdptImages)]
+        L.gdpt_render_accumulate_device.argtypes = [vp, C.POINTER(GdptRenderParams), vp, vp, vp, vp, vp]
+        L.gdpt_merge_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
+        L.gdpt_poisson.argtypes = [C.c_int, C.c_int, C.c_int, dp, dp, dp, C.c_double, dp]
+        L.gdpt_poisson_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_double, vp]
+        L.gdpt_get_stats.argtypes = [vp, C.POINTER(GdptStats)]
+        L.gdpt_synchronize.argtypes = [vp]
+        L.gdpt_sample_primary.argtypes = [vp, C.c_int, C.c_int, dp, dp]
+        L.gdpt_intersect.argtypes = [vp, C.c_int, C.c_int, dp, dp, ip, dp]
+        L.gdpt_bsdf.argtypes = [vp, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]
+        L.gdpt_grad_samples.argtypes = [vp, C.POINTER(GdptRenderParams), C.c_int, ip, ip, C.POINTER(C.c_uint64), dp]
+        L.gdpt_pcg_fill.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, dp, C.POINTER(C.c_uint32)]
+        _lib = L
+    return _lib
+
+
+class GdptError(RuntimeError):
+    pass
+
+
+def check(rc):
+    if rc != 0:
+        raise GdptError("libgdpt error %d: %s" % (rc, lib().gdpt_last_error().decode(errors="replace")))
+
+
+def as_dp(a):
+    return a.ctypes.data_as(dp) if a is not None else None
+
+
+def f64(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    return a.reshape(shape) if shape is not None else a

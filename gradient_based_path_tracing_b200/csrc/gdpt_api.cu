@@ -1,0 +1,297 @@
+// C ABI of libgdpt.so (include/gdpt.h): context management, the wavefront render loop,
+// the Poisson solve and the validation entry points.  Host code only orchestrates: every
+// arithmetic step of the path runs in the CUDA kernels of this directory.
+#include "gdpt_context.cuh"
+#include "gdpt_debug.cuh"
+
+using namespace gdpt;
+
+namespace {
+
+inline int blocks_for(long long n, int block) { return (int)((n + block - 1) / block); }
+constexpr int SM_COUNT = 148;
+
+template <typename R> struct ModeSel;
+template <> struct ModeSel<double> { static DScene<double> &scene(gdpt_ctx *c) { return c->sc_d; } static constexpr bool exact = true; };
+template <> struct ModeSel<float> { static DScene<float> &scene(gdpt_ctx *c) { return c->sc_f; } static constexpr bool exact = false; };
+
+template <bool EXACT>
+void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n) {
+    if (n <= 0) return;
+    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
+    k_trace<EXACT><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n);
+    c->stats.kernel_launches++; c->stats.rays_traced += n;
+}
+
+// One wave of pixel-samples through generate -> trace -> primary -> (trace -> bounce)*.
+template <typename R>
+int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
+    const int N = wp.n_paths;
+    if (N <= 0) return 0;
+    if (int r = c->gen.ensure((size_t)N * sizeof(GenRec<R>))) return r;
+    if (int r = c->rays.ensure((size_t)N * 5 * sizeof(RayF))) return r;
+    if (int r = c->hits.ensure((size_t)N * 5 * sizeof(Hit))) return r;
+    if (int r = c->rec_a.ensure((size_t)N * sizeof(PathRec<R>))) return r;
+    if (int r = c->rec_b.ensure((size_t)N * sizeof(PathRec<R>))) return r;
+    if (int r = c->off.ensure((size_t)N * sizeof(OffRec<R>))) return r;
+    if (int r = c->counters.ensure(64)) return r;
+    int *cnt = c->counters.as<int>();
+    GenRec<R> *gen = c->gen.as<GenRec<R>>();
+    RayF *rays = c->rays.as<RayF>(); Hit *hits = c->hits.as<Hit>();
+    PathRec<R> *cur = c->rec_a.as<PathRec<R>>(), *nxt = c->rec_b.as<PathRec<R>>();
+    OffRec<R> *off = c->off.as<OffRec<R>>();
+    cudaStream_t st = c->stream;
+
+    GD_CUDA(cudaMemsetAsync(cnt, 0, 64, st));
+    k_generate<R><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, rays);
+    c->stats.kernel_launches++;
+    launch_trace<ModeSel<R>::exact>(c, rays, hits, 5 * N);
+    k_primary<R><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, hits, cur, off, rays, cnt);
+    c->stats.kernel_launches++;
+    GD_CUDA(cudaMemcpyAsync(c->h_counts, cnt, sizeof(int), cudaMemcpyDeviceToHost, st));
+    GD_CUDA(cudaStreamSynchronize(st));
+    int count = c->h_counts[0];
+    c->stats.paths += N;
+    int which = 0; bool first = true;
+    while (count > 0) {
+        launch_trace<ModeSel<R>::exact>(c, rays, hits, count);
+        int *cin = cnt + which, *cout = cnt + (which ^ 1);
+        GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
+        k_bounce<R><<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout);
+        c->stats.kernel_launches++; c->stats.bounce_iterations++;
+        GD_CUDA(cudaMemcpyAsync(c->h_counts, cout, sizeof(int), cudaMemcpyDeviceToHost, st));
+        GD_CUDA(cudaStreamSynchronize(st));
+        count = c->h_counts[0];
+        std::swap(cur, nxt); which ^= 1; first = false;
+    }
+    GD_CUDA(cudaGetLastError());
+    return 0;
+}
+
+struct Resolved { int spp, sample0, y0, y1, precision, wave; unsigned long long seed; double alpha; int max_depth, rr_depth; };
+
+int resolve(gdpt_ctx *c, const gdpt_render_params *p, Resolved &r) {
+    if (!c || !p) return fail(GDPT_ERR_ARG, "null argument");
+    r.spp = p->spp > 0 ? p->spp : c->spp;
+    r.sample0 = p->sample0;
+    r.y0 = p->y0 > 0 ? p->y0 : 0; r.y1 = p->y1 > 0 ? std::min(p->y1, c->height) : c->height;
+    if (r.y0 >= r.y1) return fail(GDPT_ERR_ARG, "empty row band [%d,%d)", r.y0, r.y1);
+    r.precision = p->precision;
+    if (r.precision != GDPT_PRECISION_F64 && r.precision != GDPT_PRECISION_F32) return fail(GDPT_ERR_ARG, "unknown precision %d", r.precision);
+    r.seed = p->seed ? p->seed : 0x31e241f862a1fb5eULL;
+    r.alpha = p->data_cost > 0 ? p->data_cost : 0.04;
+    r.max_depth = p->max_depth == -2 ? c->max_depth : p->max_depth;
+    r.rr_depth = p->rr_depth == -2 ? c->rr_depth : p->rr_depth;
+    r.wave = p->wave_samples;
+    return 0;
+}
+
+template <typename R>
+int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, double *d_cy0, double *d_cx1, double *d_cy1) {
+    DScene<R> sc = ModeSel<R>::scene(c);
+    sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth;
+    WaveParams wp; memset(&wp, 0, sizeof(wp));
+    wp.width = c->width; wp.height = c->height; wp.y0 = r.y0; wp.y1 = r.y1;
+    wp.tiles_x = (c->width + 7) / 8;
+    int tiles_y = (r.y1 - r.y0 + 3) / 4;
+    wp.npix_pad = (long long)wp.tiles_x * tiles_y * 32;
+    wp.spp_total = r.spp; wp.seed = r.seed;
+    wp.img = d_img; wp.cx0 = d_cx0; wp.cy0 = d_cy0; wp.cx1 = d_cx1; wp.cy1 = d_cy1;
+    long long target = 4LL << 20;     // ~4M paths in flight per wave
+    int k = r.wave > 0 ? r.wave : (int)std::max<long long>(1, target / wp.npix_pad);
+    for (int s0 = 0; s0 < r.spp; s0 += k) {
+        int kk = std::min(k, r.spp - s0);
+        wp.sample0 = r.sample0 + s0; wp.n_samples = kk;
+        long long n = wp.npix_pad * kk;
+        if (n > 0x7fffffffLL / 8) return fail(GDPT_ERR_ARG, "wave too large");
+        wp.n_paths = (int)n;
+        if (int rc = run_wave<R>(c, sc, wp)) return rc;
+    }
+    return 0;
+}
+
+int ensure_images(gdpt_ctx *c) {
+    size_t n = (size_t)c->width * c->height * 3 * sizeof(double);
+    gdpt::DevBuf *bufs[] = {&c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
+    for (auto *b : bufs) if (int r = b->ensure(n)) return r;
+    return 0;
+}
+
+int ensure_poisson(gdpt_ctx *c, int w, int h) {
+    PoissonCache &pc = c->pc;
+    size_t plane = (size_t)w * h * 3 * sizeof(double);
+    if (int r = pc.work.ensure(plane)) return r;
+    if (int r = pc.work2.ensure(plane)) return r;
+    if (int r = pc.partial.ensure((size_t)SM_COUNT * 8 * 3 * sizeof(double))) return r;
+    if (int r = pc.dc.ensure(64)) return r;
+    if (pc.w != w || pc.h != h) {
+        if (int r = pc.Dw.ensure((size_t)w * w * sizeof(double))) return r;
+        if (int r = pc.DhT.ensure((size_t)h * h * sizeof(double))) return r;
+        k_dct_matrix<<<SM_COUNT * 4, 256, 0, c->stream>>>(w, 0, pc.Dw.as<double>());
+        k_dct_matrix<<<SM_COUNT * 4, 256, 0, c->stream>>>(h, 1, pc.DhT.as<double>());
+        c->stats.kernel_launches += 2;
+        pc.w = w; pc.h = h;
+    }
+    return 0;
+}
+
+int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out) {
+    if (w < 2 || h < 2) return fail(GDPT_ERR_ARG, "Poisson solve needs at least a 2x2 image");
+    if (int r = ensure_poisson(c, w, h)) return r;
+    PoissonCache &pc = c->pc;
+    cudaStream_t st = c->stream;
+    double *A = pc.work.as<double>(), *B = pc.work2.as<double>();
+    const int nb = SM_COUNT * 8;
+    k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, h, d_u, d_gx, d_gy, alpha, A, pc.partial.as<double>());
+    k_dc_reduce<<<1, 32, 0, st>>>(nb, pc.partial.as<double>(), pc.dc.as<double>());
+    Epilogue ep; memset(&ep, 0, sizeof(ep));
+    ep.img_w = w; ep.img_h = h; ep.alpha = alpha; ep.dc = pc.dc.as<double>(); ep.out = d_out;
+    ep.scale = 4.0 * (w - 1) * (h - 1);
+    long long plane = (long long)w * h;
+    dim3 g_rows(blocks_for(w, GT), blocks_for(3 * h, GT), 1), g_cols(blocks_for(w, GT), blocks_for(h, GT), 3);
+    // forward: rows then columns (+ spectral divide, DC)
+    ep.mode = EPI_STORE;
+    k_dgemm<<<g_rows, 256, 0, st>>>(3 * h, w, w, A, w, 0, pc.Dw.as<double>(), w, 0, B, w, 0, ep);
+    ep.mode = EPI_DIVIDE;
+    k_dgemm<<<g_cols, 256, 0, st>>>(h, w, h, pc.DhT.as<double>(), h, 0, B, w, plane, A, w, plane, ep);
+    // inverse (DCT-I is its own inverse up to the scale): columns then rows (+ scale, re-interleave)
+    ep.mode = EPI_STORE;
+    k_dgemm<<<g_cols, 256, 0, st>>>(h, w, h, pc.DhT.as<double>(), h, 0, A, w, plane, B, w, plane, ep);
+    ep.mode = EPI_SCALE_INTERLEAVE;
+    k_dgemm<<<g_rows, 256, 0, st>>>(3 * h, w, w, B, w, 0, pc.Dw.as<double>(), w, 0, A, w, 0, ep);
+    c->stats.kernel_launches += 6;
+    GD_CUDA(cudaGetLastError());
+    return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *gdpt_last_error(void) { return last_error().c_str(); }
+
+int gdpt_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
+
+int gdpt_create(const gdpt_scene_desc *scene, int device, gdpt_ctx **out) {
+    if (out) *out = nullptr;
+    gdpt_ctx *c = nullptr;
+    int r = create_context(scene, device, &c);
+    if (r != 0) { destroy_context(c); return r; }
+    *out = c; return 0;
+}
+
+void gdpt_destroy(gdpt_ctx *ctx) { destroy_context(ctx); }
+
+int gdpt_scene_bounds(gdpt_ctx *ctx, double *rc) {
+    if (!ctx || !rc) return fail(GDPT_ERR_ARG, "null argument");
+    for (int k = 0; k < 4; k++) rc[k] = ctx->bounds[k];
+    return 0;
+}
+
+int gdpt_synchronize(gdpt_ctx *ctx) {
+    if (!ctx) return fail(GDPT_ERR_ARG, "null argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out) {
+    if (!ctx || !out) return fail(GDPT_ERR_ARG, "null argument");
+    *out = ctx->stats; return 0;
+}
+
+int gdpt_render_accumulate_device(gdpt_ctx *ctx, const gdpt_render_params *params, double *d_img, double *d_cx0, double *d_cy0,
+                                  double *d_cx1, double *d_cy1) {
+    Resolved r;
+    if (int rc = resolve(ctx, params, r)) return rc;
+    if (!d_img || !d_cx0 || !d_cy0 || !d_cx1 || !d_cy1) return fail(GDPT_ERR_ARG, "null device image");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return r.precision == GDPT_PRECISION_F64 ? accumulate<double>(ctx, r, d_img, d_cx0, d_cy0, d_cx1, d_cy1)
+                                             : accumulate<float>(ctx, r, d_img, d_cx0, d_cy0, d_cx1, d_cy1);
+}
+
+int gdpt_merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const double *d_cx1, const double *d_cy0, const double *d_cy1,
+                      double *d_cx, double *d_cy) {
+    if (!ctx) return fail(GDPT_ERR_ARG, "null argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    k_merge<<<SM_COUNT * 8, 256, 0, ctx->stream>>>(w, h, d_cx0, d_cx1, d_cy0, d_cy1, d_cx, d_cy);
+    ctx->stats.kernel_launches++;
+    GD_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int gdpt_poisson_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out) {
+    if (!ctx) return fail(GDPT_ERR_ARG, "null argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return poisson_device(ctx, w, h, d_u, d_gx, d_gy, alpha > 0 ? alpha : 0.04, d_out);
+}
+
+int gdpt_render(gdpt_ctx *ctx, const gdpt_render_params *params, gdpt_images *out) {
+    Resolved r;
+    if (int rc = resolve(ctx, params, r)) return rc;
+    GD_CUDA(cudaSetDevice(ctx->device));
+    if (int rc = ensure_images(ctx)) return rc;
+    const int w = ctx->width, h = ctx->height;
+    size_t bytes = (size_t)w * h * 3 * sizeof(double);
+    cudaStream_t st = ctx->stream;
+    GD_CUDA(cudaEventRecord(ctx->ev[0], st));
+    gdpt::DevBuf *acc[] = {&ctx->img, &ctx->cx0, &ctx->cy0, &ctx->cx1, &ctx->cy1};
+    for (auto *b : acc) GD_CUDA(cudaMemsetAsync(b->p, 0, bytes, st));
+    int rc = r.precision == GDPT_PRECISION_F64
+                 ? accumulate<double>(ctx, r, ctx->img.as<double>(), ctx->cx0.as<double>(), ctx->cy0.as<double>(), ctx->cx1.as<double>(), ctx->cy1.as<double>())
+                 : accumulate<float>(ctx, r, ctx->img.as<double>(), ctx->cx0.as<double>(), ctx->cy0.as<double>(), ctx->cx1.as<double>(), ctx->cy1.as<double>());
+    if (rc) return rc;
+    GD_CUDA(cudaEventRecord(ctx->ev[1], st));
+    k_merge<<<SM_COUNT * 8, 256, 0, st>>>(w, h, ctx->cx0.as<double>(), ctx->cx1.as<double>(), ctx->cy0.as<double>(), ctx->cy1.as<double>(),
+                                         ctx->cx.as<double>(), ctx->cy.as<double>());
+    ctx->stats.kernel_launches++;
+    if (int rc2 = poisson_device(ctx, w, h, ctx->img.as<double>(), ctx->cx.as<double>(), ctx->cy.as<double>(), r.alpha, ctx->out.as<double>())) return rc2;
+    GD_CUDA(cudaEventRecord(ctx->ev[2], st));
+    if (out) {
+        if (out->primal) GD_CUDA(cudaMemcpyAsync(out->primal, ctx->img.p, bytes, cudaMemcpyDeviceToHost, st));
+        if (out->dx) GD_CUDA(cudaMemcpyAsync(out->dx, ctx->cx.p, bytes, cudaMemcpyDeviceToHost, st));
+        if (out->dy) GD_CUDA(cudaMemcpyAsync(out->dy, ctx->cy.p, bytes, cudaMemcpyDeviceToHost, st));
+        if (out->poisson) GD_CUDA(cudaMemcpyAsync(out->poisson, ctx->out.p, bytes, cudaMemcpyDeviceToHost, st));
+    }
+    GD_CUDA(cudaEventRecord(ctx->ev[3], st));
+    GD_CUDA(cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]); ctx->stats.ms_total = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->stats.ms_trace = ms;   // accumulate phase (trace + shade)
+    cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ctx->stats.ms_poisson = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]); ctx->stats.ms_copy = ms;
+    return 0;
+}
+
+int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, const int32_t *xs, const int32_t *ys,
+                      const uint64_t *streams, double *rec) {
+    Resolved r;
+    if (int rc = resolve(ctx, params, r)) return rc;
+    if (!xs || !ys || !streams || !rec || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
+    if (n == 0) return 0;
+    for (int i = 0; i < n; i++) if (xs[i] < 0 || xs[i] >= ctx->width || ys[i] < 0 || ys[i] >= ctx->height) return fail(GDPT_ERR_ARG, "pixel %d out of range", i);
+    GD_CUDA(cudaSetDevice(ctx->device));
+    if (int rc = ctx->xs.ensure((size_t)n * 4)) return rc;
+    if (int rc = ctx->ys.ensure((size_t)n * 4)) return rc;
+    if (int rc = ctx->streams.ensure((size_t)n * 8)) return rc;
+    if (int rc = ctx->recout.ensure((size_t)n * 23 * 8)) return rc;
+    GD_CUDA(cudaMemcpy(ctx->xs.p, xs, (size_t)n * 4, cudaMemcpyHostToDevice));
+    GD_CUDA(cudaMemcpy(ctx->ys.p, ys, (size_t)n * 4, cudaMemcpyHostToDevice));
+    GD_CUDA(cudaMemcpy(ctx->streams.p, streams, (size_t)n * 8, cudaMemcpyHostToDevice));
+    k_fill_default_records<<<blocks_for(n, 128), 128, 0, ctx->stream>>>(n, ctx->recout.as<double>());
+    ctx->stats.kernel_launches++;
+    WaveParams wp; memset(&wp, 0, sizeof(wp));
+    wp.width = ctx->width; wp.height = ctx->height; wp.y0 = 0; wp.y1 = ctx->height; wp.tiles_x = (ctx->width + 7) / 8;
+    wp.n_paths = n; wp.npix_pad = n; wp.spp_total = 1; wp.seed = r.seed;
+    wp.xs = ctx->xs.as<int>(); wp.ys = ctx->ys.as<int>(); wp.streams = ctx->streams.as<unsigned long long>();
+    wp.rec_out = ctx->recout.as<double>();
+    int rc;
+    if (r.precision == GDPT_PRECISION_F64) { DScene<double> sc = ctx->sc_d; sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth; rc = run_wave<double>(ctx, sc, wp); }
+    else { DScene<float> sc = ctx->sc_f; sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth; rc = run_wave<float>(ctx, sc, wp); }
+    if (rc) return rc;
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    GD_CUDA(cudaMemcpy(rec, ctx->recout.p, (size_t)n * 23 * 8, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+} // extern "C"

@@ -1,0 +1,129 @@
+// C ABI, second half: the stand-alone Poisson entry point with host buffers and the
+// validation entry points (gdpt_sample_primary / gdpt_intersect / gdpt_bsdf /
+// gdpt_grad_samples / gdpt_pcg_fill).  They run the renderer's own device functions.
+#include "gdpt_context.cuh"
+#include "gdpt_debug.cuh"
+
+using namespace gdpt;
+
+namespace {
+inline int blocks_for(long long n, int block) { return (int)((n + block - 1) / block); }
+
+struct Scratch {   // device scratch that frees itself
+    std::vector<void *> ptrs;
+    ~Scratch() { for (void *p : ptrs) cudaFree(p); }
+    template <typename T> int alloc(T **out, size_t n) {
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, std::max<size_t>(n * sizeof(T), 16));
+        if (e != cudaSuccess) return fail(GDPT_ERR_CUDA, "cudaMalloc failed: %s", cudaGetErrorString(e));
+        ptrs.push_back(p); *out = (T *)p; return 0;
+    }
+    template <typename T> int put(T **out, const T *host, size_t n) {
+        if (int r = alloc(out, n)) return r;
+        if (host && n) GD_CUDA(cudaMemcpy(*out, host, n * sizeof(T), cudaMemcpyHostToDevice));
+        return 0;
+    }
+};
+} // namespace
+
+// implemented in gdpt_api.cu
+extern "C" int gdpt_poisson_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
+
+extern "C" {
+
+int gdpt_poisson(int device, int w, int h, const double *u, const double *gx, const double *gy, double alpha, double *out) {
+    if (!u || !gx || !gy || !out) return fail(GDPT_ERR_ARG, "null argument");
+    if (w < 2 || h < 2) return fail(GDPT_ERR_ARG, "Poisson solve needs at least a 2x2 image");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(GDPT_ERR_CUDA, "no CUDA device: libgdpt has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(GDPT_ERR_ARG, "device out of range");
+    GD_CUDA(cudaSetDevice(device));
+    // a bare context (no scene) that only carries the stream and the Poisson cache
+    gdpt_ctx *c = new gdpt_ctx();
+    c->device = device; memset(&c->stats, 0, sizeof(c->stats));
+    for (auto &e : c->ev) e = nullptr;
+    int rc = 0;
+    size_t n = (size_t)w * h * 3;
+    Scratch s; double *du, *dgx, *dgy, *dout;
+    do {
+        if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = fail(GDPT_ERR_CUDA, "stream creation failed"); break; }
+        if ((rc = s.put(&du, u, n))) break;
+        if ((rc = s.put(&dgx, gx, n))) break;
+        if ((rc = s.put(&dgy, gy, n))) break;
+        if ((rc = s.alloc(&dout, n))) break;
+        if ((rc = gdpt_poisson_device(c, w, h, du, dgx, dgy, alpha, dout))) break;
+        if (cudaStreamSynchronize(c->stream) != cudaSuccess) { rc = fail(GDPT_ERR_CUDA, "Poisson kernels failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
+        if (cudaMemcpy(out, dout, n * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) { rc = fail(GDPT_ERR_CUDA, "copy back failed"); break; }
+    } while (false);
+    destroy_context(c);
+    return rc;
+}
+
+int gdpt_sample_primary(gdpt_ctx *ctx, int precision, int n, const double *screen_pos, double *rays) {
+    if (!ctx || !screen_pos || !rays || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
+    if (n == 0) return 0;
+    GD_CUDA(cudaSetDevice(ctx->device));
+    Scratch s; double *dsp, *dr;
+    if (int r = s.put(&dsp, screen_pos, (size_t)n * 2)) return r;
+    if (int r = s.alloc(&dr, (size_t)n * 6)) return r;
+    if (precision == GDPT_PRECISION_F64) k_dbg_sample_primary<double><<<blocks_for(n, 128), 128, 0, ctx->stream>>>(ctx->sc_d, n, dsp, dr);
+    else k_dbg_sample_primary<float><<<blocks_for(n, 128), 128, 0, ctx->stream>>>(ctx->sc_f, n, dsp, dr);
+    ctx->stats.kernel_launches++;
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    GD_CUDA(cudaMemcpy(rays, dr, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int gdpt_intersect(gdpt_ctx *ctx, int precision, int n, const double *rays, const double *rdiff, int32_t *ids, double *vtx) {
+    if (!ctx || !rays || !ids || !vtx || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
+    if (n == 0) return 0;
+    GD_CUDA(cudaSetDevice(ctx->device));
+    Scratch s; double *dr, *drd = nullptr, *dv; int *di;
+    if (int r = s.put(&dr, rays, (size_t)n * 8)) return r;
+    if (rdiff) if (int r = s.put(&drd, rdiff, (size_t)n * 2)) return r;
+    if (int r = s.alloc(&di, (size_t)n * 3)) return r;
+    if (int r = s.alloc(&dv, (size_t)n * 24)) return r;
+    if (precision == GDPT_PRECISION_F64) k_dbg_intersect<double, true><<<blocks_for(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->sc_d, ctx->bvh, n, dr, drd, di, dv);
+    else k_dbg_intersect<float, false><<<blocks_for(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->sc_f, ctx->bvh, n, dr, drd, di, dv);
+    ctx->stats.kernel_launches++;
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    GD_CUDA(cudaMemcpy(ids, di, (size_t)n * 3 * sizeof(int), cudaMemcpyDeviceToHost));
+    GD_CUDA(cudaMemcpy(vtx, dv, (size_t)n * 24 * sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int gdpt_bsdf(gdpt_ctx *ctx, int precision, int mat_id, int n, const double *vtx, const double *dirs, const double *rnd, double *out) {
+    if (!ctx || !vtx || !dirs || !rnd || !out || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
+    if (mat_id < 0 || mat_id >= ctx->sc_d.n_materials) return fail(GDPT_ERR_ARG, "material id out of range");
+    if (n == 0) return 0;
+    GD_CUDA(cudaSetDevice(ctx->device));
+    Scratch s; double *dv, *dd, *drn, *dout;
+    if (int r = s.put(&dv, vtx, (size_t)n * 15)) return r;
+    if (int r = s.put(&dd, dirs, (size_t)n * 6)) return r;
+    if (int r = s.put(&drn, rnd, (size_t)n * 3)) return r;
+    if (int r = s.alloc(&dout, (size_t)n * 10)) return r;
+    if (precision == GDPT_PRECISION_F64) k_dbg_bsdf<double><<<blocks_for(n, 64), 64, 0, ctx->stream>>>(ctx->sc_d, mat_id, n, dv, dd, drn, dout);
+    else k_dbg_bsdf<float><<<blocks_for(n, 64), 64, 0, ctx->stream>>>(ctx->sc_f, mat_id, n, dv, dd, drn, dout);
+    ctx->stats.kernel_launches++;
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    GD_CUDA(cudaMemcpy(out, dout, (size_t)n * 10 * sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int gdpt_pcg_fill(int device, uint64_t stream, uint64_t seed, int n, double *out, uint32_t *raw) {
+    if (!out || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(GDPT_ERR_CUDA, "no CUDA device: libgdpt has no CPU fallback");
+    if (n == 0) return 0;
+    GD_CUDA(cudaSetDevice(device));
+    Scratch s; double *dout; unsigned int *draw = nullptr;
+    if (int r = s.alloc(&dout, (size_t)n)) return r;
+    if (raw) if (int r = s.alloc(&draw, (size_t)n)) return r;
+    k_dbg_pcg<<<1, 32>>>(stream, seed ? seed : 0x31e241f862a1fb5eULL, n, dout, draw);
+    GD_CUDA(cudaDeviceSynchronize());
+    GD_CUDA(cudaMemcpy(out, dout, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
+    if (raw) GD_CUDA(cudaMemcpy(raw, draw, (size_t)n * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+} // extern "C"

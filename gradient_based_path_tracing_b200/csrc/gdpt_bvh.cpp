@@ -99,7 +99,7 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
                 BvhPrim p;
                 Ref r; r.b.reset();
                 for (int k = 0; k < 3; k++) {
-                    p.v0[k] = v[0][k]; p.e1[k] = v[1][k] - v[0][k]; p.e2[k] = v[2][k] - v[0][k];
+                    p.v0[k] = v[0][k]; p.v1[k] = v[1][k]; p.v2[k] = v[2][k];
                     r.b.lo[k] = std::min(v[0][k], std::min(v[1][k], v[2][k]));
                     r.b.hi[k] = std::max(v[0][k], std::max(v[1][k], v[2][k]));
                     r.c[k] = 0.5f * (r.b.lo[k] + r.b.hi[k]);
@@ -112,7 +112,7 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
             BvhPrim p;
             Ref r;
             for (int k = 0; k < 3; k++) {
-                p.v0[k] = (float)sh.sphere[k]; p.e1[k] = 0; p.e2[k] = 0;
+                p.v0[k] = (float)sh.sphere[k]; p.v1[k] = 0; p.v2[k] = 0;
                 // RTCBounds are floats: (float)(centre -/+ radius) as sphere_bounds_func stores them
                 r.b.lo[k] = (float)(sh.sphere[k] - sh.sphere[3]);
                 r.b.hi[k] = (float)(sh.sphere[k] + sh.sphere[3]);
@@ -121,7 +121,7 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
                 if ((double)r.b.hi[k] < sh.sphere[k] + sh.sphere[3]) r.b.hi[k] = std::nextafter(r.b.hi[k], std::numeric_limits<float>::infinity());
                 r.c[k] = (float)sh.sphere[k];
             }
-            p.e1[0] = (float)sh.sphere[3];
+            p.v1[0] = (float)sh.sphere[3];
             p.prim_id = 0; p.shape_id = s; p.kind = 1;
             r.idx = (int)src.size();
             src.push_back(p); B.refs.push_back(r);
@@ -183,7 +183,7 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
             BvhNode &w = out.nodes[it.wide];
             w.lox[i] = k.b.lo[0]; w.loy[i] = k.b.lo[1]; w.loz[i] = k.b.lo[2];
             w.hix[i] = k.b.hi[0]; w.hiy[i] = k.b.hi[1]; w.hiz[i] = k.b.hi[2];
-            if (k.left < 0) { w.child[i] = ~k.first; w.count[i] = k.count; }
+            if (k.left < 0) { w.child[i] = ~((k.first << 3) | k.count); w.count[i] = k.count; }
             else {
                 int c = new_wide();
                 out.nodes[it.wide].child[i] = c; out.nodes[it.wide].count[i] = 0;

@@ -5,10 +5,12 @@
 //
 // Node (128 B, one L2/L1 line, 8 x 16-byte vector loads):
 //   float4 lox, loy, loz, hix, hiy, hiz   bounds of the 4 children, SoA over children
-//   int4   child                           >=0: node index; <0: leaf, first primitive = ~child
-//   int4   count                           primitives in the leaf (0 = empty slot / inner node)
-// Primitive (48 B, 3 x 16-byte loads): v0.xyz | prim_id,  e1.xyz | shape_id,  e2.xyz | kind
-//   kind 0 = triangle (e1 = v1-v0, e2 = v2-v0), kind 1 = sphere (data in DScene::spheres)
+//   int4   child                           >0: node index; <0: leaf, ~child = (first primitive << 3) | count;
+//                                          0: empty slot (its bounds are inverted, never hit)
+//   int4   count                           primitives in the leaf (informational; pads the node to 128 B)
+// Primitive (48 B, 3 x 16-byte loads): v0.xyz | prim_id,  v1.xyz | shape_id,  v2.xyz | kind
+//   kind 0 = triangle (float-rounded vertices, exactly what Embree would hold),
+//   kind 1 = sphere (centre/radius stay double in DScene::spheres, as in sphere.inl)
 #pragma once
 #include <cstdint>
 #include <vector>
@@ -24,8 +26,8 @@ static_assert(sizeof(BvhNode) == 128, "node must be one 128-byte line");
 
 struct BvhPrim {
     float v0[3]; int prim_id;
-    float e1[3]; int shape_id;
-    float e2[3]; int kind;
+    float v1[3]; int shape_id;
+    float v2[3]; int kind;
 };
 static_assert(sizeof(BvhPrim) == 48, "primitive record must be 48 bytes");
 

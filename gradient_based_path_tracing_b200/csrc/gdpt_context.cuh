@@ -1,0 +1,246 @@
+// Host-side context behind the C ABI: device copies of the flattened scene in both
+// arithmetic modes, mip chains, the BVH, wavefront queues and Poisson work buffers.
+#pragma once
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/gdpt.h"
+#include "gdpt_bvh.h"
+#include "gdpt_poisson.cuh"
+#include "gdpt_shade.cuh"
+
+namespace gdpt {
+
+inline std::string &last_error() { static thread_local std::string e; return e; }
+inline int fail(int code, const char *fmt, ...) {
+    char buf[512]; va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    last_error() = buf; return code;
+}
+#define GD_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(GDPT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+struct DevBuf {
+    void *p = nullptr; size_t bytes = 0;
+    int ensure(size_t n) {
+        if (n <= bytes) return 0;
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e != cudaSuccess) return fail(GDPT_ERR_CUDA, "cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
+        bytes = n; return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    template <typename T> T *as() const { return (T *)p; }
+};
+
+template <typename T> int upload(DevBuf &b, const std::vector<T> &v) {
+    if (int r = b.ensure(std::max<size_t>(v.size() * sizeof(T), 16))) return r;
+    if (!v.empty()) GD_CUDA(cudaMemcpy(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+struct PoissonCache {                 // DCT matrices per image size
+    int w = 0, h = 0;
+    DevBuf Dw, DhT, work, work2, partial, dc;
+    void release() { Dw.release(); DhT.release(); work.release(); work2.release(); partial.release(); dc.release(); w = h = 0; }
+};
+
+} // namespace gdpt
+
+struct gdpt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int width = 0, height = 0;
+    int max_depth = -1, rr_depth = 5, spp = 4;
+    double bounds[4] = {0, 0, 0, 0};
+    // scene arrays
+    gdpt::DevBuf shapes, spheres, indices, materials, img3, img1;
+    gdpt::DevBuf pos_d, nrm_d, uv_d, tex_d, texels3_d, texels1_d, light_d;   // exact mode
+    gdpt::DevBuf pos_f, nrm_f, uv_f, tex_f, texels3_f, texels1_f, light_f;   // fast mode
+    gdpt::DevBuf bvh_nodes, bvh_prims;
+    gdpt::DScene<double> sc_d;
+    gdpt::DScene<float> sc_f;
+    gdpt::DBvh bvh;
+    int bvh_depth = 0;
+    // wavefront queues
+    gdpt::DevBuf gen, rays, hits, rec_a, rec_b, off, counters, recout, xs, ys, streams;
+    int *h_counts = nullptr;          // pinned
+    // accumulation / output images
+    gdpt::DevBuf img, cx0, cy0, cx1, cy1, cx, cy, out;
+    gdpt::PoissonCache pc;
+    gdpt_stats stats;
+    cudaEvent_t ev[8];
+};
+
+namespace gdpt {
+
+// make_mipmap (mipmap.h:28-44): 2x2 box filter, at most 8 levels.  The reference indexes
+// prev(2x+1, 2y+1) even when a dimension has already collapsed to 1, i.e. it reads the flat
+// element y*width+x beyond the row / the image; we reproduce the flat indexing and clamp
+// the final out-of-bounds element (documented in DESIGN.md "quirks kept").
+inline void build_mips(int w, int h, int C, const std::vector<double> &lvl0, DImage &im, std::vector<double> &pool) {
+    int size = w > h ? w : h;
+    int levels = std::min((int)ceil(log2((double)size) + 1), 8);
+    im.n_levels = levels; im.channels = C;
+    std::vector<double> prev = lvl0; int pw = w, ph = h;
+    for (int l = 0; l < levels; l++) {
+        if (l > 0) {
+            int nw = std::max(pw / 2, 1), nh = std::max(ph / 2, 1);
+            std::vector<double> next((size_t)nw * nh * C);
+            size_t plast = (size_t)pw * ph - 1;
+            auto at = [&](int x, int y, int c) { size_t i = (size_t)y * pw + x; if (i > plast) i = plast; return prev[i * C + c]; };
+            for (int y = 0; y < nh; y++) for (int x = 0; x < nw; x++) for (int c = 0; c < C; c++)
+                next[((size_t)y * nw + x) * C + c] = (at(2 * x, 2 * y, c) + at(2 * x + 1, 2 * y, c) + at(2 * x, 2 * y + 1, c) + at(2 * x + 1, 2 * y + 1, c)) * (1.0 / 4.0);
+            prev.swap(next); pw = nw; ph = nh;
+        }
+        im.w[l] = pw; im.h[l] = ph; im.off[l] = (long long)(pool.size() / C);
+        pool.insert(pool.end(), prev.begin(), prev.end());
+    }
+    for (int l = levels; l < 8; l++) { im.w[l] = im.h[l] = 1; im.off[l] = 0; }
+}
+
+inline int decode_image(const gdpt_image &gi, int C, std::vector<double> &out) {
+    if (gi.channels != C || gi.width <= 0 || gi.height <= 0) return fail(GDPT_ERR_ARG, "bad image (%d x %d x %d)", gi.width, gi.height, gi.channels);
+    size_t n = (size_t)gi.width * gi.height * C;
+    out.resize(n);
+    if (gi.data) memcpy(out.data(), gi.data, n * sizeof(double));
+    else if (gi.palette && gi.index) { for (size_t i = 0; i < n; i++) { if (gi.index[i] >= gi.palette_size) return fail(GDPT_ERR_ARG, "palette index out of range"); out[i] = gi.palette[gi.index[i]]; } }
+    else return fail(GDPT_ERR_ARG, "image has neither data nor palette");
+    return 0;
+}
+
+template <typename R> void fill_scene_common(DScene<R> &s, const gdpt_scene_desc *d) {
+    for (int i = 0; i < 16; i++) { s.s2c[i] = (R)d->sample_to_cam[i]; s.c2w[i] = (R)d->cam_to_world[i]; }
+    s.width = d->width; s.height = d->height; s.filter_kind = d->filter_kind; s.filter_param = (R)d->filter_param;
+    s.n_shapes = d->n_shapes; s.n_materials = d->n_materials; s.n_lights = d->n_lights;
+    s.max_depth = d->max_depth; s.rr_depth = d->rr_depth;
+}
+
+inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) {
+    if (!d || !out) return fail(GDPT_ERR_ARG, "null argument");
+    if (d->width <= 1 || d->height <= 1) return fail(GDPT_ERR_ARG, "film must be at least 2x2");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(GDPT_ERR_CUDA, "no CUDA device: libgdpt has no CPU fallback");
+    if (device < 0 || device >= ndev) return fail(GDPT_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
+    GD_CUDA(cudaSetDevice(device));
+    gdpt_ctx *c = new gdpt_ctx();
+    c->device = device; c->width = d->width; c->height = d->height;
+    c->max_depth = d->max_depth; c->rr_depth = d->rr_depth; c->spp = d->samples_per_pixel;
+    memset(&c->stats, 0, sizeof(c->stats));
+    *out = c;
+    GD_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (auto &e : c->ev) GD_CUDA(cudaEventCreate(&e));
+    GD_CUDA(cudaMallocHost((void **)&c->h_counts, 64));
+
+    // ---- shapes + BVH
+    std::vector<DShape> shapes(d->n_shapes);
+    std::vector<HostShape> hs(d->n_shapes);
+    for (int i = 0; i < d->n_shapes; i++) {
+        const int32_t *s = d->shapes + 6 * i; const int64_t *o = d->shape_offsets + 4 * i;
+        DShape &ds = shapes[i];
+        ds.kind = s[0]; ds.material_id = s[1]; ds.area_light_id = s[2]; ds.flags = s[5];
+        ds.vtx_off = (int)o[0]; ds.tri_off = (int)o[1]; ds.nrm_off = (int)o[2]; ds.uv_off = (int)o[3];
+        if (ds.material_id < 0 || ds.material_id >= d->n_materials) return fail(GDPT_ERR_ARG, "shape %d: material id %d out of range", i, ds.material_id);
+        if (ds.area_light_id >= d->n_lights) return fail(GDPT_ERR_ARG, "shape %d: light id out of range", i);
+        HostShape &h = hs[i];
+        h.kind = s[0]; h.nverts = s[3]; h.ntris = s[4];
+        h.positions = d->positions + 3 * o[0]; h.indices = d->indices + 3 * o[1];
+        for (int k = 0; k < 4; k++) h.sphere[k] = d->spheres[4 * i + k];
+        if (h.kind == 1) for (int t = 0; t < 3 * h.ntris; t++) if (h.indices[t] < 0 || h.indices[t] >= h.nverts) return fail(GDPT_ERR_ARG, "shape %d: vertex index out of range", i);
+    }
+    Bvh bvh; build_bvh(hs, bvh);
+    if (3 * bvh.max_depth + 1 > STACK_SMEM + STACK_SPILL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
+    c->bvh_depth = bvh.max_depth;
+    if (int r = upload(c->shapes, shapes)) return r;
+    { std::vector<double> sp(d->spheres, d->spheres + 4 * (size_t)d->n_shapes); if (int r = upload(c->spheres, sp)) return r; }
+    if (int r = upload(c->bvh_nodes, bvh.nodes)) return r;
+    if (int r = upload(c->bvh_prims, bvh.prims)) return r;
+    c->bvh.nodes = c->bvh_nodes.as<float4>(); c->bvh.prims = c->bvh_prims.as<float4>(); c->bvh.spheres = c->spheres.as<double>();
+    c->bvh.n_nodes = bvh.prims.empty() ? 0 : (int)bvh.nodes.size(); c->bvh.n_prims = (int)bvh.prims.size();
+    // bounds sphere (scene.cpp:30-34): float box from the "Embree" scene, arithmetic in double
+    {
+        double lb[3] = {bvh.lo[0], bvh.lo[1], bvh.lo[2]}, ub[3] = {bvh.hi[0], bvh.hi[1], bvh.hi[2]};
+        double dx = ub[0] - lb[0], dy = ub[1] - lb[1], dz = ub[2] - lb[2];
+        c->bounds[0] = sqrt(dx * dx + dy * dy + dz * dz) / 2;
+        for (int k = 0; k < 3; k++) c->bounds[1 + k] = (lb[k] + ub[k]) / 2.0;
+    }
+    double eps = std::min(c->bounds[0] * 1e-5, 0.01);   // scene.h:104-106
+
+    // ---- geometry pools
+    std::vector<double> pos(d->positions, d->positions + 3 * (size_t)d->n_positions), nrm(d->normals, d->normals + 3 * (size_t)d->n_normals),
+        uv(d->uvs, d->uvs + 2 * (size_t)d->n_uvs);
+    std::vector<int> idx(d->indices, d->indices + 3 * (size_t)d->n_triangles);
+    auto to_f = [](const std::vector<double> &v) { return std::vector<float>(v.begin(), v.end()); };
+    if (int r = upload(c->pos_d, pos)) return r; if (int r = upload(c->nrm_d, nrm)) return r; if (int r = upload(c->uv_d, uv)) return r;
+    if (int r = upload(c->pos_f, to_f(pos))) return r; if (int r = upload(c->nrm_f, to_f(nrm))) return r; if (int r = upload(c->uv_f, to_f(uv))) return r;
+    if (int r = upload(c->indices, idx)) return r;
+
+    // ---- materials / textures / images
+    std::vector<DMaterial> mats(d->n_materials);
+    for (int i = 0; i < d->n_materials; i++) {
+        const double *m = d->materials + 14 * i;
+        mats[i].type = (int)m[0]; mats[i].eta = m[1];
+        if (mats[i].type < 0 || mats[i].type >= MAT_COUNT) return fail(GDPT_ERR_ARG, "material %d: unknown type %d", i, mats[i].type);
+        for (int k = 0; k < 12; k++) { mats[i].tex[k] = (int)m[2 + k]; if (mats[i].tex[k] >= d->n_textures) return fail(GDPT_ERR_ARG, "material %d: texture id out of range", i); }
+    }
+    if (int r = upload(c->materials, mats)) return r;
+    std::vector<DTexture<double>> td(d->n_textures); std::vector<DTexture<float>> tf(d->n_textures);
+    for (int i = 0; i < d->n_textures; i++) {
+        const double *t = d->textures + 14 * i;
+        td[i].kind = (int)t[0]; td[i].image_id = (int)t[8];
+        bool spec = t[1] != 0;
+        if (td[i].kind == TEX_IMAGE && (td[i].image_id < 0 || td[i].image_id >= (spec ? d->n_images3 : d->n_images1))) return fail(GDPT_ERR_ARG, "texture %d: image id out of range", i);
+        for (int k = 0; k < 3; k++) { td[i].v0[k] = t[2 + k]; td[i].v1[k] = t[5 + k]; }
+        td[i].uscale = t[9]; td[i].vscale = t[10]; td[i].uoffset = t[11]; td[i].voffset = t[12];
+        tf[i].kind = td[i].kind; tf[i].image_id = td[i].image_id;
+        for (int k = 0; k < 3; k++) { tf[i].v0[k] = (float)td[i].v0[k]; tf[i].v1[k] = (float)td[i].v1[k]; }
+        tf[i].uscale = (float)t[9]; tf[i].vscale = (float)t[10]; tf[i].uoffset = (float)t[11]; tf[i].voffset = (float)t[12];
+    }
+    if (int r = upload(c->tex_d, td)) return r; if (int r = upload(c->tex_f, tf)) return r;
+    std::vector<DImage> im3(d->n_images3), im1(d->n_images1);
+    std::vector<double> pool3, pool1, tmp;
+    for (int i = 0; i < d->n_images3; i++) { if (int r = decode_image(d->images3[i], 3, tmp)) return r; build_mips(d->images3[i].width, d->images3[i].height, 3, tmp, im3[i], pool3); }
+    for (int i = 0; i < d->n_images1; i++) { if (int r = decode_image(d->images1[i], 1, tmp)) return r; build_mips(d->images1[i].width, d->images1[i].height, 1, tmp, im1[i], pool1); }
+    if (int r = upload(c->img3, im3)) return r; if (int r = upload(c->img1, im1)) return r;
+    if (int r = upload(c->texels3_d, pool3)) return r; if (int r = upload(c->texels1_d, pool1)) return r;
+    { std::vector<float4> p4(pool3.size() / 3); for (size_t i = 0; i < p4.size(); i++) p4[i] = make_float4((float)pool3[3 * i], (float)pool3[3 * i + 1], (float)pool3[3 * i + 2], 0.f);
+      if (int r = upload(c->texels3_f, p4)) return r; if (int r = upload(c->texels1_f, to_f(pool1))) return r; }
+    std::vector<double> li(3 * (size_t)std::max(d->n_lights, 1), 0.0);
+    for (int i = 0; i < d->n_lights; i++) for (int k = 0; k < 3; k++) li[3 * i + k] = d->lights[5 * i + 2 + k];
+    if (int r = upload(c->light_d, li)) return r; if (int r = upload(c->light_f, to_f(li))) return r;
+
+    fill_scene_common(c->sc_d, d); fill_scene_common(c->sc_f, d);
+    c->sc_d.eps = eps; c->sc_f.eps = (float)eps;
+    c->sc_d.shapes = c->sc_f.shapes = c->shapes.as<DShape>();
+    c->sc_d.spheres = c->sc_f.spheres = c->spheres.as<double>();
+    c->sc_d.indices = c->sc_f.indices = c->indices.as<int>();
+    c->sc_d.materials = c->sc_f.materials = c->materials.as<DMaterial>();
+    c->sc_d.img3 = c->sc_f.img3 = c->img3.as<DImage>(); c->sc_d.img1 = c->sc_f.img1 = c->img1.as<DImage>();
+    c->sc_d.positions = c->pos_d.as<double>(); c->sc_d.normals = c->nrm_d.as<double>(); c->sc_d.uvs = c->uv_d.as<double>();
+    c->sc_f.positions = c->pos_f.as<float>(); c->sc_f.normals = c->nrm_f.as<float>(); c->sc_f.uvs = c->uv_f.as<float>();
+    c->sc_d.textures = c->tex_d.as<DTexture<double>>(); c->sc_f.textures = c->tex_f.as<DTexture<float>>();
+    c->sc_d.texels3 = c->texels3_d.as<double>(); c->sc_d.texels1 = c->texels1_d.as<double>();
+    c->sc_f.texels3 = c->texels3_f.as<float4>(); c->sc_f.texels1 = c->texels1_f.as<float>();
+    c->sc_d.light_intensity = c->light_d.as<double>(); c->sc_f.light_intensity = c->light_f.as<float>();
+    return 0;
+}
+
+inline void destroy_context(gdpt_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    gdpt::DevBuf *all[] = {&c->shapes, &c->spheres, &c->indices, &c->materials, &c->img3, &c->img1, &c->pos_d, &c->nrm_d, &c->uv_d, &c->tex_d,
+                           &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tex_f, &c->texels3_f, &c->texels1_f,
+                           &c->light_f, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
+                           &c->recout, &c->xs, &c->ys, &c->streams, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
+    for (auto *b : all) b->release();
+    c->pc.release();
+    if (c->h_counts) cudaFreeHost(c->h_counts);
+    for (auto &e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+} // namespace gdpt

@@ -1,0 +1,192 @@
+// Shading half of the wavefront (see gdpt_wavefront.cuh for the overview).
+#pragma once
+#include "gdpt_wavefront.cuh"
+
+namespace gdpt {
+
+// A finished sample -> the GraidentPTRadiance record (intersection.h:65-77) and its
+// accumulation (render.cpp:311-327).  contribS/wS for disabled offsets are 0 / 1.
+template <typename R>
+GD_D void finish_path(const WaveParams &wp, int px, int py, int id, const V3<R> &rad, const double contrib[3], double prob,
+                      const double cS[4][3], const double wS[4]) {
+    if (wp.rec_out) {
+        double *o = wp.rec_out + (size_t)id * 23;
+        o[0] = rad.x; o[1] = rad.y; o[2] = rad.z;
+        o[3] = contrib[0]; o[4] = contrib[1]; o[5] = contrib[2];
+        // record order: contribX0, contribX1, contribY0, contribY1 ; offsets here are X0,Y0,X1,Y1
+        const int slot[4] = {0, 2, 1, 3};
+        for (int k = 0; k < 4; k++) for (int c = 0; c < 3; c++) o[6 + 3 * slot[k] + c] = cS[k][c];
+        o[18] = prob; o[19] = wS[0]; o[20] = wS[1]; o[21] = wS[2]; o[22] = wS[3];
+        return;
+    }
+    if (!(prob > 0.0)) return;
+    size_t p = ((size_t)py * wp.width + px) * 3;
+    double spp = (double)wp.spp_total;
+    double inv_spp = 1.0 / spp;                      // Vector3 / Real multiplies by the reciprocal
+    double rd[3] = {(double)rad.x, (double)rad.y, (double)rad.z};
+    double *bufs[4] = {wp.cx0, wp.cy0, wp.cx1, wp.cy1};
+    const double sign[4] = {1.0, 1.0, -1.0, -1.0};  // X0,Y0: contrib - contribS ; X1,Y1: contribS - contrib
+    for (int c = 0; c < 3; c++) {
+        if (rd[c] != 0.0) atomicAdd(wp.img + p + c, rd[c] * inv_spp);
+        for (int k = 0; k < 4; k++) {
+            double v = sign[k] * (contrib[c] - cS[k][c]) * (wS[k] / (prob * spp));
+            if (v != 0.0) atomicAdd(bufs[k] + p + c, v);
+        }
+    }
+}
+
+template <typename R>
+GD_D void finish_with_offsets(const WaveParams &wp, const PathRec<R> &pr, const OffRec<R> *off, double jac_num /* p2 area, or <0: jacobians stay 1 */) {
+    double cS[4][3], wS[4];
+    for (int k = 0; k < 4; k++) {
+        cS[k][0] = cS[k][1] = cS[k][2] = 0.0; wS[k] = 1.0;
+        if (off && (off->enabled >> k & 1)) {
+            double jac = 1.0;
+            bool ok = true;
+            if (jac_num >= 0.0) {
+                if (off->sampled >> k & 1) jac = jac_num / (double)off->p2s[k];
+                else ok = false;              // replayed sample failed or had pdf <= 0: contribS = 0, w = 1
+            }
+            if (ok) {
+                cS[k][0] = (double)off->contrib[k].x * jac; cS[k][1] = (double)off->contrib[k].y * jac; cS[k][2] = (double)off->contrib[k].z * jac;
+                wS[k] = pr.prob / (pr.prob + 1.0 * jac);
+            }
+        }
+    }
+    finish_path<R>(wp, pr.px, pr.py, pr.id, pr.rad, pr.contrib, pr.prob, cS, wS);
+}
+
+// Start of a loop iteration at `vtx` (path_tracing.h:528-564 + eval/pdf of :762-763, which
+// depend only on the sampled direction): draws (u,v,w), samples the BSDF, fills the ray.
+// Returns false when sample_bsdf fails (the reference then returns an EMPTY record).
+template <typename R>
+GD_D bool start_iteration(const DScene<R> &sc, const Vertex<R> &vtx, const V3<R> &dir_view, PathRec<R> &pr, RayF &ray) {
+    R u0 = pcg_real<R>(pr.rng), u1 = pcg_real<R>(pr.rng), w = pcg_real<R>(pr.rng);
+    BsdfSample<R> s;
+    if (!bsdf_sample<R>(sc, vtx, dir_view, u0, u1, w, s)) return false;
+    if (s.eta != R(0)) pr.eta_scale /= (s.eta * s.eta);
+    pr.org = vtx.position; pr.dir = s.dir_out;
+    pr.f = bsdf_eval<R>(sc, vtx, dir_view, s.dir_out);
+    pr.p2 = bsdf_pdf<R>(sc, vtx, dir_view, s.dir_out);
+    ray.ox = (float)pr.org.x; ray.oy = (float)pr.org.y; ray.oz = (float)pr.org.z; ray.tnear = (float)sc.eps;
+    ray.dx = (float)pr.dir.x; ray.dy = (float)pr.dir.y; ray.dz = (float)pr.dir.z; ray.tfar = __int_as_float(0x7f800000);
+    return true;
+}
+
+// ---------------------------------------------------------------- primary stage
+template <typename R>
+__global__ void __launch_bounds__(128) k_primary(DScene<R> sc, WaveParams wp, const GenRec<R> *gen, const Hit *hits,
+                                                 PathRec<R> *out, OffRec<R> *off_out, RayF *rays_out, int *out_count) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool alive = false;
+    PathRec<R> pr; OffRec<R> off; RayF ray;
+    if (i < wp.n_paths) {
+        GenRec<R> g = gen[i];
+        Hit h0 = hits[i];
+        if (h0.shape_id >= 0) {   // inactive padding slots carry a ray that cannot hit
+            const int ox[5] = {0, -1, 0, 1, 0}, oy[5] = {0, 0, 1, 0, -1};
+            const R spread0 = R(0.25) / R(sc.width > sc.height ? sc.width : sc.height);   // init_ray_differential
+            V3<R> o, d;
+            sample_primary<R>(sc, (R(g.px) + g.rng_x) / R(sc.width), (R(g.py) + g.rng_y) / R(sc.height), o, d);
+            Vertex<R> vtx;
+            make_vertex<R>(sc, o, d, 0.f, __int_as_float(0x7f800000), h0, R(0), spread0, vtx);
+            pr.px = g.px; pr.py = g.py; pr.id = g.id; pr.rng = g.rng; pr.nv = 3;
+            pr.thr = V3<R>(1, 1, 1); pr.rad = V3<R>(0, 0, 0); pr.eta_scale = R(1);
+            pr.contrib[0] = pr.contrib[1] = pr.contrib[2] = 1.0; pr.prob = 1.0;
+            V3<R> dir_view = -d;
+            if (is_light(sc, vtx.shape_id)) {
+                V3<R> e = emission<R>(sc, vtx, dir_view);
+                pr.rad = pr.rad + pr.thr * e;
+                pr.contrib[0] = e.x; pr.contrib[1] = e.y; pr.contrib[2] = e.z;
+            }
+            // offsets: enabled iff they hit something with the base's material (path_tracing.h:424-443);
+            // each enabled one replays the base's (u,v,w) at its own vertex (path_tracing.h:774-959)
+            const bool loop_runs = sc.max_depth == -1 || 3 <= sc.max_depth + 1;
+            Pcg r2 = pr.rng;
+            const R u0 = pcg_real<R>(r2), u1 = pcg_real<R>(r2), w = pcg_real<R>(r2);
+            off.enabled = 0; off.sampled = 0;
+            for (int k = 0; k < 4; k++) {
+                off.contrib[k] = V3<R>(1, 1, 1); off.p2s[k] = R(1);
+                Hit hk = hits[(size_t)(k + 1) * wp.n_paths + i];
+                if (hk.shape_id < 0) continue;
+                if (sc.shapes[hk.shape_id].material_id != vtx.material_id) continue;
+                V3<R> ok_, dk;
+                sample_primary<R>(sc, (R(g.px + ox[k + 1]) + g.rng_x) / R(sc.width), (R(g.py + oy[k + 1]) + g.rng_y) / R(sc.height), ok_, dk);
+                Vertex<R> vo;
+                make_vertex<R>(sc, ok_, dk, 0.f, __int_as_float(0x7f800000), hk, R(0), spread0, vo);
+                V3<R> dvo = -dk;
+                off.enabled |= 1 << k;
+                if (is_light(sc, vo.shape_id)) off.contrib[k] = emission<R>(sc, vo, dvo);
+                if (!loop_runs) continue;
+                BsdfSample<R> s;
+                if (!bsdf_sample<R>(sc, vo, dvo, u0, u1, w, s)) continue;
+                R p = bsdf_pdf<R>(sc, vo, dvo, s.dir_out);
+                if (p <= R(0)) continue;
+                off.p2s[k] = p; off.sampled |= 1 << k;
+            }
+            if (!loop_runs) {
+                finish_with_offsets<R>(wp, pr, &off, -1.0);
+            } else {
+                if (start_iteration<R>(sc, vtx, dir_view, pr, ray)) alive = true;
+                // sample_bsdf failure at the base vertex: `return GraidentPTRadiance{}` -> contributes nothing
+            }
+        }
+    }
+    int slot = warp_slot(alive, out_count);
+    if (alive) { out[slot] = pr; off_out[slot] = off; rays_out[slot] = ray; }
+}
+
+// ---------------------------------------------------------------- bounce stage
+template <typename R>
+__global__ void __launch_bounds__(128) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
+                                                const Hit *hits, const int *in_count, int in_max,
+                                                PathRec<R> *out, RayF *rays_out, int *out_count) {
+    int n = min(*in_count, in_max);
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool alive = false;
+    PathRec<R> pr; RayF ray;
+    if (i < n) {
+        pr = in[i];
+        const bool first = off_in != nullptr;          // iteration with num_vertices == 3
+        OffRec<R> off; if (first) off = off_in[i];
+        const OffRec<R> *offp = first ? &off : nullptr;
+        Hit h = hits[i];
+        bool hit = h.shape_id >= 0;
+        Vertex<R> nv;
+        R G = R(1);
+        if (hit) {
+            make_vertex<R>(sc, pr.org, pr.dir, (float)sc.eps, __int_as_float(0x7f800000), h, R(0), R(0), nv);   // intersect(scene, bsdf_ray): default ray differential
+            G = fabs(dot(pr.dir, nv.gn)) / distance_squared(nv.position, pr.org);
+        }
+        do {
+            if (pr.p2 <= R(0)) { finish_with_offsets<R>(wp, pr, offp, -1.0); break; }     // path_tracing.h:766-769 (offset jacobians still 1)
+            R p2 = pr.p2 * G;
+            pr.contrib[0] = pr.contrib[0] * (double)pr.f.x * (double)G; pr.contrib[1] = pr.contrib[1] * (double)pr.f.y * (double)G;
+            pr.contrib[2] = pr.contrib[2] * (double)pr.f.z * (double)G;
+            pr.prob *= (double)p2;
+            if (hit && is_light(sc, nv.shape_id)) {
+                V3<R> L = emission<R>(sc, nv, -pr.dir);
+                V3<R> C2 = (G * pr.f) * L;
+                pr.contrib[0] *= (double)L.x; pr.contrib[1] *= (double)L.y; pr.contrib[2] *= (double)L.z;
+                C2 = C2 / p2;
+                pr.rad = pr.rad + pr.thr * C2;
+            }
+            if (!hit) { finish_with_offsets<R>(wp, pr, offp, (double)p2); break; }
+            R rr = R(1);
+            if (pr.nv - 1 >= sc.rr_depth) {
+                rr = rmin(max3((R(1) / pr.eta_scale) * pr.thr), R(0.95));
+                if (pcg_real<R>(pr.rng) > rr) { finish_with_offsets<R>(wp, pr, offp, (double)p2); break; }
+            }
+            pr.thr = (pr.thr * (G * pr.f)) / (p2 * rr);
+            pr.nv++;
+            if (!(sc.max_depth == -1 || pr.nv <= sc.max_depth + 1)) { finish_with_offsets<R>(wp, pr, offp, (double)p2); break; }
+            // the loop goes on: from here every offset is dropped (garbage-vertex rule, path_tracing.h:607-612,1007-1010)
+            V3<R> dir_view = -pr.dir;
+            if (start_iteration<R>(sc, nv, dir_view, pr, ray)) alive = true;
+        } while (false);
+    }
+    int slot = warp_slot(alive, out_count);
+    if (alive) { out[slot] = pr; rays_out[slot] = ray; }
+}
+
+} // namespace gdpt

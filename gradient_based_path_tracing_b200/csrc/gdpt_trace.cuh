@@ -1,0 +1,141 @@
+// Closest-hit traversal of the 4-wide BVH (gdpt_bvh.h) — the replacement for
+// rtcIntersect1 (/root/reference/src/intersection.cpp:15-36) and the sphere user-geometry
+// callback (/root/reference/src/shapes/sphere.inl:40-106).
+//
+//  * one thread per ray; the ray is the FLOAT ray Embree would be handed;
+//  * node = one 128-byte line fetched as 8 x 16-byte __ldg loads, 4 slab tests;
+//  * children visited front to back; the traversal stack lives in shared memory
+//    ([level][thread] -> bank-conflict free) with a small local-memory spill;
+//  * hit rule: tnear < t <= tfar, closest t, ties -> smaller shape id, then smaller
+//    primitive id (same rule as the oracle's Embree stand-in);
+//  * EXACT=true evaluates Moeller-Trumbore in double on the float vertices (bit-comparable
+//    with the oracle), EXACT=false in float.
+#pragma once
+#include "gdpt_scene.cuh"
+
+namespace gdpt {
+
+struct DBvh {
+    const float4 *nodes;   // 8 float4 per node
+    const float4 *prims;   // 3 float4 per primitive
+    const double *spheres; // [n_shapes][4]
+    int n_nodes, n_prims;
+};
+
+constexpr int TRACE_BLOCK = 128;
+constexpr int STACK_SMEM = 20;     // entries per thread in shared memory
+constexpr int STACK_SPILL = 44;    // entries per thread in local memory
+
+struct TraceStack {
+    int2 *smem;            // [STACK_SMEM][TRACE_BLOCK]
+    int2 spill[STACK_SPILL];
+    GD_D void put(int sp, int node, float d) {
+        int2 e = make_int2(node, __float_as_int(d));
+        if (sp < STACK_SMEM) smem[sp * TRACE_BLOCK + threadIdx.x] = e; else spill[sp - STACK_SMEM] = e;
+    }
+    GD_D int2 get(int sp) const { return sp < STACK_SMEM ? smem[sp * TRACE_BLOCK + threadIdx.x] : spill[sp - STACK_SMEM]; }
+};
+
+template <bool EXACT>
+GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3], float tnear, float &best, Hit &hit) {
+    float4 a = __ldg(bvh.prims + 3 * pi), b = __ldg(bvh.prims + 3 * pi + 1), c = __ldg(bvh.prims + 3 * pi + 2);
+    int prim_id = __float_as_int(a.w), shape_id = __float_as_int(b.w), kind = __float_as_int(c.w);
+    if (kind == 1) {
+        double t = sphere_hit_d(bvh.spheres + 4 * shape_id, o, d, tnear, best);
+        if (t >= 0.0) { best = (float)t; hit.t = best; hit.u = 0.f; hit.v = 0.f; hit.shape_id = shape_id; hit.prim_id = prim_id; }
+        return;
+    }
+    float t, u, v;
+    if (EXACT) {
+        double e1x = (double)b.x - a.x, e1y = (double)b.y - a.y, e1z = (double)b.z - a.z;
+        double e2x = (double)c.x - a.x, e2y = (double)c.y - a.y, e2z = (double)c.z - a.z;
+        double dx = d[0], dy = d[1], dz = d[2];
+        double px = dy * e2z - dz * e2y, py = dz * e2x - dx * e2z, pz = dx * e2y - dy * e2x;
+        double det = e1x * px + e1y * py + e1z * pz;
+        if (det == 0.0 || det != det) return;
+        double inv = 1.0 / det;
+        double sx = (double)o[0] - a.x, sy = (double)o[1] - a.y, sz = (double)o[2] - a.z;
+        double ud = (sx * px + sy * py + sz * pz) * inv;
+        if (!(ud >= 0.0 && ud <= 1.0)) return;
+        double qx = sy * e1z - sz * e1y, qy = sz * e1x - sx * e1z, qz = sx * e1y - sy * e1x;
+        double vd = (dx * qx + dy * qy + dz * qz) * inv;
+        if (!(vd >= 0.0 && ud + vd <= 1.0)) return;
+        double td = (e2x * qx + e2y * qy + e2z * qz) * inv;
+        if (!(td > (double)tnear && td <= (double)best)) return;
+        t = (float)td; u = (float)ud; v = (float)vd;
+        // an earlier hit whose double t rounded to the same float: keep the ordering rule
+        if (t == best && hit.shape_id >= 0 && !(shape_id < hit.shape_id || (shape_id == hit.shape_id && prim_id < hit.prim_id))) return;
+    } else {
+        float e1x = b.x - a.x, e1y = b.y - a.y, e1z = b.z - a.z;
+        float e2x = c.x - a.x, e2y = c.y - a.y, e2z = c.z - a.z;
+        float px = d[1] * e2z - d[2] * e2y, py = d[2] * e2x - d[0] * e2z, pz = d[0] * e2y - d[1] * e2x;
+        float det = e1x * px + e1y * py + e1z * pz;
+        if (det == 0.f || det != det) return;
+        float inv = 1.0f / det;
+        float sx = o[0] - a.x, sy = o[1] - a.y, sz = o[2] - a.z;
+        u = (sx * px + sy * py + sz * pz) * inv;
+        if (!(u >= 0.f && u <= 1.f)) return;
+        float qx = sy * e1z - sz * e1y, qy = sz * e1x - sx * e1z, qz = sx * e1y - sy * e1x;
+        v = (d[0] * qx + d[1] * qy + d[2] * qz) * inv;
+        if (!(v >= 0.f && u + v <= 1.f)) return;
+        t = (e2x * qx + e2y * qy + e2z * qz) * inv;
+        if (!(t > tnear && t <= best)) return;
+        if (t == best && hit.shape_id >= 0 && !(shape_id < hit.shape_id || (shape_id == hit.shape_id && prim_id < hit.prim_id))) return;
+    }
+    best = t; hit.t = t; hit.u = u; hit.v = v; hit.shape_id = shape_id; hit.prim_id = prim_id;
+}
+
+// smem_stack: TRACE_BLOCK * STACK_SMEM int2 of shared memory owned by the block
+template <bool EXACT>
+GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], float tnear, float tfar, int2 *smem_stack) {
+    Hit hit; hit.t = tfar; hit.u = hit.v = 0.f; hit.shape_id = -1; hit.prim_id = -1;
+    if (bvh.n_nodes == 0) return hit;
+    TraceStack st; st.smem = smem_stack;
+    float idx = 1.0f / d[0], idy = 1.0f / d[1], idz = 1.0f / d[2];
+    float best = tfar;
+    int sp = 0;
+    int cur = 0;   // root node
+    while (true) {
+        if (cur >= 0) {
+            const float4 *n = bvh.nodes + 8 * (size_t)cur;
+            float4 lox = __ldg(n), loy = __ldg(n + 1), loz = __ldg(n + 2), hix = __ldg(n + 3), hiy = __ldg(n + 4), hiz = __ldg(n + 5);
+            int4 ch = __ldg((const int4 *)(n + 6));
+            float dist[4]; int cid[4] = {ch.x, ch.y, ch.z, ch.w};
+            const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
+            const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                float t0x = (lx[k] - o[0]) * idx, t1x = (hx[k] - o[0]) * idx;
+                float t0y = (ly[k] - o[1]) * idy, t1y = (hy[k] - o[1]) * idy;
+                float t0z = (lz[k] - o[2]) * idz, t1z = (hz[k] - o[2]) * idz;
+                float tmn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tnear));
+                float tmx = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best));
+                tmx *= 1.0000005f;   // conservative slab (rounding of the three products)
+                dist[k] = (cid[k] != 0 && tmn <= tmx) ? tmn : __int_as_float(0x7f800000);
+            }
+            // sort the 4 candidates by distance (network), nearest first
+#define GD_CSWAP(i, j) if (dist[j] < dist[i]) { float td = dist[i]; dist[i] = dist[j]; dist[j] = td; int tc = cid[i]; cid[i] = cid[j]; cid[j] = tc; }
+            GD_CSWAP(0, 1) GD_CSWAP(2, 3) GD_CSWAP(0, 2) GD_CSWAP(1, 3) GD_CSWAP(1, 2)
+#undef GD_CSWAP
+            const float INF = __int_as_float(0x7f800000);
+            if (dist[3] < INF) st.put(sp++, cid[3], dist[3]);
+            if (dist[2] < INF) st.put(sp++, cid[2], dist[2]);
+            if (dist[1] < INF) st.put(sp++, cid[1], dist[1]);
+            if (dist[0] < INF) { cur = cid[0]; continue; }
+        } else {
+            int enc = ~cur;
+            int first = enc >> 3, cnt = enc & 7;
+            for (int i = 0; i < cnt; i++) test_prim<EXACT>(bvh, first + i, o, d, tnear, best, hit);
+        }
+        // pop
+        bool found = false;
+        while (sp > 0) {
+            int2 e = st.get(--sp);
+            if (__int_as_float(e.y) <= best) { cur = e.x; found = true; break; }
+        }
+        if (!found) break;
+    }
+    return hit;
+}
+
+} // namespace gdpt

@@ -1,0 +1,132 @@
+"""Host-side mirror of the reference's operator interface for the hot path:
+
+    Image3 render(const Scene &scene)          /root/reference/src/render.h:9
+    -> Integrator::GradPath arm                 /root/reference/src/render.cpp:387-388
+
+`render(scene)` returns the Poisson-reconstructed image like the reference does;
+`gradient_path_render(scene)` additionally returns the primal / dx / dy buffers the
+reference computes and then drops (render.cpp:355-369).  All arithmetic runs in
+libgdpt.so on the GPU; an integrator other than GradPath raises like the reference's
+`assert(false)` arm (render.cpp:390-393).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from .scene import Integrator, Scene
+
+
+class RenderResult(dict):
+    """primal, dx, dy, poisson: (H, W, 3) float64 arrays; stats: dict"""
+    __getattr__ = dict.__getitem__
+
+
+def _params(scene, spp=None, precision="f64", seed=0, sample0=0, max_depth=None, rr_depth=None, data_cost=0.04,
+            rows=None, wave_samples=0):
+    p = _capi.GdptRenderParams()
+    p.spp = int(spp if spp is not None else scene.options.samples_per_pixel)
+    p.sample0 = int(sample0)
+    p.max_depth = -2 if max_depth is None else int(max_depth)
+    p.rr_depth = -2 if rr_depth is None else int(rr_depth)
+    p.seed = int(seed)
+    p.data_cost = float(data_cost)
+    p.precision = {"f64": _capi.PRECISION_F64, "f32": _capi.PRECISION_F32}[precision]
+    p.y0, p.y1 = (0, 0) if rows is None else (int(rows[0]), int(rows[1]))
+    p.wave_samples = int(wave_samples)
+    return p
+
+
+def stats(scene, device=0):
+    s = _capi.GdptStats()
+    _capi.check(_capi.lib().gdpt_get_stats(scene.context(device), C.byref(s)))
+    return {k: getattr(s, k) for k, _ in s._fields_}
+
+
+def gradient_path_render(scene, device=0, outputs=("primal", "dx", "dy", "poisson"), **kw):
+    """gradient_path_render (render.cpp:257-370) on the GPU; returns all four buffers."""
+    ctx = scene.context(device)
+    p = _params(scene, **kw)
+    imgs = _capi.GdptImages()
+    res = RenderResult()
+    for name in outputs:
+        a = np.zeros((scene.height, scene.width, 3), dtype=np.float64)
+        res[name] = a
+        setattr(imgs, name, _capi.as_dp(a))
+    _capi.check(_capi.lib().gdpt_render(ctx, C.byref(p), C.byref(imgs)))
+    res["stats"] = stats(scene, device)
+    return res
+
+
+def render(scene, device=0, **kw):
+    """Image3 render(const Scene&): dispatch on scene.options.integrator; only GradPath lives here."""
+    if scene.options.integrator != Integrator.GradPath:
+        raise AssertionError("render(): integrator %s is outside the gradpath hot path (render.cpp:390-393)" % scene.options.integrator.name)
+    return gradient_path_render(scene, device, outputs=("poisson",), **kw)["poisson"]
+
+
+def fourier_solve(u, gx, gy, data_cost=0.04, device=0):
+    """fourierSolve(width, height, imgData, imgGradX, imgGradY, dataCost, imgOut) (render.cpp:172-254)."""
+    u, gx, gy = (_capi.f64(a) for a in (u, gx, gy))
+    if u.ndim != 3 or u.shape[2] != 3 or gx.shape != u.shape or gy.shape != u.shape:
+        raise ValueError("expected three (H, W, 3) arrays")
+    h, w, _ = u.shape
+    out = np.zeros_like(u)
+    _capi.check(_capi.lib().gdpt_poisson(device, w, h, _capi.as_dp(u), _capi.as_dp(gx), _capi.as_dp(gy), data_cost, _capi.as_dp(out)))
+    return out
+
+
+# ---- validation entry points (same device functions as the renderer) ----
+def _prec(precision):
+    return {"f64": _capi.PRECISION_F64, "f32": _capi.PRECISION_F32}[precision]
+
+
+def sample_primary(scene, screen_pos, precision="f64", device=0):
+    sp = _capi.f64(screen_pos).reshape(-1, 2)
+    rays = np.zeros((sp.shape[0], 6))
+    _capi.check(_capi.lib().gdpt_sample_primary(scene.context(device), _prec(precision), sp.shape[0], _capi.as_dp(sp), _capi.as_dp(rays)))
+    return rays
+
+
+def intersect(scene, rays, rdiff=None, precision="f64", device=0):
+    rays = _capi.f64(rays).reshape(-1, 8)
+    n = rays.shape[0]
+    ids = np.zeros((n, 3), dtype=np.int32)
+    vtx = np.zeros((n, 24))
+    rd = _capi.f64(rdiff).reshape(-1, 2) if rdiff is not None else None
+    _capi.check(_capi.lib().gdpt_intersect(scene.context(device), _prec(precision), n, _capi.as_dp(rays), _capi.as_dp(rd),
+                                           ids.ctypes.data_as(_capi.ip), _capi.as_dp(vtx)))
+    return ids, vtx
+
+
+def bsdf(scene, mat_id, vtx, dirs, rnd, precision="f64", device=0):
+    vtx, dirs, rnd = _capi.f64(vtx).reshape(-1, 15), _capi.f64(dirs).reshape(-1, 6), _capi.f64(rnd).reshape(-1, 3)
+    out = np.zeros((vtx.shape[0], 10))
+    _capi.check(_capi.lib().gdpt_bsdf(scene.context(device), _prec(precision), mat_id, vtx.shape[0], _capi.as_dp(vtx), _capi.as_dp(dirs),
+                                      _capi.as_dp(rnd), _capi.as_dp(out)))
+    return out
+
+
+def grad_samples(scene, xs, ys, streams, device=0, **kw):
+    """grad_path_tracing for explicit (x, y, rng stream) triples -> (n, 23) records."""
+    xs = np.ascontiguousarray(xs, dtype=np.int32)
+    ys = np.ascontiguousarray(ys, dtype=np.int32)
+    st = np.ascontiguousarray(streams, dtype=np.uint64)
+    rec = np.zeros((xs.size, 23))
+    p = _params(scene, **kw)
+    _capi.check(_capi.lib().gdpt_grad_samples(scene.context(device), C.byref(p), xs.size, xs.ctypes.data_as(_capi.ip),
+                                              ys.ctypes.data_as(_capi.ip), st.ctypes.data_as(C.POINTER(C.c_uint64)), _capi.as_dp(rec)))
+    return rec
+
+
+def pcg_fill(stream, n, seed=_capi.DEFAULT_SEED, device=0):
+    out = np.zeros(n)
+    raw = np.zeros(n, dtype=np.uint32)
+    _capi.check(_capi.lib().gdpt_pcg_fill(device, stream, seed, n, _capi.as_dp(out), raw.ctypes.data_as(C.POINTER(C.c_uint32))))
+    return out, raw
+
+
+def scene_bounds(scene, device=0):
+    b = np.zeros(4)
+    _capi.check(_capi.lib().gdpt_scene_bounds(scene.context(device), _capi.as_dp(b)))
+    return b

@@ -1,0 +1,142 @@
+/* gdpt.h — C ABI of the B200 gradient-domain path tracer (libgdpt.so).
+ *
+ * Drop-in boundary for the `gradpath` arm of lajolla's
+ *     Image3 render(const Scene &scene)            /root/reference/src/render.h:9
+ *                                                  /root/reference/src/render.cpp:387-388
+ * i.e. for gradient_path_render (render.cpp:257-370), grad_path_tracing
+ * (path_tracing.h:354-1050), the Embree scene build + rtcIntersect1 it sits on
+ * (scene.cpp:19-34, intersection.cpp:7-65) and fourierSolve (render.cpp:172-254).
+ * The reference-side binding is shown in INTEGRATION.md.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a
+ * negative error code (message via gdpt_last_error()); nothing throws across the ABI; the
+ * caller owns every host buffer; a context owns all device memory it allocates.  Images
+ * are interleaved-RGB doubles, row-major, y down, W*H*3 — exactly the layout of the
+ * c / cx / cy / out arrays at render.cpp:336-353.  There is no CPU fallback: every entry
+ * point that computes fails with GDPT_ERR_CUDA when no CUDA device is usable.
+ */
+#ifndef GDPT_H
+#define GDPT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GDPT_OK 0
+#define GDPT_ERR_ARG (-1)
+#define GDPT_ERR_CUDA (-2)
+#define GDPT_ERR_UNSUPPORTED (-3)
+
+#define GDPT_PRECISION_F64 0 /* arithmetic in double like the reference (Real = double, lajolla.h:23) */
+#define GDPT_PRECISION_F32 1 /* float shading/traversal, double accumulation and Poisson */
+
+typedef struct gdpt_ctx gdpt_ctx;
+
+/* One image of a TexturePool mip chain, level 0 only (src/texture.h:13-19, src/mipmap.h:28-44;
+ * the mip levels are rebuilt by gdpt_create).  Either `data` (w*h*channels doubles) or
+ * `palette` + `index` (w*h*channels bytes indexing palette) is set. */
+typedef struct {
+    int32_t width, height, channels;
+    const double *data;
+    const double *palette; int32_t palette_size;
+    const uint8_t *index;
+} gdpt_image;
+
+/* POD mirror of the fields of lajolla's Scene that gradpath reads (src/scene.h:43-83). */
+typedef struct {
+    /* Camera (src/camera.h:10-24): row-major 4x4 */
+    double sample_to_cam[16], cam_to_world[16];
+    int32_t width, height;
+    int32_t filter_kind;      /* 0 Box, 1 Tent, 2 Gaussian (src/filter.h:31-43) */
+    double filter_param;      /* Box/Tent width, Gaussian stddev */
+    /* Shapes (src/shape.h:26-53); shape id == index == Embree geomID */
+    int32_t n_shapes;
+    const int32_t *shapes;        /* [n][6]: kind(0 sphere,1 mesh), material_id, area_light_id, n_verts, n_tris, flags(1 normals|2 uvs) */
+    const int64_t *shape_offsets; /* [n][4]: first vertex, first triangle, first normal, first uv of the mesh in the pools below */
+    const double *spheres;        /* [n][4]: centre xyz, radius (zeros for meshes) */
+    int64_t n_positions, n_triangles, n_normals, n_uvs;
+    const double *positions;      /* [n_positions][3] */
+    const int32_t *indices;       /* [n_triangles][3], mesh-local vertex indices */
+    const double *normals;        /* [n_normals][3] */
+    const double *uvs;            /* [n_uvs][2] */
+    /* Materials (src/material.h:12-110) */
+    int32_t n_materials;
+    const double *materials;      /* [n][14]: type(0..8 in variant order), eta, 12 texture ids (-1 unused) */
+    int32_t n_textures;
+    const double *textures;       /* [n][14]: kind(0 const,1 image,2 checker), is_spectrum, v0[3], v1[3], image id, uscale, vscale, uoffset, voffset, pad */
+    int32_t n_images3, n_images1;
+    const gdpt_image *images3, *images1;
+    /* Lights (src/light.h:15-34) */
+    int32_t n_lights;
+    const double *lights;         /* [n][5]: kind(0 area, 1 envmap — ignored by gradpath), shape_id, intensity rgb */
+    /* RenderOptions (src/scene.h:25-32) */
+    int32_t max_depth, rr_depth, samples_per_pixel;
+} gdpt_scene_desc;
+
+typedef struct {
+    int32_t spp;              /* samples per pixel (the estimator divides by this, render.cpp:313-317) */
+    int32_t sample0;          /* index of the first sample: RNG stream = (sample0+s)*W*H + y*W + x */
+    int32_t max_depth;        /* -2: keep the scene's value */
+    int32_t rr_depth;         /* -2: keep the scene's value */
+    uint64_t seed;            /* 0: the PCG default 0x31e241f862a1fb5e (src/pcg.h:33) */
+    double data_cost;         /* Poisson alpha; <=0: 0.04 (render.cpp:353) */
+    int32_t precision;        /* GDPT_PRECISION_* */
+    int32_t y0, y1;           /* row band [y0,y1) to render; y1 <= 0: whole image */
+    int32_t wave_samples;     /* samples per pixel per wave; 0: auto */
+} gdpt_render_params;
+
+/* Host output images; any pointer may be NULL.  primal/dx/dy/poisson = c/cx/cy/out of render.cpp:336-353. */
+typedef struct { double *primal, *dx, *dy, *poisson; } gdpt_images;
+
+typedef struct {
+    double ms_total, ms_trace, ms_shade, ms_poisson, ms_copy;
+    int64_t kernel_launches, rays_traced, paths, bounce_iterations;
+} gdpt_stats;
+
+const char *gdpt_last_error(void);
+int gdpt_device_count(void);
+
+/* Upload the scene to `device`, rebuild mip chains, build the BVH (replaces Scene::Scene's
+ * Embree registration/commit, scene.cpp:19-34). */
+int gdpt_create(const gdpt_scene_desc *scene, int device, gdpt_ctx **out);
+void gdpt_destroy(gdpt_ctx *ctx);
+/* scene bounds radius / centre as scene.cpp:30-34 derives them (for parity checks) */
+int gdpt_scene_bounds(gdpt_ctx *ctx, double *radius_center4);
+
+/* render(): gradient_path_render end to end with HOST outputs (accumulate, merge, Poisson, copy back). */
+int gdpt_render(gdpt_ctx *ctx, const gdpt_render_params *params, gdpt_images *out);
+/* Same accumulation into caller-provided DEVICE images (W*H*3 doubles each, already zeroed or
+ * holding earlier passes): the five buffers of render.cpp:264-268.  No merge, no solve, no copy. */
+int gdpt_render_accumulate_device(gdpt_ctx *ctx, const gdpt_render_params *params,
+                                  double *d_img, double *d_cx0, double *d_cy0, double *d_cx1, double *d_cy1);
+/* render.cpp:340-350 on device buffers */
+int gdpt_merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const double *d_cx1, const double *d_cy0,
+                      const double *d_cy1, double *d_cx, double *d_cy);
+/* fourierSolve (render.cpp:172-254): host buffers / device buffers.  `device` selects the GPU for the host form. */
+int gdpt_poisson(int device, int w, int h, const double *u, const double *gx, const double *gy, double alpha, double *out);
+int gdpt_poisson_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
+int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out);
+int gdpt_synchronize(gdpt_ctx *ctx);
+
+/* ---- parity / validation entry points (same device code as the renderer) ---- */
+/* sample_primary (camera.cpp:23-47): screen_pos[n][2] -> rays[n][6] (origin, direction) */
+int gdpt_sample_primary(gdpt_ctx *ctx, int precision, int n, const double *screen_pos, double *rays);
+/* intersect (intersection.cpp:7-65): rays[n][8] = org, dir, tnear, tfar; rdiff[n][2] or NULL;
+ * ids[n][3] = shape, primitive, material (-1 miss); vtx[n][24] = position3, geometric_normal3, frame x3 y3 n3,
+ * st2, uv2, uv_screen_size, mean_curvature, ray_radius, t, pad */
+int gdpt_intersect(gdpt_ctx *ctx, int precision, int n, const double *rays, const double *rdiff, int32_t *ids, double *vtx);
+/* eval / pdf_sample_bsdf / sample_bsdf (material.cpp:90-119) for material `mat_id`:
+ * vtx[n][15] = geometric_normal3, frame x3 y3 n3, uv2, uv_screen_size; dirs[n][6] = dir_in, dir_out; rnd[n][3];
+ * out[n][10] = eval3, pdf, ok, sampled dir3, eta, roughness */
+int gdpt_bsdf(gdpt_ctx *ctx, int precision, int mat_id, int n, const double *vtx, const double *dirs, const double *rnd, double *out);
+/* grad_path_tracing (path_tracing.h:354-1050) for n explicit (x, y, rng stream) triples;
+ * rec[n][23] = radiance3, contrib3, contribX0 3, contribX1 3, contribY0 3, contribY1 3, prob, wX0, wY0, wX1, wY1 */
+int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, const int32_t *xs, const int32_t *ys,
+                      const uint64_t *streams, double *rec);
+/* PCG32 (pcg.h): first n doubles (and raw 32-bit outputs, may be NULL) of a stream, generated on the device */
+int gdpt_pcg_fill(int device, uint64_t stream, uint64_t seed, int n, double *out, uint32_t *raw);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -189,3 +189,66 @@ def fourier_solve(u, gx, gy, alpha=0.04):
     out = np.zeros_like(u)
     lib().gdpt_ref_fourier_solve(w, h, _dp(u), _dp(gx), _dp(gy), alpha, _dp(out))
     return out
+
+
+# ---------------------------------------------------------------------------------------
+# Staged scenes: copies of the reference's scene ASSETS (XML/OBJ/.serialized/JPG — data,
+# not source) plus generated variant XMLs, under oracle/_ref/scenes/ (git-ignored, but it
+# travels to the GPU box with oracle/_ref/).  Only test infrastructure reads them.
+STAGE_DIR = os.path.join(_HERE, "_ref", "scenes")
+
+AREA_EMITTER_XML = """
+	<shape type="sphere">
+		<point name="center" x="1.5" y="-1.5" z="6"/>
+		<float name="radius" value="1.0"/>
+		<emitter type="area">
+			<rgb name="radiance" value="40, 40, 40"/>
+		</emitter>
+		<bsdf type="diffuse">
+			<rgb name="reflectance" value="0,0,0"/>
+		</bsdf>
+	</shape>
+"""
+
+# name -> (scene dir, source xml, substitutions)
+VARIANTS = {
+    "cbox_gdpt": ("cbox", "cbox_gdpt.xml", dict()),
+    "cbox_gdpt_64": ("cbox", "cbox_gdpt.xml", dict(width=64, height=64)),
+    "cbox_gdpt_d2": ("cbox", "cbox_gdpt.xml", dict(width=64, height=64, max_depth=2)),
+    "veach_mi_gradpath": ("veach_mi", "mi.xml", dict(integrator="gradpath", max_depth=-1, spp=64)),
+    "veach_mi_small": ("veach_mi", "mi.xml", dict(integrator="gradpath", max_depth=-1, spp=4, width=96, height=64)),
+    "disney_gradpath": ("disney_bsdf_test", "disney_bsdf.xml", dict(integrator="gradpath", spp=256, extra_xml=AREA_EMITTER_XML)),
+    "disney_small": ("disney_bsdf_test", "disney_bsdf.xml", dict(integrator="gradpath", spp=4, width=96, height=72, extra_xml=AREA_EMITTER_XML)),
+    "sponza_1080p": ("sponza", "sponza.xml", dict(integrator="gradpath", width=1920, height=1080, spp=512)),
+    "sponza_2160p": ("sponza", "sponza.xml", dict(integrator="gradpath", width=3840, height=2160, spp=1024)),
+    "sponza_native": ("sponza", "sponza.xml", dict(integrator="gradpath")),
+    "sponza_small": ("sponza", "sponza.xml", dict(integrator="gradpath", width=160, height=90, spp=4)),
+}
+
+
+def stage_scenes():
+    """Copy the scene assets next to generated variant XMLs. Needs /root/reference."""
+    import shutil
+    src_root = os.path.join(REFERENCE_DIR, "scenes")
+    if not os.path.isdir(src_root):
+        return False
+    for d in ("cbox", "veach_mi", "sponza", "matpreview", "disney_bsdf_test"):
+        dst = os.path.join(STAGE_DIR, d)
+        if not os.path.isdir(dst):
+            shutil.copytree(os.path.join(src_root, d), dst, ignore=shutil.ignore_patterns(".DS_Store"))
+    for name, (d, xml, subs) in VARIANTS.items():
+        make_variant(os.path.join(STAGE_DIR, d, xml), out_dir=os.path.join(STAGE_DIR, d), name="gdpt_" + name, **subs)
+    return True
+
+
+def scene_path(name):
+    d, _, _ = VARIANTS[name]
+    p = os.path.join(STAGE_DIR, d, "gdpt_" + name + ".xml")
+    if not os.path.exists(p):
+        if not stage_scenes():
+            raise RuntimeError("staged scene %s missing and /root/reference not available" % name)
+    return p
+
+
+def scenes_available():
+    return available() and (os.path.isdir(STAGE_DIR) or os.path.isdir(os.path.join(REFERENCE_DIR, "scenes")))
