@@ -1,18 +1,28 @@
 #!/usr/bin/env bash
-# Builds libgdpt.so (the C-ABI library) for sm_100a, in tree.
+# Builds libgdpt.so (the C-ABI library) for sm_100a, in tree.  The two arithmetic modes and
+# the validation launchers are separate translation units so they compile in parallel.
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 OUT="$HERE/../libgdpt.so"
+B="$HERE/../_build"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 --expt-relaxed-constexpr --extended-lambda -Xcompiler -fPIC -Xcompiler -O3 ${GDPT_NVCC_EXTRA:-}"
-mkdir -p "$HERE/../_build"
-pids=()
-for f in gdpt_api.cu gdpt_api_validate.cu; do
-  $NVCC $FLAGS -c "$HERE/$f" -o "$HERE/../_build/${f%.cu}.o" &
-  pids+=($!)
+mkdir -p "$B"
+SRCS="gdpt_api.cu gdpt_api_validate.cu gdpt_wave_f64.cu gdpt_wave_f32.cu gdpt_validate_f64.cu gdpt_validate_f32.cu gdpt_poisson.cu"
+pids=(); OBJS=()
+newest_hdr=$(ls -t "$HERE"/*.cuh "$HERE"/*.h "$HERE/../../include/gdpt.h" | head -1)
+for f in $SRCS; do
+  o="$B/${f%.cu}.o"; OBJS+=("$o")
+  if [ ! -f "$o" ] || [ "$HERE/$f" -nt "$o" ] || [ "$newest_hdr" -nt "$o" ] || [ -n "${GDPT_FORCE:-}" ]; then
+    $NVCC $FLAGS -c "$HERE/$f" -o "$o" &
+    pids+=($!)
+  fi
 done
-g++ -O3 -std=c++17 -fPIC -c "$HERE/gdpt_bvh.cpp" -o "$HERE/../_build/gdpt_bvh.o" &
-pids+=($!)
-for p in "${pids[@]}"; do wait "$p"; done
-$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT" "$HERE/../_build/gdpt_api.o" "$HERE/../_build/gdpt_api_validate.o" "$HERE/../_build/gdpt_bvh.o" -lcudart
+o="$B/gdpt_bvh.o"; OBJS+=("$o")
+if [ ! -f "$o" ] || [ "$HERE/gdpt_bvh.cpp" -nt "$o" ] || [ "$HERE/gdpt_bvh.h" -nt "$o" ]; then
+  g++ -O3 -std=c++17 -fPIC -c "$HERE/gdpt_bvh.cpp" -o "$o" &
+  pids+=($!)
+fi
+for p in "${pids[@]:-}"; do [ -n "$p" ] && wait "$p"; done
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT" "${OBJS[@]}" -lcudart
 echo "built $OUT"

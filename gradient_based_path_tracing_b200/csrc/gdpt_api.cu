@@ -1,72 +1,32 @@
-// C ABI of libgdpt.so (include/gdpt.h): context management, the wavefront render loop,
-// the Poisson solve and the validation entry points.  Host code only orchestrates: every
-// arithmetic step of the path runs in the CUDA kernels of this directory.
+// C ABI of libgdpt.so (include/gdpt.h).  Host glue only: every arithmetic step of the path
+// runs in the CUDA kernels of this directory (wavefront: gdpt_wave_f64.cu / _f32.cu, Poisson:
+// gdpt_poisson.cu, validation launchers: gdpt_validate_*.cu).
 #include "gdpt_context.cuh"
-#include "gdpt_debug.cuh"
+#include "gdpt_wavefront.cuh"
+
+namespace gdpt {
+// other translation units
+template <typename R> int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp);
+extern template int run_wave<double>(gdpt_ctx *, DScene<double>, WaveParams);
+extern template int run_wave<float>(gdpt_ctx *, DScene<float>, WaveParams);
+int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
+int merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const double *d_cx1, const double *d_cy0, const double *d_cy1, double *d_cx, double *d_cy);
+template <typename R> int dbg_sample_primary(gdpt_ctx *ctx, const DScene<R> &sc, int n, const double *screen_pos, double *rays);
+template <typename R> int dbg_intersect(gdpt_ctx *ctx, const DScene<R> &sc, int n, const double *rays, const double *rdiff, int32_t *ids, double *vtx);
+template <typename R> int dbg_bsdf(gdpt_ctx *ctx, const DScene<R> &sc, int mat_id, int n, const double *vtx, const double *dirs, const double *rnd, double *out);
+extern template int dbg_sample_primary<double>(gdpt_ctx *, const DScene<double> &, int, const double *, double *);
+extern template int dbg_sample_primary<float>(gdpt_ctx *, const DScene<float> &, int, const double *, double *);
+extern template int dbg_intersect<double>(gdpt_ctx *, const DScene<double> &, int, const double *, const double *, int32_t *, double *);
+extern template int dbg_intersect<float>(gdpt_ctx *, const DScene<float> &, int, const double *, const double *, int32_t *, double *);
+extern template int dbg_bsdf<double>(gdpt_ctx *, const DScene<double> &, int, int, const double *, const double *, const double *, double *);
+extern template int dbg_bsdf<float>(gdpt_ctx *, const DScene<float> &, int, int, const double *, const double *, const double *, double *);
+int fill_default_records(gdpt_ctx *ctx, int n, double *d_rec);
+int pcg_fill_device(unsigned long long stream, unsigned long long seed, int n, double *d_out, unsigned int *d_raw);
+} // namespace gdpt
 
 using namespace gdpt;
 
 namespace {
-
-inline int blocks_for(long long n, int block) { return (int)((n + block - 1) / block); }
-constexpr int SM_COUNT = 148;
-
-template <typename R> struct ModeSel;
-template <> struct ModeSel<double> { static DScene<double> &scene(gdpt_ctx *c) { return c->sc_d; } static constexpr bool exact = true; };
-template <> struct ModeSel<float> { static DScene<float> &scene(gdpt_ctx *c) { return c->sc_f; } static constexpr bool exact = false; };
-
-template <bool EXACT>
-void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n) {
-    if (n <= 0) return;
-    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
-    k_trace<EXACT><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n);
-    c->stats.kernel_launches++; c->stats.rays_traced += n;
-}
-
-// One wave of pixel-samples through generate -> trace -> primary -> (trace -> bounce)*.
-template <typename R>
-int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
-    const int N = wp.n_paths;
-    if (N <= 0) return 0;
-    if (int r = c->gen.ensure((size_t)N * sizeof(GenRec<R>))) return r;
-    if (int r = c->rays.ensure((size_t)N * 5 * sizeof(RayF))) return r;
-    if (int r = c->hits.ensure((size_t)N * 5 * sizeof(Hit))) return r;
-    if (int r = c->rec_a.ensure((size_t)N * sizeof(PathRec<R>))) return r;
-    if (int r = c->rec_b.ensure((size_t)N * sizeof(PathRec<R>))) return r;
-    if (int r = c->off.ensure((size_t)N * sizeof(OffRec<R>))) return r;
-    if (int r = c->counters.ensure(64)) return r;
-    int *cnt = c->counters.as<int>();
-    GenRec<R> *gen = c->gen.as<GenRec<R>>();
-    RayF *rays = c->rays.as<RayF>(); Hit *hits = c->hits.as<Hit>();
-    PathRec<R> *cur = c->rec_a.as<PathRec<R>>(), *nxt = c->rec_b.as<PathRec<R>>();
-    OffRec<R> *off = c->off.as<OffRec<R>>();
-    cudaStream_t st = c->stream;
-
-    GD_CUDA(cudaMemsetAsync(cnt, 0, 64, st));
-    k_generate<R><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, rays);
-    c->stats.kernel_launches++;
-    launch_trace<ModeSel<R>::exact>(c, rays, hits, 5 * N);
-    k_primary<R><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, hits, cur, off, rays, cnt);
-    c->stats.kernel_launches++;
-    GD_CUDA(cudaMemcpyAsync(c->h_counts, cnt, sizeof(int), cudaMemcpyDeviceToHost, st));
-    GD_CUDA(cudaStreamSynchronize(st));
-    int count = c->h_counts[0];
-    c->stats.paths += N;
-    int which = 0; bool first = true;
-    while (count > 0) {
-        launch_trace<ModeSel<R>::exact>(c, rays, hits, count);
-        int *cin = cnt + which, *cout = cnt + (which ^ 1);
-        GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
-        k_bounce<R><<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout);
-        c->stats.kernel_launches++; c->stats.bounce_iterations++;
-        GD_CUDA(cudaMemcpyAsync(c->h_counts, cout, sizeof(int), cudaMemcpyDeviceToHost, st));
-        GD_CUDA(cudaStreamSynchronize(st));
-        count = c->h_counts[0];
-        std::swap(cur, nxt); which ^= 1; first = false;
-    }
-    GD_CUDA(cudaGetLastError());
-    return 0;
-}
 
 struct Resolved { int spp, sample0, y0, y1, precision, wave; unsigned long long seed; double alpha; int max_depth, rr_depth; };
 
@@ -86,9 +46,13 @@ int resolve(gdpt_ctx *c, const gdpt_render_params *p, Resolved &r) {
     return 0;
 }
 
+template <typename R> DScene<R> &scene_of(gdpt_ctx *c);
+template <> DScene<double> &scene_of<double>(gdpt_ctx *c) { return c->sc_d; }
+template <> DScene<float> &scene_of<float>(gdpt_ctx *c) { return c->sc_f; }
+
 template <typename R>
 int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, double *d_cy0, double *d_cx1, double *d_cy1) {
-    DScene<R> sc = ModeSel<R>::scene(c);
+    DScene<R> sc = scene_of<R>(c);
     sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth;
     WaveParams wp; memset(&wp, 0, sizeof(wp));
     wp.width = c->width; wp.height = c->height; wp.y0 = r.y0; wp.y1 = r.y1;
@@ -114,53 +78,6 @@ int ensure_images(gdpt_ctx *c) {
     size_t n = (size_t)c->width * c->height * 3 * sizeof(double);
     gdpt::DevBuf *bufs[] = {&c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
     for (auto *b : bufs) if (int r = b->ensure(n)) return r;
-    return 0;
-}
-
-int ensure_poisson(gdpt_ctx *c, int w, int h) {
-    PoissonCache &pc = c->pc;
-    size_t plane = (size_t)w * h * 3 * sizeof(double);
-    if (int r = pc.work.ensure(plane)) return r;
-    if (int r = pc.work2.ensure(plane)) return r;
-    if (int r = pc.partial.ensure((size_t)SM_COUNT * 8 * 3 * sizeof(double))) return r;
-    if (int r = pc.dc.ensure(64)) return r;
-    if (pc.w != w || pc.h != h) {
-        if (int r = pc.Dw.ensure((size_t)w * w * sizeof(double))) return r;
-        if (int r = pc.DhT.ensure((size_t)h * h * sizeof(double))) return r;
-        k_dct_matrix<<<SM_COUNT * 4, 256, 0, c->stream>>>(w, 0, pc.Dw.as<double>());
-        k_dct_matrix<<<SM_COUNT * 4, 256, 0, c->stream>>>(h, 1, pc.DhT.as<double>());
-        c->stats.kernel_launches += 2;
-        pc.w = w; pc.h = h;
-    }
-    return 0;
-}
-
-int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out) {
-    if (w < 2 || h < 2) return fail(GDPT_ERR_ARG, "Poisson solve needs at least a 2x2 image");
-    if (int r = ensure_poisson(c, w, h)) return r;
-    PoissonCache &pc = c->pc;
-    cudaStream_t st = c->stream;
-    double *A = pc.work.as<double>(), *B = pc.work2.as<double>();
-    const int nb = SM_COUNT * 8;
-    k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, h, d_u, d_gx, d_gy, alpha, A, pc.partial.as<double>());
-    k_dc_reduce<<<1, 32, 0, st>>>(nb, pc.partial.as<double>(), pc.dc.as<double>());
-    Epilogue ep; memset(&ep, 0, sizeof(ep));
-    ep.img_w = w; ep.img_h = h; ep.alpha = alpha; ep.dc = pc.dc.as<double>(); ep.out = d_out;
-    ep.scale = 4.0 * (w - 1) * (h - 1);
-    long long plane = (long long)w * h;
-    dim3 g_rows(blocks_for(w, GT), blocks_for(3 * h, GT), 1), g_cols(blocks_for(w, GT), blocks_for(h, GT), 3);
-    // forward: rows then columns (+ spectral divide, DC)
-    ep.mode = EPI_STORE;
-    k_dgemm<<<g_rows, 256, 0, st>>>(3 * h, w, w, A, w, 0, pc.Dw.as<double>(), w, 0, B, w, 0, ep);
-    ep.mode = EPI_DIVIDE;
-    k_dgemm<<<g_cols, 256, 0, st>>>(h, w, h, pc.DhT.as<double>(), h, 0, B, w, plane, A, w, plane, ep);
-    // inverse (DCT-I is its own inverse up to the scale): columns then rows (+ scale, re-interleave)
-    ep.mode = EPI_STORE;
-    k_dgemm<<<g_cols, 256, 0, st>>>(h, w, h, pc.DhT.as<double>(), h, 0, A, w, plane, B, w, plane, ep);
-    ep.mode = EPI_SCALE_INTERLEAVE;
-    k_dgemm<<<g_rows, 256, 0, st>>>(3 * h, w, w, B, w, 0, pc.Dw.as<double>(), w, 0, A, w, 0, ep);
-    c->stats.kernel_launches += 6;
-    GD_CUDA(cudaGetLastError());
     return 0;
 }
 
@@ -214,10 +131,7 @@ int gdpt_merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const do
                       double *d_cx, double *d_cy) {
     if (!ctx) return fail(GDPT_ERR_ARG, "null argument");
     GD_CUDA(cudaSetDevice(ctx->device));
-    k_merge<<<SM_COUNT * 8, 256, 0, ctx->stream>>>(w, h, d_cx0, d_cx1, d_cy0, d_cy1, d_cx, d_cy);
-    ctx->stats.kernel_launches++;
-    GD_CUDA(cudaGetLastError());
-    return 0;
+    return merge_device(ctx, w, h, d_cx0, d_cx1, d_cy0, d_cy1, d_cx, d_cy);
 }
 
 int gdpt_poisson_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out) {
@@ -234,6 +148,7 @@ int gdpt_render(gdpt_ctx *ctx, const gdpt_render_params *params, gdpt_images *ou
     const int w = ctx->width, h = ctx->height;
     size_t bytes = (size_t)w * h * 3 * sizeof(double);
     cudaStream_t st = ctx->stream;
+    ctx->stats.ms_trace = ctx->stats.ms_shade = 0;
     GD_CUDA(cudaEventRecord(ctx->ev[0], st));
     gdpt::DevBuf *acc[] = {&ctx->img, &ctx->cx0, &ctx->cy0, &ctx->cx1, &ctx->cy1};
     for (auto *b : acc) GD_CUDA(cudaMemsetAsync(b->p, 0, bytes, st));
@@ -242,9 +157,8 @@ int gdpt_render(gdpt_ctx *ctx, const gdpt_render_params *params, gdpt_images *ou
                  : accumulate<float>(ctx, r, ctx->img.as<double>(), ctx->cx0.as<double>(), ctx->cy0.as<double>(), ctx->cx1.as<double>(), ctx->cy1.as<double>());
     if (rc) return rc;
     GD_CUDA(cudaEventRecord(ctx->ev[1], st));
-    k_merge<<<SM_COUNT * 8, 256, 0, st>>>(w, h, ctx->cx0.as<double>(), ctx->cx1.as<double>(), ctx->cy0.as<double>(), ctx->cy1.as<double>(),
-                                         ctx->cx.as<double>(), ctx->cy.as<double>());
-    ctx->stats.kernel_launches++;
+    if (int rc2 = merge_device(ctx, w, h, ctx->cx0.as<double>(), ctx->cx1.as<double>(), ctx->cy0.as<double>(), ctx->cy1.as<double>(),
+                               ctx->cx.as<double>(), ctx->cy.as<double>())) return rc2;
     if (int rc2 = poisson_device(ctx, w, h, ctx->img.as<double>(), ctx->cx.as<double>(), ctx->cy.as<double>(), r.alpha, ctx->out.as<double>())) return rc2;
     GD_CUDA(cudaEventRecord(ctx->ev[2], st));
     if (out) {
@@ -257,7 +171,6 @@ int gdpt_render(gdpt_ctx *ctx, const gdpt_render_params *params, gdpt_images *ou
     GD_CUDA(cudaStreamSynchronize(st));
     float ms = 0;
     cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]); ctx->stats.ms_total = ms;
-    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]); ctx->stats.ms_trace = ms;   // accumulate phase (trace + shade)
     cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ctx->stats.ms_poisson = ms;
     cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]); ctx->stats.ms_copy = ms;
     return 0;
@@ -278,8 +191,7 @@ int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, co
     GD_CUDA(cudaMemcpy(ctx->xs.p, xs, (size_t)n * 4, cudaMemcpyHostToDevice));
     GD_CUDA(cudaMemcpy(ctx->ys.p, ys, (size_t)n * 4, cudaMemcpyHostToDevice));
     GD_CUDA(cudaMemcpy(ctx->streams.p, streams, (size_t)n * 8, cudaMemcpyHostToDevice));
-    k_fill_default_records<<<blocks_for(n, 128), 128, 0, ctx->stream>>>(n, ctx->recout.as<double>());
-    ctx->stats.kernel_launches++;
+    if (int rc = fill_default_records(ctx, n, ctx->recout.as<double>())) return rc;
     WaveParams wp; memset(&wp, 0, sizeof(wp));
     wp.width = ctx->width; wp.height = ctx->height; wp.y0 = 0; wp.y1 = ctx->height; wp.tiles_x = (ctx->width + 7) / 8;
     wp.n_paths = n; wp.npix_pad = n; wp.spp_total = 1; wp.seed = r.seed;

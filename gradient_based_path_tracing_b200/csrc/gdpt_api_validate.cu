@@ -1,14 +1,23 @@
 // C ABI, second half: the stand-alone Poisson entry point with host buffers and the
-// validation entry points (gdpt_sample_primary / gdpt_intersect / gdpt_bsdf /
-// gdpt_grad_samples / gdpt_pcg_fill).  They run the renderer's own device functions.
+// validation entry points (gdpt_sample_primary / gdpt_intersect / gdpt_bsdf / gdpt_pcg_fill).
+// Host glue only; kernels live in gdpt_validate_*.cu / gdpt_poisson.cu.
 #include "gdpt_context.cuh"
-#include "gdpt_debug.cuh"
 
+namespace gdpt {
+template <typename R> int dbg_sample_primary(gdpt_ctx *ctx, const DScene<R> &sc, int n, const double *screen_pos, double *rays);
+template <typename R> int dbg_intersect(gdpt_ctx *ctx, const DScene<R> &sc, int n, const double *rays, const double *rdiff, int32_t *ids, double *vtx);
+template <typename R> int dbg_bsdf(gdpt_ctx *ctx, const DScene<R> &sc, int mat_id, int n, const double *vtx, const double *dirs, const double *rnd, double *out);
+extern template int dbg_sample_primary<double>(gdpt_ctx *, const DScene<double> &, int, const double *, double *);
+extern template int dbg_sample_primary<float>(gdpt_ctx *, const DScene<float> &, int, const double *, double *);
+extern template int dbg_intersect<double>(gdpt_ctx *, const DScene<double> &, int, const double *, const double *, int32_t *, double *);
+extern template int dbg_intersect<float>(gdpt_ctx *, const DScene<float> &, int, const double *, const double *, int32_t *, double *);
+extern template int dbg_bsdf<double>(gdpt_ctx *, const DScene<double> &, int, int, const double *, const double *, const double *, double *);
+extern template int dbg_bsdf<float>(gdpt_ctx *, const DScene<float> &, int, int, const double *, const double *, const double *, double *);
+int pcg_fill_device(unsigned long long stream, unsigned long long seed, int n, double *d_out, unsigned int *d_raw);
+}
 using namespace gdpt;
 
 namespace {
-inline int blocks_for(long long n, int block) { return (int)((n + block - 1) / block); }
-
 struct Scratch {   // device scratch that frees itself
     std::vector<void *> ptrs;
     ~Scratch() { for (void *p : ptrs) cudaFree(p); }
@@ -63,33 +72,16 @@ int gdpt_sample_primary(gdpt_ctx *ctx, int precision, int n, const double *scree
     if (!ctx || !screen_pos || !rays || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
     if (n == 0) return 0;
     GD_CUDA(cudaSetDevice(ctx->device));
-    Scratch s; double *dsp, *dr;
-    if (int r = s.put(&dsp, screen_pos, (size_t)n * 2)) return r;
-    if (int r = s.alloc(&dr, (size_t)n * 6)) return r;
-    if (precision == GDPT_PRECISION_F64) k_dbg_sample_primary<double><<<blocks_for(n, 128), 128, 0, ctx->stream>>>(ctx->sc_d, n, dsp, dr);
-    else k_dbg_sample_primary<float><<<blocks_for(n, 128), 128, 0, ctx->stream>>>(ctx->sc_f, n, dsp, dr);
-    ctx->stats.kernel_launches++;
-    GD_CUDA(cudaStreamSynchronize(ctx->stream));
-    GD_CUDA(cudaMemcpy(rays, dr, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost));
-    return 0;
+    return precision == GDPT_PRECISION_F64 ? dbg_sample_primary<double>(ctx, ctx->sc_d, n, screen_pos, rays)
+                                           : dbg_sample_primary<float>(ctx, ctx->sc_f, n, screen_pos, rays);
 }
 
 int gdpt_intersect(gdpt_ctx *ctx, int precision, int n, const double *rays, const double *rdiff, int32_t *ids, double *vtx) {
     if (!ctx || !rays || !ids || !vtx || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
     if (n == 0) return 0;
     GD_CUDA(cudaSetDevice(ctx->device));
-    Scratch s; double *dr, *drd = nullptr, *dv; int *di;
-    if (int r = s.put(&dr, rays, (size_t)n * 8)) return r;
-    if (rdiff) if (int r = s.put(&drd, rdiff, (size_t)n * 2)) return r;
-    if (int r = s.alloc(&di, (size_t)n * 3)) return r;
-    if (int r = s.alloc(&dv, (size_t)n * 24)) return r;
-    if (precision == GDPT_PRECISION_F64) k_dbg_intersect<double, true><<<blocks_for(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->sc_d, ctx->bvh, n, dr, drd, di, dv);
-    else k_dbg_intersect<float, false><<<blocks_for(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->sc_f, ctx->bvh, n, dr, drd, di, dv);
-    ctx->stats.kernel_launches++;
-    GD_CUDA(cudaStreamSynchronize(ctx->stream));
-    GD_CUDA(cudaMemcpy(ids, di, (size_t)n * 3 * sizeof(int), cudaMemcpyDeviceToHost));
-    GD_CUDA(cudaMemcpy(vtx, dv, (size_t)n * 24 * sizeof(double), cudaMemcpyDeviceToHost));
-    return 0;
+    return precision == GDPT_PRECISION_F64 ? dbg_intersect<double>(ctx, ctx->sc_d, n, rays, rdiff, ids, vtx)
+                                           : dbg_intersect<float>(ctx, ctx->sc_f, n, rays, rdiff, ids, vtx);
 }
 
 int gdpt_bsdf(gdpt_ctx *ctx, int precision, int mat_id, int n, const double *vtx, const double *dirs, const double *rnd, double *out) {
@@ -97,17 +89,8 @@ int gdpt_bsdf(gdpt_ctx *ctx, int precision, int mat_id, int n, const double *vtx
     if (mat_id < 0 || mat_id >= ctx->sc_d.n_materials) return fail(GDPT_ERR_ARG, "material id out of range");
     if (n == 0) return 0;
     GD_CUDA(cudaSetDevice(ctx->device));
-    Scratch s; double *dv, *dd, *drn, *dout;
-    if (int r = s.put(&dv, vtx, (size_t)n * 15)) return r;
-    if (int r = s.put(&dd, dirs, (size_t)n * 6)) return r;
-    if (int r = s.put(&drn, rnd, (size_t)n * 3)) return r;
-    if (int r = s.alloc(&dout, (size_t)n * 10)) return r;
-    if (precision == GDPT_PRECISION_F64) k_dbg_bsdf<double><<<blocks_for(n, 64), 64, 0, ctx->stream>>>(ctx->sc_d, mat_id, n, dv, dd, drn, dout);
-    else k_dbg_bsdf<float><<<blocks_for(n, 64), 64, 0, ctx->stream>>>(ctx->sc_f, mat_id, n, dv, dd, drn, dout);
-    ctx->stats.kernel_launches++;
-    GD_CUDA(cudaStreamSynchronize(ctx->stream));
-    GD_CUDA(cudaMemcpy(out, dout, (size_t)n * 10 * sizeof(double), cudaMemcpyDeviceToHost));
-    return 0;
+    return precision == GDPT_PRECISION_F64 ? dbg_bsdf<double>(ctx, ctx->sc_d, mat_id, n, vtx, dirs, rnd, out)
+                                           : dbg_bsdf<float>(ctx, ctx->sc_f, mat_id, n, vtx, dirs, rnd, out);
 }
 
 int gdpt_pcg_fill(int device, uint64_t stream, uint64_t seed, int n, double *out, uint32_t *raw) {
@@ -119,8 +102,7 @@ int gdpt_pcg_fill(int device, uint64_t stream, uint64_t seed, int n, double *out
     Scratch s; double *dout; unsigned int *draw = nullptr;
     if (int r = s.alloc(&dout, (size_t)n)) return r;
     if (raw) if (int r = s.alloc(&draw, (size_t)n)) return r;
-    k_dbg_pcg<<<1, 32>>>(stream, seed ? seed : 0x31e241f862a1fb5eULL, n, dout, draw);
-    GD_CUDA(cudaDeviceSynchronize());
+    if (int r = pcg_fill_device(stream, seed ? seed : 0x31e241f862a1fb5eULL, n, dout, draw)) return r;
     GD_CUDA(cudaMemcpy(out, dout, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
     if (raw) GD_CUDA(cudaMemcpy(raw, draw, (size_t)n * sizeof(unsigned int), cudaMemcpyDeviceToHost));
     return 0;

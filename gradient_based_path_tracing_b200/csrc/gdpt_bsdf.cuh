@@ -441,7 +441,7 @@ template <typename R> GD_D bool sample_disney_bsdf(const BCtx<R> &c, const DMate
 }
 
 // ------------------------------------------------------------------ dispatch
-template <typename R> GD_D V3<R> bsdf_eval(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
+template <typename R> GD_BIG V3<R> bsdf_eval(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
     const DMaterial &m = sc.materials[v.material_id];
     BCtx<R> c{sc, v, dir_in};
     switch (m.type) {
@@ -456,7 +456,7 @@ template <typename R> GD_D V3<R> bsdf_eval(const DScene<R> &sc, const Vertex<R> 
     default: return eval_disney_bsdf(c, dir_out, m);
     }
 }
-template <typename R> GD_D R bsdf_pdf(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
+template <typename R> GD_BIG R bsdf_pdf(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
     const DMaterial &m = sc.materials[v.material_id];
     BCtx<R> c{sc, v, dir_in};
     switch (m.type) {
@@ -469,7 +469,7 @@ template <typename R> GD_D R bsdf_pdf(const DScene<R> &sc, const Vertex<R> &v, c
     default: return pdf_disney_bsdf(c, dir_out, m);
     }
 }
-template <typename R> GD_D bool bsdf_sample(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, R u0, R u1, R w, BsdfSample<R> &s) {
+template <typename R> GD_BIG bool bsdf_sample(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, R u0, R u1, R w, BsdfSample<R> &s) {
     const DMaterial &m = sc.materials[v.material_id];
     BCtx<R> c{sc, v, dir_in};
     switch (m.type) {

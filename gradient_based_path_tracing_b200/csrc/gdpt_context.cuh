@@ -10,8 +10,7 @@
 
 #include "../../include/gdpt.h"
 #include "gdpt_bvh.h"
-#include "gdpt_poisson.cuh"
-#include "gdpt_shade.cuh"
+#include "gdpt_trace.cuh"
 
 namespace gdpt {
 

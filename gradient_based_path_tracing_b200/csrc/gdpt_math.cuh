@@ -13,6 +13,11 @@
 
 #define GD_HD __host__ __device__ __forceinline__
 #define GD_D __device__ __forceinline__
+// large device functions (BSDF dispatch, vertex construction): one out-of-line copy per
+// arithmetic type keeps code size, I-cache pressure and compile time down
+#ifndef GD_BIG
+#define GD_BIG __device__ __noinline__
+#endif
 
 namespace gdpt {
 

@@ -167,7 +167,7 @@ GD_D double sphere_hit_d(const double *sph, const float *o, const float *d, floa
 // org/dir: the ray in working precision (what lajolla holds in double); tnear/tfar_in: the
 // values that were handed to the traversal (needed to re-derive the double sphere root).
 template <typename R>
-GD_D void make_vertex(const DScene<R> &sc, const V3<R> &org, const V3<R> &dir, float tnear, float tfar_in,
+GD_BIG void make_vertex(const DScene<R> &sc, const V3<R> &org, const V3<R> &dir, float tnear, float tfar_in,
                       const Hit &hit, R rd_radius, R rd_spread, Vertex<R> &v) {
     const DShape sh = sc.shapes[hit.shape_id];
     v.shape_id = hit.shape_id; v.prim_id = hit.prim_id; v.material_id = sh.material_id;

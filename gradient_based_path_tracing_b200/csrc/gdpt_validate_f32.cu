@@ -1,0 +1,7 @@
+// validation launchers, R = float: explicit instantiation
+#include "gdpt_validate.cuh"
+namespace gdpt {
+template int dbg_sample_primary<float>(gdpt_ctx *, const DScene<float> &, int, const double *, double *);
+template int dbg_intersect<float>(gdpt_ctx *, const DScene<float> &, int, const double *, const double *, int32_t *, double *);
+template int dbg_bsdf<float>(gdpt_ctx *, const DScene<float> &, int, int, const double *, const double *, const double *, double *);
+}

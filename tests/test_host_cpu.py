@@ -1,0 +1,102 @@
+"""CPU suite: host logic and the C-ABI surface (no compute calls without a GPU)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+def test_library_loads_and_exports_every_declared_symbol(g):
+    hdr = open(os.path.join(ROOT, "include", "gdpt.h")).read()
+    declared = set(re.findall(r"\b(gdpt_[a-z_0-9]+)\s*\(", hdr))
+    declared -= {"gdpt_ctx"}
+    assert declared == set(g._capi.EXPORTS), declared ^ set(g._capi.EXPORTS)
+    lib = g._capi.lib()
+    for name in declared:
+        assert getattr(lib, name) is not None
+
+
+def test_abi_struct_sizes_match_header(g, tmp_path):
+    """ctypes mirrors must have the sizes a C compiler gives the header's structs."""
+    import subprocess
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include "gdpt.h"\nint main(void){printf("%zu %zu %zu %zu %zu\\n", sizeof(gdpt_render_params),'
+                   ' sizeof(gdpt_images), sizeof(gdpt_stats), sizeof(gdpt_image), sizeof(gdpt_scene_desc));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    sizes = [int(v) for v in subprocess.check_output([str(exe)]).split()]
+    c = g._capi
+    assert sizes == [ctypes.sizeof(t) for t in (c.GdptRenderParams, c.GdptImages, c.GdptStats, c.GdptImage, c.GdptSceneDesc)]
+
+
+def test_no_cpu_fallback_without_device(g):
+    lib = g._capi.lib()
+    if lib.gdpt_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    u = np.zeros((4, 4, 3))
+    with pytest.raises(g._capi.GdptError, match="no CUDA device"):
+        g.fourier_solve(u, u, u)
+    sc = g.Scene.named("cbox_gdpt_64")
+    with pytest.raises(g._capi.GdptError, match="no CUDA device"):
+        g.render(sc)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "gradient_based_path_tracing_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt and "liboracle" not in txt and "lajolla_ref" not in txt, f
+
+
+def test_container_roundtrip(tmp_path, g):
+    from gradient_based_path_tracing_b200.scene import read_container, write_container
+    arrays = {"a": np.arange(12, dtype=np.float64).reshape(3, 4), "b.c": np.array([1, 2, 3], dtype=np.int32),
+              "e": np.zeros((0, 3), dtype=np.float64), "u": np.arange(5, dtype=np.uint8)}
+    for name in ("x.gdpt", "x.gdpt.z"):
+        p = str(tmp_path / name)
+        write_container(p, arrays)
+        back = read_container(p)
+        assert set(back) == set(arrays)
+        for k in arrays:
+            assert back[k].dtype == arrays[k].dtype and np.array_equal(back[k], arrays[k])
+
+
+@pytest.mark.parametrize("name,size,spp", [("cbox_gdpt", (512, 512), 4), ("veach_mi_gradpath", (768, 512), 64),
+                                           ("disney_gradpath", (683, 512), 256), ("sponza_1080p", (1920, 1080), 512),
+                                           ("sponza_2160p", (3840, 2160), 1024)])
+def test_shipped_scene_containers_match_baseline_configs(g, name, size, spp):
+    sc = g.Scene.named(name)
+    assert (sc.width, sc.height) == size
+    assert sc.options.samples_per_pixel == spp
+    assert sc.options.integrator == g.Integrator.GradPath and int(g.Integrator.GradPath) == 7   # src/scene.h:14-23
+    d = sc.desc()
+    assert d.n_shapes == sc.a["shapes"].shape[0] and d.n_materials == sc.a["materials"].shape[0]
+    if name.startswith("sponza"):
+        assert d.n_triangles == 66445 and d.n_shapes == 38 and d.n_images3 == 10    # 37 meshes + 1 sphere light
+
+
+def test_render_rejects_other_integrators(g):
+    sc = g.Scene.named("cbox_gdpt_64")
+    sc.options.integrator = g.Integrator.Path
+    with pytest.raises(AssertionError):
+        g.render(sc)
+
+
+def test_row_band_partition(g):
+    from gradient_based_path_tracing_b200.multi import partition_rows
+    for h in (1, 3, 64, 90, 575, 1080, 2160):
+        for n in (1, 2, 3, 4, 8):
+            bands = partition_rows(h, n)
+            assert len(bands) == n
+            assert bands[0][0] == 0 and bands[-1][1] == h
+            for (a0, a1), (b0, b1) in zip(bands, bands[1:]):
+                assert a1 == b0 and a0 <= a1
+            assert all(b0 % 4 == 0 for b0, b1 in bands if b1 > b0)   # non-empty bands start on a 4-row tile boundary
+            sizes = [b1 - b0 for b0, b1 in bands if b1 > b0]
+            if h >= 4 * n:
+                assert max(sizes) - min(sizes) <= 4 + h % 4
