@@ -14,7 +14,10 @@ newest_hdr=$(ls -t "$HERE"/*.cuh "$HERE"/*.h "$HERE/../../include/gdpt.h" | head
 for f in $SRCS; do
   o="$B/${f%.cu}.o"; OBJS+=("$o")
   if [ ! -f "$o" ] || [ "$HERE/$f" -nt "$o" ] || [ "$newest_hdr" -nt "$o" ] || [ -n "${GDPT_FORCE:-}" ]; then
-    $NVCC $FLAGS -c "$HERE/$f" -o "$o" &
+    # exact mode mirrors the reference's double arithmetic (gcc, x86-64, no FMA contraction):
+    # keep multiply and add separate there so ties and branch decisions fall the same way
+    EXTRA=""; case "$f" in *_f64.cu) EXTRA="-fmad=false";; esac
+    $NVCC $FLAGS $EXTRA -c "$HERE/$f" -o "$o" &
     pids+=($!)
   fi
 done

@@ -112,6 +112,45 @@ int gdpt_synchronize(gdpt_ctx *ctx) {
     return 0;
 }
 
+int gdpt_set_stream(gdpt_ctx *ctx, void *cuda_stream) {
+    if (!ctx) return fail(GDPT_ERR_ARG, "null argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (cuda_stream) {
+        if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+        ctx->stream = (cudaStream_t)cuda_stream; ctx->own_stream = false;
+    } else if (!ctx->own_stream) {
+        GD_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->own_stream = true;
+    }
+    return 0;
+}
+
+int gdpt_traversal_counts(gdpt_ctx *ctx, const gdpt_render_params *params, double *out3) {
+    Resolved r;
+    if (int rc = resolve(ctx, params, r)) return rc;
+    if (!out3) return fail(GDPT_ERR_ARG, "null argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    if (int rc = ensure_images(ctx)) return rc;
+    if (int rc = ctx->trav_counters.ensure(64)) return rc;
+    GD_CUDA(cudaMemsetAsync(ctx->trav_counters.p, 0, 64, ctx->stream));
+    size_t bytes = (size_t)ctx->width * ctx->height * 3 * sizeof(double);
+    gdpt::DevBuf *acc[] = {&ctx->img, &ctx->cx0, &ctx->cy0, &ctx->cx1, &ctx->cy1};
+    for (auto *b : acc) GD_CUDA(cudaMemsetAsync(b->p, 0, bytes, ctx->stream));
+    long long rays0 = ctx->stats.rays_traced;
+    ctx->count_traversal = true;
+    int rc = r.precision == GDPT_PRECISION_F64
+                 ? accumulate<double>(ctx, r, ctx->img.as<double>(), ctx->cx0.as<double>(), ctx->cy0.as<double>(), ctx->cx1.as<double>(), ctx->cy1.as<double>())
+                 : accumulate<float>(ctx, r, ctx->img.as<double>(), ctx->cx0.as<double>(), ctx->cy0.as<double>(), ctx->cx1.as<double>(), ctx->cy1.as<double>());
+    ctx->count_traversal = false;
+    if (rc) return rc;
+    unsigned long long h[2];
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    GD_CUDA(cudaMemcpy(h, ctx->trav_counters.p, 16, cudaMemcpyDeviceToHost));
+    double rays = (double)(ctx->stats.rays_traced - rays0);
+    out3[0] = rays > 0 ? h[0] / rays : 0; out3[1] = rays > 0 ? h[1] / rays : 0; out3[2] = rays;
+    return 0;
+}
+
 int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out) {
     if (!ctx || !out) return fail(GDPT_ERR_ARG, "null argument");
     *out = ctx->stats; return 0;

@@ -72,6 +72,9 @@ struct gdpt_ctx {
     gdpt::PoissonCache pc;
     gdpt_stats stats;
     cudaEvent_t ev[8];
+    bool count_traversal = false;     // bench-only: count nodes/primitives per ray
+    bool own_stream = true;
+    gdpt::DevBuf trav_counters;
 };
 
 namespace gdpt {
@@ -233,12 +236,12 @@ inline void destroy_context(gdpt_ctx *c) {
     gdpt::DevBuf *all[] = {&c->shapes, &c->spheres, &c->indices, &c->materials, &c->img3, &c->img1, &c->pos_d, &c->nrm_d, &c->uv_d, &c->tex_d,
                            &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tex_f, &c->texels3_f, &c->texels1_f,
                            &c->light_f, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
-                           &c->recout, &c->xs, &c->ys, &c->streams, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
+                           &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
     for (auto *b : all) b->release();
     c->pc.release();
     if (c->h_counts) cudaFreeHost(c->h_counts);
     for (auto &e : c->ev) if (e) cudaEventDestroy(e);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->stream && c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
 

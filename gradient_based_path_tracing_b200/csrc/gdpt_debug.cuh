@@ -25,7 +25,7 @@ static __global__ void __launch_bounds__(TRACE_BLOCK) k_dbg_intersect(DScene<R> 
     V3<R> org((R)q[0], (R)q[1], (R)q[2]), dir((R)q[3], (R)q[4], (R)q[5]);
     float o[3] = {(float)q[0], (float)q[1], (float)q[2]}, d[3] = {(float)q[3], (float)q[4], (float)q[5]};
     float tnear = (float)q[6], tfar = (float)q[7];
-    Hit h = trace_closest<EXACT>(bvh, o, d, tnear, tfar, stack);
+    Hit h = trace_closest<EXACT, false>(bvh, o, d, tnear, tfar, stack);
     double *out = vtx + 24 * i;
     if (h.shape_id < 0) { ids[3 * i] = ids[3 * i + 1] = ids[3 * i + 2] = -1; for (int k = 0; k < 24; k++) out[k] = 0; return; }
     Vertex<R> v;

@@ -86,8 +86,9 @@ GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3],
 }
 
 // smem_stack: TRACE_BLOCK * STACK_SMEM int2 of shared memory owned by the block
-template <bool EXACT>
-GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], float tnear, float tfar, int2 *smem_stack) {
+template <bool EXACT, bool COUNT = false>
+GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], float tnear, float tfar, int2 *smem_stack,
+                       unsigned *n_nodes = nullptr, unsigned *n_prims = nullptr) {
     Hit hit; hit.t = tfar; hit.u = hit.v = 0.f; hit.shape_id = -1; hit.prim_id = -1;
     if (bvh.n_nodes == 0) return hit;
     TraceStack st; st.smem = smem_stack;
@@ -97,6 +98,7 @@ GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], floa
     int cur = 0;   // root node
     while (true) {
         if (cur >= 0) {
+            if (COUNT) (*n_nodes)++;
             const float4 *n = bvh.nodes + 8 * (size_t)cur;
             float4 lox = __ldg(n), loy = __ldg(n + 1), loz = __ldg(n + 2), hix = __ldg(n + 3), hiy = __ldg(n + 4), hiz = __ldg(n + 5);
             int4 ch = __ldg((const int4 *)(n + 6));
@@ -125,6 +127,7 @@ GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], floa
         } else {
             int enc = ~cur;
             int first = enc >> 3, cnt = enc & 7;
+            if (COUNT) (*n_prims) += cnt;
             for (int i = 0; i < cnt; i++) test_prim<EXACT>(bvh, first + i, o, d, tnear, best, hit);
         }
         // pop

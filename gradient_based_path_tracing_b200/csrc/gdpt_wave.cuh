@@ -18,7 +18,8 @@ template <bool EXACT>
 inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n) {
     if (n <= 0) return;
     int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
-    k_trace<EXACT><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n);
+    if (c->count_traversal) k_trace<EXACT, true><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n, c->trav_counters.as<unsigned long long>());
+    else k_trace<EXACT, false><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n, nullptr);
     c->stats.kernel_launches++; c->stats.rays_traced += n;
 }
 

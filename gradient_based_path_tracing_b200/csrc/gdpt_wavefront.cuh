@@ -107,18 +107,30 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 }
 
 // ---------------------------------------------------------------- trace
-template <bool EXACT>
-__global__ void __launch_bounds__(TRACE_BLOCK) k_trace(DBvh bvh, const RayF *rays, Hit *hits, const int *count_ptr, int count_max) {
+// COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
+// (used once by bench.py to derive the algorithmic bytes per ray; never in timed runs).
+template <bool EXACT, bool COUNT>
+__global__ void __launch_bounds__(TRACE_BLOCK) k_trace(DBvh bvh, const RayF *rays, Hit *hits, const int *count_ptr, int count_max,
+                                                       unsigned long long *counters) {
     __shared__ int2 stack[STACK_SMEM * TRACE_BLOCK];
     int n = count_ptr ? min(*count_ptr, count_max) : count_max;
+    unsigned long long cn = 0, cp = 0;
     for (int i = blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += gridDim.x * TRACE_BLOCK) {
         const float4 *rp = (const float4 *)(rays + i);
         float4 a = __ldg(rp), b = __ldg(rp + 1);
         float o[3] = {a.x, a.y, a.z}, d[3] = {b.x, b.y, b.z};
         Hit h;
         if (b.w < a.w) { h.t = b.w; h.u = h.v = 0.f; h.shape_id = -1; h.prim_id = -1; }
-        else h = trace_closest<EXACT>(bvh, o, d, a.w, b.w, stack);
+        else {
+            unsigned nn = 0, np = 0;
+            h = trace_closest<EXACT, COUNT>(bvh, o, d, a.w, b.w, stack, &nn, &np);
+            if (COUNT) { cn += nn; cp += np; }
+        }
         hits[i] = h;
+    }
+    if (COUNT) {
+        for (int s = 16; s > 0; s >>= 1) { cn += __shfl_down_sync(0xffffffffu, cn, s); cp += __shfl_down_sync(0xffffffffu, cp, s); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(counters, cn); atomicAdd(counters + 1, cp); }
     }
 }
 

@@ -116,6 +116,11 @@ int gdpt_merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const do
 int gdpt_poisson(int device, int w, int h, const double *u, const double *gx, const double *gy, double alpha, double *out);
 int gdpt_poisson_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
 int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out);
+/* Run all of the context's work on the caller's CUDA stream (a cudaStream_t; NULL restores the context's own). */
+int gdpt_set_stream(gdpt_ctx *ctx, void *cuda_stream);
+/* Measurement aid: render `spp` samples with a counting traversal and return the mean number of BVH nodes
+ * visited and primitives tested per ray (out[0], out[1]) and the rays traced (out[2]).  Not for timed runs. */
+int gdpt_traversal_counts(gdpt_ctx *ctx, const gdpt_render_params *params, double *out3);
 int gdpt_synchronize(gdpt_ctx *ctx);
 
 /* ---- parity / validation entry points (same device code as the renderer) ---- */
