@@ -441,7 +441,7 @@ template <typename R> GD_D bool sample_disney_bsdf(const BCtx<R> &c, const DMate
 }
 
 // ------------------------------------------------------------------ dispatch
-template <typename R> GD_BIG V3<R> bsdf_eval(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
+template <typename R> GD_D V3<R> bsdf_eval_impl(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
     const DMaterial &m = sc.materials[v.material_id];
     BCtx<R> c{sc, v, dir_in};
     switch (m.type) {
@@ -456,7 +456,7 @@ template <typename R> GD_BIG V3<R> bsdf_eval(const DScene<R> &sc, const Vertex<R
     default: return eval_disney_bsdf(c, dir_out, m);
     }
 }
-template <typename R> GD_BIG R bsdf_pdf(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
+template <typename R> GD_D R bsdf_pdf_impl(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
     const DMaterial &m = sc.materials[v.material_id];
     BCtx<R> c{sc, v, dir_in};
     switch (m.type) {
@@ -469,7 +469,7 @@ template <typename R> GD_BIG R bsdf_pdf(const DScene<R> &sc, const Vertex<R> &v,
     default: return pdf_disney_bsdf(c, dir_out, m);
     }
 }
-template <typename R> GD_BIG bool bsdf_sample(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, R u0, R u1, R w, BsdfSample<R> &s) {
+template <typename R> GD_D bool bsdf_sample_impl(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, R u0, R u1, R w, BsdfSample<R> &s) {
     const DMaterial &m = sc.materials[v.material_id];
     BCtx<R> c{sc, v, dir_in};
     switch (m.type) {
@@ -482,6 +482,28 @@ template <typename R> GD_BIG bool bsdf_sample(const DScene<R> &sc, const Vertex<
     case MAT_DISNEY_CLEARCOAT: return sample_disney_clearcoat(c, c.t1(m.tex[0]), u0, u1, s);
     default: return sample_disney_bsdf(c, m, u0, u1, w, s);
     }
+}
+
+// Out-of-line generic dispatch (any of the nine materials) ...
+template <typename R> GD_BIG V3<R> bsdf_eval(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) { return bsdf_eval_impl<R>(sc, v, dir_in, dir_out); }
+template <typename R> GD_BIG R bsdf_pdf(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) { return bsdf_pdf_impl<R>(sc, v, dir_in, dir_out); }
+template <typename R> GD_BIG bool bsdf_sample(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, R u0, R u1, R w, BsdfSample<R> &s) { return bsdf_sample_impl<R>(sc, v, dir_in, u0, u1, w, s); }
+
+// ... and the material-set selector used by the wavefront kernels: MS_LAMBERTIAN scenes
+// (cbox, Sponza: every material is a Lambertian) get the diffuse code fully inlined, with
+// the register budget of that one lobe instead of the Disney uber-shader's.
+enum { MS_GENERIC = 0, MS_LAMBERTIAN = 1 };
+template <typename R, int MS> GD_D V3<R> bsdf_eval_ms(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
+    if (MS == MS_LAMBERTIAN) { BCtx<R> c{sc, v, dir_in}; return eval_lambertian(c, dir_out, sc.materials[v.material_id].tex[0]); }
+    return bsdf_eval<R>(sc, v, dir_in, dir_out);
+}
+template <typename R, int MS> GD_D R bsdf_pdf_ms(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, const V3<R> &dir_out) {
+    if (MS == MS_LAMBERTIAN) { BCtx<R> c{sc, v, dir_in}; return pdf_cosine(c, dir_out); }
+    return bsdf_pdf<R>(sc, v, dir_in, dir_out);
+}
+template <typename R, int MS> GD_D bool bsdf_sample_ms(const DScene<R> &sc, const Vertex<R> &v, const V3<R> &dir_in, R u0, R u1, R w, BsdfSample<R> &s) {
+    if (MS == MS_LAMBERTIAN) { BCtx<R> c{sc, v, dir_in}; return sample_cosine(c, u0, u1, R(1), s); }
+    return bsdf_sample<R>(sc, v, dir_in, u0, u1, w, s);
 }
 
 } // namespace gdpt

@@ -72,6 +72,7 @@ struct gdpt_ctx {
     gdpt::PoissonCache pc;
     gdpt_stats stats;
     cudaEvent_t ev[8];
+    bool lambertian_only = false;     // every material is a Lambertian -> specialised shade kernels
     bool count_traversal = false;     // bench-only: count nodes/primitives per ray
     bool own_stream = true;
     gdpt::DevBuf trav_counters;
@@ -188,6 +189,8 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         if (mats[i].type < 0 || mats[i].type >= MAT_COUNT) return fail(GDPT_ERR_ARG, "material %d: unknown type %d", i, mats[i].type);
         for (int k = 0; k < 12; k++) { mats[i].tex[k] = (int)m[2 + k]; if (mats[i].tex[k] >= d->n_textures) return fail(GDPT_ERR_ARG, "material %d: texture id out of range", i); }
     }
+    c->lambertian_only = !mats.empty();
+    for (const DMaterial &m : mats) if (m.type != MAT_LAMBERTIAN) c->lambertian_only = false;
     if (int r = upload(c->materials, mats)) return r;
     std::vector<DTexture<double>> td(d->n_textures); std::vector<DTexture<float>> tf(d->n_textures);
     for (int i = 0; i < d->n_textures; i++) {

@@ -35,14 +35,14 @@ template <> struct Consts<float> {
 
 template <typename R> struct V3 {
     R x, y, z;
-    GD_HD V3() {}
+    V3() = default;
     GD_HD V3(R a, R b, R c) : x(a), y(b), z(c) {}
     template <typename S> GD_HD explicit V3(const V3<S> &o) : x((R)o.x), y((R)o.y), z((R)o.z) {}
     GD_HD R operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
 };
 template <typename R> struct V2 {
     R x, y;
-    GD_HD V2() {}
+    V2() = default;
     GD_HD V2(R a, R b) : x(a), y(b) {}
 };
 
@@ -76,7 +76,7 @@ template <typename R> GD_HD R rmin(R a, R b) { return a < b ? a : b; }
 
 template <typename R> struct Frame {
     V3<R> x, y, n;
-    GD_HD Frame() {}
+    Frame() = default;
     GD_HD Frame(const V3<R> &x_, const V3<R> &y_, const V3<R> &n_) : x(x_), y(y_), n(n_) {}
     GD_HD explicit Frame(const V3<R> &n_) : n(n_) {
         if (n_.z < R(-1 + 1e-6)) { x = V3<R>(0, -1, 0); y = V3<R>(-1, 0, 0); }

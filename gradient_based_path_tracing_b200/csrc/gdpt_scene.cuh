@@ -167,7 +167,7 @@ GD_D double sphere_hit_d(const double *sph, const float *o, const float *d, floa
 // org/dir: the ray in working precision (what lajolla holds in double); tnear/tfar_in: the
 // values that were handed to the traversal (needed to re-derive the double sphere root).
 template <typename R>
-GD_BIG void make_vertex(const DScene<R> &sc, const V3<R> &org, const V3<R> &dir, float tnear, float tfar_in,
+GD_D void make_vertex_impl(const DScene<R> &sc, const V3<R> &org, const V3<R> &dir, float tnear, float tfar_in,
                       const Hit &hit, R rd_radius, R rd_spread, Vertex<R> &v) {
     const DShape sh = sc.shapes[hit.shape_id];
     v.shape_id = hit.shape_id; v.prim_id = hit.prim_id; v.material_id = sh.material_id;
@@ -248,6 +248,19 @@ GD_BIG void make_vertex(const DScene<R> &sc, const V3<R> &org, const V3<R> &dir,
     v.ray_radius = rd_radius + rd_spread * distance(org, v.position);
     v.uv_screen_size = v.ray_radius / inv_uv_size;
     if (dot(v.gn, v.sf.n) < R(0)) v.gn = -v.gn;
+}
+
+template <typename R>
+GD_BIG void make_vertex(const DScene<R> &sc, const V3<R> &org, const V3<R> &dir, float tnear, float tfar_in,
+                        const Hit &hit, R rd_radius, R rd_spread, Vertex<R> &v) {
+    make_vertex_impl<R>(sc, org, dir, tnear, tfar_in, hit, rd_radius, rd_spread, v);
+}
+// INL != 0: inline the construction into the caller (specialised wavefront kernels)
+template <typename R, int INL>
+GD_D void make_vertex_ms(const DScene<R> &sc, const V3<R> &org, const V3<R> &dir, float tnear, float tfar_in,
+                         const Hit &hit, R rd_radius, R rd_spread, Vertex<R> &v) {
+    if (INL) make_vertex_impl<R>(sc, org, dir, tnear, tfar_in, hit, rd_radius, rd_spread, v);
+    else make_vertex<R>(sc, org, dir, tnear, tfar_in, hit, rd_radius, rd_spread, v);
 }
 
 // ---------------------------------------------------------------- textures

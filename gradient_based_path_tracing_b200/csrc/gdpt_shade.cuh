@@ -59,29 +59,29 @@ GD_D void finish_with_offsets(const WaveParams &wp, const PathRec<R> &pr, const 
 // Start of a loop iteration at `vtx` (path_tracing.h:528-564 + eval/pdf of :762-763, which
 // depend only on the sampled direction): draws (u,v,w), samples the BSDF, fills the ray.
 // Returns false when sample_bsdf fails (the reference then returns an EMPTY record).
-template <typename R>
+template <typename R, int MS>
 GD_D bool start_iteration(const DScene<R> &sc, const Vertex<R> &vtx, const V3<R> &dir_view, PathRec<R> &pr, RayF &ray) {
     R u0 = pcg_real<R>(pr.rng), u1 = pcg_real<R>(pr.rng), w = pcg_real<R>(pr.rng);
     BsdfSample<R> s;
-    if (!bsdf_sample<R>(sc, vtx, dir_view, u0, u1, w, s)) return false;
+    if (!bsdf_sample_ms<R, MS>(sc, vtx, dir_view, u0, u1, w, s)) return false;
     if (s.eta != R(0)) pr.eta_scale /= (s.eta * s.eta);
     pr.org = vtx.position; pr.dir = s.dir_out;
-    pr.f = bsdf_eval<R>(sc, vtx, dir_view, s.dir_out);
-    pr.p2 = bsdf_pdf<R>(sc, vtx, dir_view, s.dir_out);
+    pr.f = bsdf_eval_ms<R, MS>(sc, vtx, dir_view, s.dir_out);
+    pr.p2 = bsdf_pdf_ms<R, MS>(sc, vtx, dir_view, s.dir_out);
     ray.ox = (float)pr.org.x; ray.oy = (float)pr.org.y; ray.oz = (float)pr.org.z; ray.tnear = (float)sc.eps;
     ray.dx = (float)pr.dir.x; ray.dy = (float)pr.dir.y; ray.dz = (float)pr.dir.z; ray.tfar = __int_as_float(0x7f800000);
     return true;
 }
 
 // ---------------------------------------------------------------- primary stage
-template <typename R>
+template <typename R, int MS>
 __global__ void __launch_bounds__(128) k_primary(DScene<R> sc, WaveParams wp, const GenRec<R> *gen, const Hit *hits,
                                                  PathRec<R> *out, OffRec<R> *off_out, RayF *rays_out, int *out_count) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     bool alive = false;
     PathRec<R> pr; OffRec<R> off; RayF ray;
     if (i < wp.n_paths) {
-        GenRec<R> g = gen[i];
+        GenRec<R> g; load_rec(g, gen + i);
         Hit h0 = hits[i];
         if (h0.shape_id >= 0) {   // inactive padding slots carry a ray that cannot hit
             const int ox[5] = {0, -1, 0, 1, 0}, oy[5] = {0, 0, 1, 0, -1};
@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(128) k_primary(DScene<R> sc, WaveParams wp, co
             V3<R> o, d;
             sample_primary<R>(sc, (R(g.px) + g.rng_x) / R(sc.width), (R(g.py) + g.rng_y) / R(sc.height), o, d);
             Vertex<R> vtx;
-            make_vertex<R>(sc, o, d, 0.f, __int_as_float(0x7f800000), h0, R(0), spread0, vtx);
+            make_vertex_ms<R, MS>(sc, o, d, 0.f, __int_as_float(0x7f800000), h0, R(0), spread0, vtx);
             pr.px = g.px; pr.py = g.py; pr.id = g.id; pr.rng = g.rng; pr.nv = 3;
             pr.thr = V3<R>(1, 1, 1); pr.rad = V3<R>(0, 0, 0); pr.eta_scale = R(1);
             pr.contrib[0] = pr.contrib[1] = pr.contrib[2] = 1.0; pr.prob = 1.0;
@@ -113,31 +113,31 @@ __global__ void __launch_bounds__(128) k_primary(DScene<R> sc, WaveParams wp, co
                 V3<R> ok_, dk;
                 sample_primary<R>(sc, (R(g.px + ox[k + 1]) + g.rng_x) / R(sc.width), (R(g.py + oy[k + 1]) + g.rng_y) / R(sc.height), ok_, dk);
                 Vertex<R> vo;
-                make_vertex<R>(sc, ok_, dk, 0.f, __int_as_float(0x7f800000), hk, R(0), spread0, vo);
+                make_vertex_ms<R, MS>(sc, ok_, dk, 0.f, __int_as_float(0x7f800000), hk, R(0), spread0, vo);
                 V3<R> dvo = -dk;
                 off.enabled |= 1 << k;
                 if (is_light(sc, vo.shape_id)) off.contrib[k] = emission<R>(sc, vo, dvo);
                 if (!loop_runs) continue;
                 BsdfSample<R> s;
-                if (!bsdf_sample<R>(sc, vo, dvo, u0, u1, w, s)) continue;
-                R p = bsdf_pdf<R>(sc, vo, dvo, s.dir_out);
+                if (!bsdf_sample_ms<R, MS>(sc, vo, dvo, u0, u1, w, s)) continue;
+                R p = bsdf_pdf_ms<R, MS>(sc, vo, dvo, s.dir_out);
                 if (p <= R(0)) continue;
                 off.p2s[k] = p; off.sampled |= 1 << k;
             }
             if (!loop_runs) {
                 finish_with_offsets<R>(wp, pr, &off, -1.0);
             } else {
-                if (start_iteration<R>(sc, vtx, dir_view, pr, ray)) alive = true;
+                if (start_iteration<R, MS>(sc, vtx, dir_view, pr, ray)) alive = true;
                 // sample_bsdf failure at the base vertex: `return GraidentPTRadiance{}` -> contributes nothing
             }
         }
     }
     int slot = warp_slot(alive, out_count);
-    if (alive) { out[slot] = pr; off_out[slot] = off; rays_out[slot] = ray; }
+    if (alive) { store_rec(out + slot, pr); store_rec(off_out + slot, off); store_rec(rays_out + slot, ray); }
 }
 
 // ---------------------------------------------------------------- bounce stage
-template <typename R>
+template <typename R, int MS>
 __global__ void __launch_bounds__(128) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
                                                 const Hit *hits, const int *in_count, int in_max,
                                                 PathRec<R> *out, RayF *rays_out, int *out_count) {
@@ -146,16 +146,16 @@ __global__ void __launch_bounds__(128) k_bounce(DScene<R> sc, WaveParams wp, con
     bool alive = false;
     PathRec<R> pr; RayF ray;
     if (i < n) {
-        pr = in[i];
+        load_rec(pr, in + i);
         const bool first = off_in != nullptr;          // iteration with num_vertices == 3
-        OffRec<R> off; if (first) off = off_in[i];
+        OffRec<R> off; if (first) load_rec(off, off_in + i);
         const OffRec<R> *offp = first ? &off : nullptr;
         Hit h = hits[i];
         bool hit = h.shape_id >= 0;
         Vertex<R> nv;
         R G = R(1);
         if (hit) {
-            make_vertex<R>(sc, pr.org, pr.dir, (float)sc.eps, __int_as_float(0x7f800000), h, R(0), R(0), nv);   // intersect(scene, bsdf_ray): default ray differential
+            make_vertex_ms<R, MS>(sc, pr.org, pr.dir, (float)sc.eps, __int_as_float(0x7f800000), h, R(0), R(0), nv);   // intersect(scene, bsdf_ray): default ray differential
             G = fabs(dot(pr.dir, nv.gn)) / distance_squared(nv.position, pr.org);
         }
         do {
@@ -182,11 +182,11 @@ __global__ void __launch_bounds__(128) k_bounce(DScene<R> sc, WaveParams wp, con
             if (!(sc.max_depth == -1 || pr.nv <= sc.max_depth + 1)) { finish_with_offsets<R>(wp, pr, offp, (double)p2); break; }
             // the loop goes on: from here every offset is dropped (garbage-vertex rule, path_tracing.h:607-612,1007-1010)
             V3<R> dir_view = -pr.dir;
-            if (start_iteration<R>(sc, nv, dir_view, pr, ray)) alive = true;
+            if (start_iteration<R, MS>(sc, nv, dir_view, pr, ray)) alive = true;
         } while (false);
     }
     int slot = warp_slot(alive, out_count);
-    if (alive) { out[slot] = pr; rays_out[slot] = ray; }
+    if (alive) { store_rec(out + slot, pr); store_rec(rays_out + slot, ray); }
 }
 
 } // namespace gdpt

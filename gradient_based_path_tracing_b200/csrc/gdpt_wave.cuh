@@ -24,8 +24,8 @@ inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n) {
 }
 
 // generate -> trace -> primary -> (trace -> bounce)*
-template <typename R>
-int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
+template <typename R, int MS>
+int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     const int N = wp.n_paths;
     if (N <= 0) return 0;
     if (int r = c->gen.ensure((size_t)N * sizeof(GenRec<R>))) return r;
@@ -50,7 +50,7 @@ int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     GD_CUDA(cudaEventRecord(e0, st));
     launch_trace<ModeSel<R>::exact>(c, rays, hits, 5 * N);
     GD_CUDA(cudaEventRecord(e1, st));
-    k_primary<R><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, hits, cur, off, rays, cnt);
+    k_primary<R, MS><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, hits, cur, off, rays, cnt);
     c->stats.kernel_launches++;
     GD_CUDA(cudaEventRecord(e2, st));
     GD_CUDA(cudaMemcpyAsync(c->h_counts, cnt, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -66,7 +66,7 @@ int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
         GD_CUDA(cudaEventRecord(e1, st));
         int *cin = cnt + which, *cout = cnt + (which ^ 1);
         GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
-        k_bounce<R><<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout);
+        k_bounce<R, MS><<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout);
         c->stats.kernel_launches++; c->stats.bounce_iterations++;
         GD_CUDA(cudaEventRecord(e2, st));
         GD_CUDA(cudaMemcpyAsync(c->h_counts, cout, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -78,6 +78,11 @@ int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     }
     GD_CUDA(cudaGetLastError());
     return 0;
+}
+
+template <typename R>
+int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
+    return c->lambertian_only ? run_wave_ms<R, MS_LAMBERTIAN>(c, sc, wp) : run_wave_ms<R, MS_GENERIC>(c, sc, wp);
 }
 
 } // namespace gdpt

@@ -19,7 +19,7 @@
 
 namespace gdpt {
 
-struct RayF { float ox, oy, oz, tnear, dx, dy, dz, tfar; };   // 32 B, two float4
+struct alignas(16) RayF { float ox, oy, oz, tnear, dx, dy, dz, tfar; };   // 32 B, two float4
 
 template <typename R> struct alignas(32) PathRec {
     V3<R> org, dir;          // the ray being traced: org = current vertex position, dir = sampled direction
@@ -39,7 +39,7 @@ template <typename R> struct alignas(32) OffRec {   // the four pixel-shifted of
     int sampled;             // bit k: p2s[k] is valid (sample succeeded with pdf > 0)
 };
 
-template <typename R> struct GenRec { R rng_x, rng_y; Pcg rng; int px, py, id; };
+template <typename R> struct alignas(16) GenRec { R rng_x, rng_y; Pcg rng; int px, py, id; };
 
 struct WaveParams {
     int width, height;       // full image
@@ -55,6 +55,23 @@ struct WaveParams {
     // image mode: five accumulation images, W*H*3 doubles each, row-major, y down
     double *img, *cx0, *cy0, *cx1, *cy1;
 };
+
+// Records move between registers and HBM as 16-byte vectors (the compiler's own struct copy
+// degenerates to byte accesses for these aggregates).
+template <typename T> GD_D void load_rec(T &dst, const T *src) {
+    static_assert(sizeof(T) % 16 == 0 && alignof(T) >= 16, "record must be a multiple of 16 bytes");
+    const int4 *s = reinterpret_cast<const int4 *>(src);
+    int4 *d = reinterpret_cast<int4 *>(&dst);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); i++) d[i] = s[i];
+}
+template <typename T> GD_D void store_rec(T *dst, const T &src) {
+    static_assert(sizeof(T) % 16 == 0 && alignof(T) >= 16, "record must be a multiple of 16 bytes");
+    int4 *d = reinterpret_cast<int4 *>(dst);
+    const int4 *s = reinterpret_cast<const int4 *>(&src);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); i++) d[i] = s[i];
+}
 
 GD_D int warp_slot(bool alive, int *counter) {
     unsigned mask = __ballot_sync(0xffffffffu, alive);
@@ -88,13 +105,13 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
     }
     RayF r; r.ox = r.oy = r.oz = 0.f; r.dx = r.dy = r.dz = 0.f; r.tnear = 0.f; r.tfar = -1.f;   // tfar < tnear: never hits
     if (!active) {
-        gen[i] = g;
-        for (int k = 0; k < 5; k++) rays[(size_t)k * wp.n_paths + i] = r;
+        store_rec(gen + i, g);
+        for (int k = 0; k < 5; k++) store_rec(rays + (size_t)k * wp.n_paths + i, r);
         return;
     }
     g.rng = pcg_init(stream, wp.seed);
     g.rng_x = pcg_real<R>(g.rng); g.rng_y = pcg_real<R>(g.rng);
-    gen[i] = g;
+    store_rec(gen + i, g);
     const int ox[5] = {0, -1, 0, 1, 0}, oy[5] = {0, 0, 1, 0, -1};   // base, X0=(x-1,y), Y0=(x,y+1), X1=(x+1,y), Y1=(x,y-1)
 #pragma unroll
     for (int k = 0; k < 5; k++) {
@@ -102,7 +119,7 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
         sample_primary<R>(sc, (R(g.px + ox[k]) + g.rng_x) / R(sc.width), (R(g.py + oy[k]) + g.rng_y) / R(sc.height), o, d);
         r.ox = (float)o.x; r.oy = (float)o.y; r.oz = (float)o.z; r.dx = (float)d.x; r.dy = (float)d.y; r.dz = (float)d.z;
         r.tnear = 0.f; r.tfar = __int_as_float(0x7f800000);
-        rays[(size_t)k * wp.n_paths + i] = r;
+        store_rec(rays + (size_t)k * wp.n_paths + i, r);
     }
 }
 

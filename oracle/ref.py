@@ -51,6 +51,27 @@ def lib():
     return _lib
 
 
+class _quiet:
+    """The reference prints a progress line per tile and banners to stdout (progress_reporter.h,
+    parse_scene.cpp); silence fd 1 around its calls so callers keep a clean stdout (bench.py's JSON line)."""
+
+    def __enter__(self):
+        import sys
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        self.null = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 1)
+
+    def __exit__(self, *a):
+        try:
+            C.CDLL(None).fflush(None)
+        except Exception:
+            pass
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+        os.close(self.null)
+
+
 def _dp(a):
     return a.ctypes.data_as(C.POINTER(C.c_double)) if a is not None else None
 
@@ -106,7 +127,8 @@ def make_variant(xml_path, out_dir=None, **subs):
 class RefScene:
     def __init__(self, xml_path, threads=None):
         init(threads)
-        self.h = lib().gdpt_ref_load(os.path.abspath(xml_path).encode())
+        with _quiet():
+            self.h = lib().gdpt_ref_load(os.path.abspath(xml_path).encode())
         if not self.h:
             raise RuntimeError("reference failed to parse " + xml_path)
         self.refresh()
@@ -132,12 +154,14 @@ class RefScene:
     def render(self):
         """Reference render() with GradPath. Returns dict(primal, dx, dy, poisson) = c, cx, cy, out."""
         c, cx, cy, out = self._img(), self._img(), self._img(), self._img()
-        lib().gdpt_ref_render(self.h, _dp(c), _dp(cx), _dp(cy), _dp(out))
+        with _quiet():
+            lib().gdpt_ref_render(self.h, _dp(c), _dp(cx), _dp(cy), _dp(out))
         return dict(primal=c, dx=cx, dy=cy, poisson=out)
 
     def render_path(self):
         out = self._img()
-        lib().gdpt_ref_render_path(self.h, _dp(out))
+        with _quiet():
+            lib().gdpt_ref_render_path(self.h, _dp(out))
         return out
 
     def grad_sample(self, x, y, stream, seed=DEFAULT_SEED):
