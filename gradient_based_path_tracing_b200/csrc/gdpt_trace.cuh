@@ -3,6 +3,8 @@
 // callback (/root/reference/src/shapes/sphere.inl:40-106).
 //
 //  * one thread per ray; the ray is the FLOAT ray Embree would be handed;
+//  * "while-while" traversal: all lanes of a warp walk inner nodes until each holds a leaf
+//    (or is done), then all test leaves — the two phases never interleave inside a warp;
 //  * node = one 128-byte line fetched as 8 x 16-byte __ldg loads, 4 slab tests;
 //  * children visited front to back; the traversal stack lives in shared memory
 //    ([level][thread] -> bank-conflict free) with a small local-memory spill;
@@ -85,60 +87,83 @@ GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3],
     best = t; hit.t = t; hit.u = u; hit.v = v; hit.shape_id = shape_id; hit.prim_id = prim_id;
 }
 
-// smem_stack: TRACE_BLOCK * STACK_SMEM int2 of shared memory owned by the block
+constexpr int TRACE_DONE = (int)0x80000000;   // "no more work for this ray" (never a valid leaf encoding)
+
+// Per-ray traversal state kept in registers.
+struct RayState {
+    float o[3], d[3], id[3];   // origin, direction, 1/direction
+    float tnear, best;         // best = current tfar
+    Hit hit;
+    GD_D void init(const float4 &a, const float4 &b) {
+        o[0] = a.x; o[1] = a.y; o[2] = a.z; d[0] = b.x; d[1] = b.y; d[2] = b.z;
+        id[0] = 1.0f / b.x; id[1] = 1.0f / b.y; id[2] = 1.0f / b.z;
+        tnear = a.w; best = b.w;
+        hit.t = b.w; hit.u = hit.v = 0.f; hit.shape_id = -1; hit.prim_id = -1;
+    }
+};
+
+// next entry of the stack that can still contain a closer hit
+GD_D int trace_pop(const TraceStack &st, int &sp, float best) {
+    while (sp > 0) {
+        int2 e = st.get(--sp);
+        if (__int_as_float(e.y) <= best) return e.x;
+    }
+    return TRACE_DONE;
+}
+
+// Inner node: slab-test the 4 children, descend into the nearest, push the rest far-to-near.
+GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, TraceStack &st, int &sp) {
+    const float4 *n = bvh.nodes + 8 * (size_t)cur;
+    float4 lox = __ldg(n), loy = __ldg(n + 1), loz = __ldg(n + 2), hix = __ldg(n + 3), hiy = __ldg(n + 4), hiz = __ldg(n + 5);
+    int4 ch = __ldg((const int4 *)(n + 6));
+    float dist[4]; int cid[4] = {ch.x, ch.y, ch.z, ch.w};
+    const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
+    const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+    const float INF = __int_as_float(0x7f800000);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        float t0x = (lx[k] - r.o[0]) * r.id[0], t1x = (hx[k] - r.o[0]) * r.id[0];
+        float t0y = (ly[k] - r.o[1]) * r.id[1], t1y = (hy[k] - r.o[1]) * r.id[1];
+        float t0z = (lz[k] - r.o[2]) * r.id[2], t1z = (hz[k] - r.o[2]) * r.id[2];
+        float tmn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tnear));
+        float tmx = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), r.best));
+        tmx *= 1.0000005f;   // conservative slab (rounding of the three products)
+        dist[k] = (cid[k] != 0 && tmn <= tmx) ? tmn : INF;
+    }
+    // sort the 4 candidates by distance (network), nearest first
+#define GD_CSWAP(i, j) if (dist[j] < dist[i]) { float td = dist[i]; dist[i] = dist[j]; dist[j] = td; int tc = cid[i]; cid[i] = cid[j]; cid[j] = tc; }
+    GD_CSWAP(0, 1) GD_CSWAP(2, 3) GD_CSWAP(0, 2) GD_CSWAP(1, 3) GD_CSWAP(1, 2)
+#undef GD_CSWAP
+    if (dist[3] < INF) st.put(sp++, cid[3], dist[3]);
+    if (dist[2] < INF) st.put(sp++, cid[2], dist[2]);
+    if (dist[1] < INF) st.put(sp++, cid[1], dist[1]);
+    if (dist[0] < INF) return cid[0];
+    return trace_pop(st, sp, r.best);
+}
+
+// Leaf (cur < 0, != TRACE_DONE): test its primitives, then pop.
+template <bool EXACT>
+GD_D int trace_leaf(const DBvh &bvh, int cur, RayState &r, const TraceStack &st, int &sp, unsigned *n_prims) {
+    int enc = ~cur;
+    int first = enc >> 3, cnt = enc & 7;
+    if (n_prims) *n_prims += cnt;
+    for (int i = 0; i < cnt; i++) test_prim<EXACT>(bvh, first + i, r.o, r.d, r.tnear, r.best, r.hit);
+    return trace_pop(st, sp, r.best);
+}
+
+// One ray, one thread (validation entry points).  smem_stack: TRACE_BLOCK * STACK_SMEM int2 owned by the block.
 template <bool EXACT, bool COUNT = false>
 GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], float tnear, float tfar, int2 *smem_stack,
                        unsigned *n_nodes = nullptr, unsigned *n_prims = nullptr) {
-    Hit hit; hit.t = tfar; hit.u = hit.v = 0.f; hit.shape_id = -1; hit.prim_id = -1;
-    if (bvh.n_nodes == 0) return hit;
+    RayState r; r.init(make_float4(o[0], o[1], o[2], tnear), make_float4(d[0], d[1], d[2], tfar));
+    if (bvh.n_nodes == 0) return r.hit;
     TraceStack st; st.smem = smem_stack;
-    float idx = 1.0f / d[0], idy = 1.0f / d[1], idz = 1.0f / d[2];
-    float best = tfar;
-    int sp = 0;
-    int cur = 0;   // root node
-    while (true) {
-        if (cur >= 0) {
-            if (COUNT) (*n_nodes)++;
-            const float4 *n = bvh.nodes + 8 * (size_t)cur;
-            float4 lox = __ldg(n), loy = __ldg(n + 1), loz = __ldg(n + 2), hix = __ldg(n + 3), hiy = __ldg(n + 4), hiz = __ldg(n + 5);
-            int4 ch = __ldg((const int4 *)(n + 6));
-            float dist[4]; int cid[4] = {ch.x, ch.y, ch.z, ch.w};
-            const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
-            const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                float t0x = (lx[k] - o[0]) * idx, t1x = (hx[k] - o[0]) * idx;
-                float t0y = (ly[k] - o[1]) * idy, t1y = (hy[k] - o[1]) * idy;
-                float t0z = (lz[k] - o[2]) * idz, t1z = (hz[k] - o[2]) * idz;
-                float tmn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tnear));
-                float tmx = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), best));
-                tmx *= 1.0000005f;   // conservative slab (rounding of the three products)
-                dist[k] = (cid[k] != 0 && tmn <= tmx) ? tmn : __int_as_float(0x7f800000);
-            }
-            // sort the 4 candidates by distance (network), nearest first
-#define GD_CSWAP(i, j) if (dist[j] < dist[i]) { float td = dist[i]; dist[i] = dist[j]; dist[j] = td; int tc = cid[i]; cid[i] = cid[j]; cid[j] = tc; }
-            GD_CSWAP(0, 1) GD_CSWAP(2, 3) GD_CSWAP(0, 2) GD_CSWAP(1, 3) GD_CSWAP(1, 2)
-#undef GD_CSWAP
-            const float INF = __int_as_float(0x7f800000);
-            if (dist[3] < INF) st.put(sp++, cid[3], dist[3]);
-            if (dist[2] < INF) st.put(sp++, cid[2], dist[2]);
-            if (dist[1] < INF) st.put(sp++, cid[1], dist[1]);
-            if (dist[0] < INF) { cur = cid[0]; continue; }
-        } else {
-            int enc = ~cur;
-            int first = enc >> 3, cnt = enc & 7;
-            if (COUNT) (*n_prims) += cnt;
-            for (int i = 0; i < cnt; i++) test_prim<EXACT>(bvh, first + i, o, d, tnear, best, hit);
-        }
-        // pop
-        bool found = false;
-        while (sp > 0) {
-            int2 e = st.get(--sp);
-            if (__int_as_float(e.y) <= best) { cur = e.x; found = true; break; }
-        }
-        if (!found) break;
+    int sp = 0, cur = 0;
+    while (cur != TRACE_DONE) {
+        while (cur >= 0) { if (COUNT) (*n_nodes)++; cur = trace_node(bvh, cur, r, st, sp); }
+        if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? n_prims : nullptr);
     }
-    return hit;
+    return r.hit;
 }
 
 } // namespace gdpt

@@ -17,7 +17,7 @@ template <> struct ModeSel<float> { static constexpr bool exact = false; };
 template <bool EXACT>
 inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n) {
     if (n <= 0) return;
-    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
+    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 8);   // persistent blocks, ~7 resident per SM
     if (c->count_traversal) k_trace<EXACT, true><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n, c->trav_counters.as<unsigned long long>());
     else k_trace<EXACT, false><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n, nullptr);
     c->stats.kernel_launches++; c->stats.rays_traced += n;

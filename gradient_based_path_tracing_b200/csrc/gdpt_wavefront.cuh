@@ -124,30 +124,56 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 }
 
 // ---------------------------------------------------------------- trace
-// COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
-// (used once by bench.py to derive the algorithmic bytes per ray; never in timed runs).
+// Persistent blocks: each block owns a contiguous chunk of the ray queue and its lanes pull
+// the next ray from a shared-memory cursor the moment their current ray finishes, so a warp
+// is not held hostage by its longest ray.  COUNT=true additionally sums visited nodes /
+// tested primitives into counters[0..1] (used once by bench.py to derive the algorithmic
+// bytes per ray; never in timed runs).
 template <bool EXACT, bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_trace(DBvh bvh, const RayF *rays, Hit *hits, const int *count_ptr, int count_max,
                                                        unsigned long long *counters) {
     __shared__ int2 stack[STACK_SMEM * TRACE_BLOCK];
-    int n = count_ptr ? min(*count_ptr, count_max) : count_max;
-    unsigned long long cn = 0, cp = 0;
-    for (int i = blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += gridDim.x * TRACE_BLOCK) {
-        const float4 *rp = (const float4 *)(rays + i);
-        float4 a = __ldg(rp), b = __ldg(rp + 1);
-        float o[3] = {a.x, a.y, a.z}, d[3] = {b.x, b.y, b.z};
-        Hit h;
-        if (b.w < a.w) { h.t = b.w; h.u = h.v = 0.f; h.shape_id = -1; h.prim_id = -1; }
-        else {
-            unsigned nn = 0, np = 0;
-            h = trace_closest<EXACT, COUNT>(bvh, o, d, a.w, b.w, stack, &nn, &np);
-            if (COUNT) { cn += nn; cp += np; }
+    __shared__ int cursor;
+    const unsigned FULL = 0xffffffffu;
+    const int n = count_ptr ? min(*count_ptr, count_max) : count_max;
+    const long long per = (((long long)n + gridDim.x - 1) / gridDim.x + 31) & ~31LL;
+    const int begin = (int)min((long long)n, blockIdx.x * per), end = (int)min((long long)n, begin + per);
+    if (threadIdx.x == 0) cursor = begin;
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    TraceStack st; st.smem = stack;
+    RayState r;
+    int ray = -1, cur = TRACE_DONE, sp = 0;
+    bool exhausted = false;
+    unsigned cn = 0, cp = 0;
+    unsigned long long tn = 0, tp = 0;
+    while (true) {
+        const bool need = cur == TRACE_DONE && !exhausted;
+        const unsigned m = __ballot_sync(FULL, need);
+        if (m) {
+            int base = 0;
+            const int leader = __ffs(m) - 1;
+            if (lane == leader) base = atomicAdd(&cursor, __popc(m));
+            base = __shfl_sync(FULL, base, leader);
+            if (need) {
+                if (ray >= 0) { hits[ray] = r.hit; if (COUNT) { tn += cn; tp += cp; cn = cp = 0; } }
+                ray = base + __popc(m & ((1u << lane) - 1u));
+                if (ray < end) {
+                    const float4 *rp = (const float4 *)(rays + ray);
+                    float4 a = __ldg(rp), b = __ldg(rp + 1);
+                    r.init(a, b);
+                    sp = 0;
+                    cur = (b.w < a.w || bvh.n_nodes == 0) ? TRACE_DONE : 0;   // tfar < tnear: never hits
+                } else { ray = -1; exhausted = true; }
+            }
         }
-        hits[i] = h;
+        if (__all_sync(FULL, cur == TRACE_DONE && exhausted)) break;
+        while (cur >= 0) { if (COUNT) cn++; cur = trace_node(bvh, cur, r, st, sp); }
+        if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
     }
     if (COUNT) {
-        for (int s = 16; s > 0; s >>= 1) { cn += __shfl_down_sync(0xffffffffu, cn, s); cp += __shfl_down_sync(0xffffffffu, cp, s); }
-        if ((threadIdx.x & 31) == 0) { atomicAdd(counters, cn); atomicAdd(counters + 1, cp); }
+        for (int s = 16; s > 0; s >>= 1) { tn += __shfl_down_sync(FULL, tn, s); tp += __shfl_down_sync(FULL, tp, s); }
+        if (lane == 0) { atomicAdd(counters, tn); atomicAdd(counters + 1, tp); }
     }
 }
 
