@@ -185,10 +185,8 @@ def test_pixel_seeded_image_matches_reference(g, scenes):
     cx, cy = cport.merge(z["cx0"], z["cx1"], z["cy0"], z["cy1"])
     for got, want in ((r.dx, cx), (r.dy, cy)):
         close = np.isclose(got, want, rtol=1e-7, atol=1e-9)
-        # an offset ray that grazes a shared edge may resolve to the other coplanar triangle than under the
-        # oracle's stand-in BVH (documented tie; same rate as test_fp64_records: <= 4e-3 of the samples, each
-        # touching up to 4 gradient entries) — the primal image above must agree everywhere
-        assert close.mean() > 0.99
+        # same tolerance as test_fp64_records: a last-ulp difference may flip a branch in a handful of samples
+        assert close.mean() > 0.995
     assert rel_l2(r.poisson, cport.poisson(r.primal, r.dx, r.dy)) < 1e-9
 
 
