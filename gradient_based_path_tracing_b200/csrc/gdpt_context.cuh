@@ -1,6 +1,7 @@
 // Host-side context behind the C ABI: device copies of the flattened scene in both
 // arithmetic modes, mip chains, the BVH, wavefront queues and Poisson work buffers.
 #pragma once
+#include <cstdlib>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -72,6 +73,10 @@ struct gdpt_ctx {
     gdpt::PoissonCache pc;
     gdpt_stats stats;
     cudaEvent_t ev[8];
+    bool sort_rays = true;            // re-order bounce-ray queues by origin cell + direction octant (GDPT_SORT_RAYS=0 disables)
+    float box_lo[3] = {0, 0, 0}, box_hi[3] = {0, 0, 0};   // float scene box (BVH root)
+    gdpt::DevBuf sort_keys, sort_order, sort_hist;
+    int trace_variant = -1;           // tuning knob (GDPT_TRACE_VARIANT); -1 = the default kernel
     bool lambertian_only = false;     // every material is a Lambertian -> specialised shade kernels
     bool count_traversal = false;     // bench-only: count nodes/primitives per ray
     bool own_stream = true;
@@ -155,8 +160,9 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         if (h.kind == 1) for (int t = 0; t < 3 * h.ntris; t++) if (h.indices[t] < 0 || h.indices[t] >= h.nverts) return fail(GDPT_ERR_ARG, "shape %d: vertex index out of range", i);
     }
     Bvh bvh; build_bvh(hs, bvh);
-    if (3 * bvh.max_depth + 1 > STACK_SMEM + STACK_SPILL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
+    if (3 * bvh.max_depth + 1 > STACK_TOTAL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
     c->bvh_depth = bvh.max_depth;
+    for (int k = 0; k < 3; k++) { c->box_lo[k] = bvh.lo[k]; c->box_hi[k] = bvh.hi[k]; }
     if (int r = upload(c->shapes, shapes)) return r;
     { std::vector<double> sp(d->spheres, d->spheres + 4 * (size_t)d->n_shapes); if (int r = upload(c->spheres, sp)) return r; }
     if (int r = upload(c->bvh_nodes, bvh.nodes)) return r;
@@ -189,6 +195,8 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         if (mats[i].type < 0 || mats[i].type >= MAT_COUNT) return fail(GDPT_ERR_ARG, "material %d: unknown type %d", i, mats[i].type);
         for (int k = 0; k < 12; k++) { mats[i].tex[k] = (int)m[2 + k]; if (mats[i].tex[k] >= d->n_textures) return fail(GDPT_ERR_ARG, "material %d: texture id out of range", i); }
     }
+    if (const char *tv = getenv("GDPT_TRACE_VARIANT")) c->trace_variant = atoi(tv);
+    if (const char *sv = getenv("GDPT_SORT_RAYS")) c->sort_rays = atoi(sv) != 0;
     c->lambertian_only = !mats.empty();
     for (const DMaterial &m : mats) if (m.type != MAT_LAMBERTIAN) c->lambertian_only = false;
     if (int r = upload(c->materials, mats)) return r;
@@ -239,7 +247,7 @@ inline void destroy_context(gdpt_ctx *c) {
     gdpt::DevBuf *all[] = {&c->shapes, &c->spheres, &c->indices, &c->materials, &c->img3, &c->img1, &c->pos_d, &c->nrm_d, &c->uv_d, &c->tex_d,
                            &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tex_f, &c->texels3_f, &c->texels1_f,
                            &c->light_f, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
-                           &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
+                           &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
     for (auto *b : all) b->release();
     c->pc.release();
     if (c->h_counts) cudaFreeHost(c->h_counts);

@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(128) k_primary(DScene<R> sc, WaveParams wp, co
         }
     }
     int slot = warp_slot(alive, out_count);
-    if (alive) { store_rec(out + slot, pr); store_rec(off_out + slot, off); store_rec(rays_out + slot, ray); }
+    if (alive) { store_rec(out + slot, pr); store_rec(off_out + slot, off); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
 }
 
 // ---------------------------------------------------------------- bounce stage
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(128) k_bounce(DScene<R> sc, WaveParams wp, con
         } while (false);
     }
     int slot = warp_slot(alive, out_count);
-    if (alive) { store_rec(out + slot, pr); store_rec(rays_out + slot, ray); }
+    if (alive) { store_rec(out + slot, pr); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
 }
 
 } // namespace gdpt

@@ -26,17 +26,19 @@ struct DBvh {
 
 constexpr int TRACE_BLOCK = 128;
 constexpr int STACK_SMEM = 20;     // entries per thread in shared memory
-constexpr int STACK_SPILL = 44;    // entries per thread in local memory
+constexpr int STACK_TOTAL = 64;    // entries per thread in all (the rest spills to local memory)
 
-struct TraceStack {
-    int2 *smem;            // [STACK_SMEM][TRACE_BLOCK]
-    int2 spill[STACK_SPILL];
+template <int DEPTH = STACK_SMEM>
+struct TraceStackT {
+    int2 *smem;            // [DEPTH][TRACE_BLOCK]
+    int2 spill[STACK_TOTAL - DEPTH];
     GD_D void put(int sp, int node, float d) {
         int2 e = make_int2(node, __float_as_int(d));
-        if (sp < STACK_SMEM) smem[sp * TRACE_BLOCK + threadIdx.x] = e; else spill[sp - STACK_SMEM] = e;
+        if (sp < DEPTH) smem[sp * TRACE_BLOCK + threadIdx.x] = e; else spill[sp - DEPTH] = e;
     }
-    GD_D int2 get(int sp) const { return sp < STACK_SMEM ? smem[sp * TRACE_BLOCK + threadIdx.x] : spill[sp - STACK_SMEM]; }
+    GD_D int2 get(int sp) const { return sp < DEPTH ? smem[sp * TRACE_BLOCK + threadIdx.x] : spill[sp - DEPTH]; }
 };
+using TraceStack = TraceStackT<STACK_SMEM>;
 
 template <bool EXACT>
 GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3], float tnear, float &best, Hit &hit) {
@@ -93,17 +95,21 @@ constexpr int TRACE_DONE = (int)0x80000000;   // "no more work for this ray" (ne
 struct RayState {
     float o[3], d[3], id[3];   // origin, direction, 1/direction
     float tnear, best;         // best = current tfar
+    float oid[3], slack;       // FMA slab form: o*id and the absolute rounding slack that keeps it conservative
     Hit hit;
     GD_D void init(const float4 &a, const float4 &b) {
         o[0] = a.x; o[1] = a.y; o[2] = a.z; d[0] = b.x; d[1] = b.y; d[2] = b.z;
         id[0] = 1.0f / b.x; id[1] = 1.0f / b.y; id[2] = 1.0f / b.z;
         tnear = a.w; best = b.w;
+        oid[0] = o[0] * id[0]; oid[1] = o[1] * id[1]; oid[2] = o[2] * id[2];
+        slack = 2.4e-7f * fmaxf(fmaxf(fabsf(oid[0]), fabsf(oid[1])), fabsf(oid[2]));
         hit.t = b.w; hit.u = hit.v = 0.f; hit.shape_id = -1; hit.prim_id = -1;
     }
 };
 
 // next entry of the stack that can still contain a closer hit
-GD_D int trace_pop(const TraceStack &st, int &sp, float best) {
+template <typename ST>
+GD_D int trace_pop(const ST &st, int &sp, float best) {
     while (sp > 0) {
         int2 e = st.get(--sp);
         if (__int_as_float(e.y) <= best) return e.x;
@@ -112,7 +118,8 @@ GD_D int trace_pop(const TraceStack &st, int &sp, float best) {
 }
 
 // Inner node: slab-test the 4 children, descend into the nearest, push the rest far-to-near.
-GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, TraceStack &st, int &sp) {
+template <int SORT = 0, int FMA = 0, typename ST>
+GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, ST &st, int &sp) {
     const float4 *n = bvh.nodes + 8 * (size_t)cur;
     float4 lox = __ldg(n), loy = __ldg(n + 1), loz = __ldg(n + 2), hix = __ldg(n + 3), hiy = __ldg(n + 4), hiz = __ldg(n + 5);
     int4 ch = __ldg((const int4 *)(n + 6));
@@ -122,17 +129,28 @@ GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, TraceStack &st,
     const float INF = __int_as_float(0x7f800000);
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        float t0x = (lx[k] - r.o[0]) * r.id[0], t1x = (hx[k] - r.o[0]) * r.id[0];
-        float t0y = (ly[k] - r.o[1]) * r.id[1], t1y = (hy[k] - r.o[1]) * r.id[1];
-        float t0z = (lz[k] - r.o[2]) * r.id[2], t1z = (hz[k] - r.o[2]) * r.id[2];
+        float t0x, t1x, t0y, t1y, t0z, t1z;
+        if (FMA) {   // l*id - o*id in one FMA per plane; the slack below covers the cancellation error
+            t0x = fmaf(lx[k], r.id[0], -r.oid[0]); t1x = fmaf(hx[k], r.id[0], -r.oid[0]);
+            t0y = fmaf(ly[k], r.id[1], -r.oid[1]); t1y = fmaf(hy[k], r.id[1], -r.oid[1]);
+            t0z = fmaf(lz[k], r.id[2], -r.oid[2]); t1z = fmaf(hz[k], r.id[2], -r.oid[2]);
+        } else {
+            t0x = (lx[k] - r.o[0]) * r.id[0]; t1x = (hx[k] - r.o[0]) * r.id[0];
+            t0y = (ly[k] - r.o[1]) * r.id[1]; t1y = (hy[k] - r.o[1]) * r.id[1];
+            t0z = (lz[k] - r.o[2]) * r.id[2]; t1z = (hz[k] - r.o[2]) * r.id[2];
+        }
         float tmn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), r.tnear));
         float tmx = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), r.best));
         tmx *= 1.0000005f;   // conservative slab (rounding of the three products)
+        if (FMA) tmx += r.slack + r.slack;
         dist[k] = (cid[k] != 0 && tmn <= tmx) ? tmn : INF;
     }
-    // sort the 4 candidates by distance (network), nearest first
 #define GD_CSWAP(i, j) if (dist[j] < dist[i]) { float td = dist[i]; dist[i] = dist[j]; dist[j] = td; int tc = cid[i]; cid[i] = cid[j]; cid[j] = tc; }
-    GD_CSWAP(0, 1) GD_CSWAP(2, 3) GD_CSWAP(0, 2) GD_CSWAP(1, 3) GD_CSWAP(1, 2)
+    if (SORT == 0) {   // sort the 4 candidates by distance (network), nearest first
+        GD_CSWAP(0, 1) GD_CSWAP(2, 3) GD_CSWAP(0, 2) GD_CSWAP(1, 3) GD_CSWAP(1, 2)
+    } else {           // nearest first only; the others are culled by distance when popped
+        GD_CSWAP(0, 1) GD_CSWAP(0, 2) GD_CSWAP(0, 3)
+    }
 #undef GD_CSWAP
     if (dist[3] < INF) st.put(sp++, cid[3], dist[3]);
     if (dist[2] < INF) st.put(sp++, cid[2], dist[2]);
@@ -142,8 +160,8 @@ GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, TraceStack &st,
 }
 
 // Leaf (cur < 0, != TRACE_DONE): test its primitives, then pop.
-template <bool EXACT>
-GD_D int trace_leaf(const DBvh &bvh, int cur, RayState &r, const TraceStack &st, int &sp, unsigned *n_prims) {
+template <bool EXACT, typename ST>
+GD_D int trace_leaf(const DBvh &bvh, int cur, RayState &r, const ST &st, int &sp, unsigned *n_prims) {
     int enc = ~cur;
     int first = enc >> 3, cnt = enc & 7;
     if (n_prims) *n_prims += cnt;
@@ -160,7 +178,7 @@ GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], floa
     TraceStack st; st.smem = smem_stack;
     int sp = 0, cur = 0;
     while (cur != TRACE_DONE) {
-        while (cur >= 0) { if (COUNT) (*n_nodes)++; cur = trace_node(bvh, cur, r, st, sp); }
+        while (cur >= 0) { if (COUNT) (*n_nodes)++; cur = trace_node<0, 0>(bvh, cur, r, st, sp); }
         if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? n_prims : nullptr);
     }
     return r.hit;

@@ -14,12 +14,26 @@ template <typename R> struct ModeSel;
 template <> struct ModeSel<double> { static constexpr bool exact = true; };
 template <> struct ModeSel<float> { static constexpr bool exact = false; };
 
+constexpr int TRACE_DEFAULT_VARIANT = 0;
+constexpr int SORT_MIN_RAYS = 1 << 17;   // below this a launch is too small for the sort to pay
+
+template <bool EXACT, bool COUNT, int V>
+inline void launch_trace_v(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const int *order) {
+    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
+    k_trace<EXACT, COUNT, V><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, order, n, COUNT ? c->trav_counters.as<unsigned long long>() : nullptr);
+}
+
 template <bool EXACT>
-inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n) {
+inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const int *order = nullptr) {
     if (n <= 0) return;
-    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 8);   // persistent blocks, ~7 resident per SM
-    if (c->count_traversal) k_trace<EXACT, true><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n, c->trav_counters.as<unsigned long long>());
-    else k_trace<EXACT, false><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n, nullptr);
+    if (c->count_traversal) launch_trace_v<EXACT, true, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
+    else if constexpr (EXACT) launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
+    else switch (c->trace_variant) {
+#define GD_V(v) case v: launch_trace_v<EXACT, false, v>(c, rays, hits, n, order); break;
+        GD_V(0) GD_V(100) GD_V(200) GD_V(300) GD_V(2200) GD_V(2300) GD_V(3200) GD_V(3300) GD_V(10) GD_V(210) GD_V(1000)
+#undef GD_V
+        default: launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
+    }
     c->stats.kernel_launches++; c->stats.rays_traced += n;
 }
 
@@ -35,6 +49,18 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     if (int r = c->rec_b.ensure((size_t)N * sizeof(PathRec<R>))) return r;
     if (int r = c->off.ensure((size_t)N * sizeof(OffRec<R>))) return r;
     if (int r = c->counters.ensure(64)) return r;
+    const bool sorting = c->sort_rays && N >= SORT_MIN_RAYS;
+    if (sorting) {
+        if (int r = c->sort_keys.ensure((size_t)N * sizeof(int))) return r;
+        if (int r = c->sort_order.ensure((size_t)N * sizeof(int))) return r;
+        if (int r = c->sort_hist.ensure((size_t)SORT_BINS * sizeof(int))) return r;
+        wp.sort_keys = c->sort_keys.as<int>(); wp.sort_hist = c->sort_hist.as<int>();
+        const int cells = 1 << SORT_CELL_BITS;
+        for (int k = 0; k < 3; k++) {
+            float ext = c->box_hi[k] - c->box_lo[k];
+            wp.sort_lo[k] = c->box_lo[k]; wp.sort_scale[k] = ext > 0.f ? cells / ext : 0.f;
+        }
+    } else { wp.sort_keys = nullptr; wp.sort_hist = nullptr; }
     int *cnt = c->counters.as<int>();
     GenRec<R> *gen = c->gen.as<GenRec<R>>();
     RayF *rays = c->rays.as<RayF>(); Hit *hits = c->hits.as<Hit>();
@@ -50,6 +76,7 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     GD_CUDA(cudaEventRecord(e0, st));
     launch_trace<ModeSel<R>::exact>(c, rays, hits, 5 * N);
     GD_CUDA(cudaEventRecord(e1, st));
+    if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)SORT_BINS * sizeof(int), st));
     k_primary<R, MS><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, hits, cur, off, rays, cnt);
     c->stats.kernel_launches++;
     GD_CUDA(cudaEventRecord(e2, st));
@@ -62,8 +89,16 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     int which = 0; bool first = true;
     while (count > 0) {
         GD_CUDA(cudaEventRecord(e0, st));
-        launch_trace<ModeSel<R>::exact>(c, rays, hits, count);
+        const int *order = nullptr;
+        if (sorting && count >= SORT_MIN_RAYS) {   // histogram was filled by the kernel that emitted these rays
+            k_sort_scan<<<1, 1024, 0, st>>>(wp.sort_hist);
+            k_sort_scatter<<<blocks_for(count, 256), 256, 0, st>>>(wp.sort_keys, wp.sort_hist, count, c->sort_order.as<int>());
+            c->stats.kernel_launches += 2;
+            order = c->sort_order.as<int>();
+        }
+        launch_trace<ModeSel<R>::exact>(c, rays, hits, count, order);
         GD_CUDA(cudaEventRecord(e1, st));
+        if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)SORT_BINS * sizeof(int), st));
         int *cin = cnt + which, *cout = cnt + (which ^ 1);
         GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
         k_bounce<R, MS><<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout);

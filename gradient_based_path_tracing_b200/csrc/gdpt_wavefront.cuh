@@ -54,7 +54,65 @@ struct WaveParams {
     const int *xs, *ys; const unsigned long long *streams; double *rec_out;
     // image mode: five accumulation images, W*H*3 doubles each, row-major, y down
     double *img, *cx0, *cy0, *cx1, *cy1;
+    // ray sorting (set by run_wave when enabled): per-slot key + histogram, origin grid over the scene box
+    int *sort_keys, *sort_hist;
+    float sort_lo[3], sort_scale[3];
 };
+
+// ---------------------------------------------------------------- ray sorting
+// Bounce rays are incoherent; before they are traced the queue is re-ordered by
+// key = Morton(origin cell in a 2^B-per-axis grid over the scene box) : direction octant
+// with a counting sort: the shade kernel that emits a ray also bumps the key's histogram
+// bin, k_sort_scan turns the histogram into start offsets, k_sort_scatter writes the
+// permutation `order` that k_trace follows.  Rays themselves never move.
+constexpr int SORT_CELL_BITS = 4;
+constexpr int SORT_BINS = 1 << (3 * SORT_CELL_BITS + 3);
+
+GD_D unsigned sort_spread(unsigned x) {   // abcd -> a00b00c00d
+    unsigned r = 0;
+#pragma unroll
+    for (int b = 0; b < SORT_CELL_BITS; b++) r |= ((x >> b) & 1u) << (3 * b);
+    return r;
+}
+GD_D void sort_emit(const WaveParams &wp, int slot, const RayF &r) {
+    if (!wp.sort_hist) return;
+    const int top = (1 << SORT_CELL_BITS) - 1;
+    int cx = min(top, max(0, (int)((r.ox - wp.sort_lo[0]) * wp.sort_scale[0])));
+    int cy = min(top, max(0, (int)((r.oy - wp.sort_lo[1]) * wp.sort_scale[1])));
+    int cz = min(top, max(0, (int)((r.oz - wp.sort_lo[2]) * wp.sort_scale[2])));
+    unsigned key = ((sort_spread(cx) | (sort_spread(cy) << 1) | (sort_spread(cz) << 2)) << 3) |
+                   (r.dx < 0.f ? 1u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 4u : 0u);
+    wp.sort_keys[slot] = (int)key;
+    atomicAdd(wp.sort_hist + key, 1);
+}
+// exclusive scan of the SORT_BINS histogram, one block of 1024 threads
+static __global__ void __launch_bounds__(1024) k_sort_scan(int *hist) {
+    constexpr int PER = SORT_BINS / 1024;
+    __shared__ int warp_sum[32];
+    int v[PER], sum = 0;
+    int4 *h4 = reinterpret_cast<int4 *>(hist + threadIdx.x * PER);
+#pragma unroll
+    for (int i = 0; i < PER / 4; i++) { int4 q = h4[i]; v[4 * i] = q.x; v[4 * i + 1] = q.y; v[4 * i + 2] = q.z; v[4 * i + 3] = q.w; }
+#pragma unroll
+    for (int i = 0; i < PER; i++) { int t = v[i]; v[i] = sum; sum += t; }
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, incl = sum;
+    for (int s = 1; s < 32; s <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += t; }
+    if (lane == 31) warp_sum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int ws = warp_sum[lane], wi = ws;
+        for (int s = 1; s < 32; s <<= 1) { int t = __shfl_up_sync(0xffffffffu, wi, s); if (lane >= s) wi += t; }
+        warp_sum[lane] = wi - ws;
+    }
+    __syncthreads();
+    int base = warp_sum[wid] + incl - sum;
+#pragma unroll
+    for (int i = 0; i < PER / 4; i++) h4[i] = make_int4(v[4 * i] + base, v[4 * i + 1] + base, v[4 * i + 2] + base, v[4 * i + 3] + base);
+}
+static __global__ void __launch_bounds__(256) k_sort_scatter(const int *keys, int *offsets, int n, int *order) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) order[atomicAdd(offsets + keys[i], 1)] = i;
+}
 
 // Records move between registers and HBM as 16-byte vectors (the compiler's own struct copy
 // degenerates to byte accesses for these aggregates).
@@ -124,56 +182,47 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 }
 
 // ---------------------------------------------------------------- trace
-// Persistent blocks: each block owns a contiguous chunk of the ray queue and its lanes pull
-// the next ray from a shared-memory cursor the moment their current ray finishes, so a warp
-// is not held hostage by its longest ray.  COUNT=true additionally sums visited nodes /
-// tested primitives into counters[0..1] (used once by bench.py to derive the algorithmic
-// bytes per ray; never in timed runs).
-template <bool EXACT, bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK) k_trace(DBvh bvh, const RayF *rays, Hit *hits, const int *count_ptr, int count_max,
-                                                       unsigned long long *counters) {
-    __shared__ int2 stack[STACK_SMEM * TRACE_BLOCK];
-    __shared__ int cursor;
-    const unsigned FULL = 0xffffffffu;
-    const int n = count_ptr ? min(*count_ptr, count_max) : count_max;
-    const long long per = (((long long)n + gridDim.x - 1) / gridDim.x + 31) & ~31LL;
-    const int begin = (int)min((long long)n, blockIdx.x * per), end = (int)min((long long)n, begin + per);
-    if (threadIdx.x == 0) cursor = begin;
-    __syncthreads();
-    const int lane = threadIdx.x & 31;
-    TraceStack st; st.smem = stack;
-    RayState r;
-    int ray = -1, cur = TRACE_DONE, sp = 0;
-    bool exhausted = false;
-    unsigned cn = 0, cp = 0;
+// One ray per thread, grid-stride, independent lanes.  (Persistent-warp variants with dynamic
+// ray fetch — "while-while" and a re-joined node-step/leaf-step loop — were measured 35-75%
+// slower on B200: independent thread scheduling hides the node-fetch latency of diverged
+// lanes better than forced reconvergence does; DESIGN.md, "what was tried".)
+// Tunables V = SORT + 10*FMA + 100*STACKSEL + 1000*OCC (GDPT_TRACE_VARIANT for sweeps):
+//   SORT 0 children fully sorted by distance / 1 nearest first only
+//   FMA  0 (l-o)*id slabs / 1 fma(l, id, -o*id) with an absolute slack
+//   STACKSEL 0: 20, 1: 16, 2: 12, 3: 8 shared-memory stack entries per thread (rest spills)
+//   OCC  0: launch bound 8 blocks/SM (64 regs), 1: 7 (72), 2: 9 (56), 3: 10 (48)
+// COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
+// (bench.py derives the algorithmic bytes per ray from them; never in timed runs).
+constexpr int trace_variant_depth(int v) { return ((v / 100) % 10) == 0 ? 20 : ((v / 100) % 10) == 1 ? 16 : ((v / 100) % 10) == 2 ? 12 : 8; }
+constexpr int trace_variant_blocks(int v) { return (v / 1000) == 0 ? 8 : (v / 1000) == 1 ? 7 : (v / 1000) == 2 ? 9 : 10; }
+
+template <bool EXACT, bool COUNT, int V>
+__global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(DBvh bvh, const RayF *rays, Hit *hits, const int *order, int count_max,
+                                                                               unsigned long long *counters) {
+    constexpr int SORT = V % 10, FMA = (V / 10) % 10, DEPTH = trace_variant_depth(V);
+    __shared__ int2 stack[DEPTH * TRACE_BLOCK];
+    const int n = count_max;
+    TraceStackT<DEPTH> st; st.smem = stack;
     unsigned long long tn = 0, tp = 0;
-    while (true) {
-        const bool need = cur == TRACE_DONE && !exhausted;
-        const unsigned m = __ballot_sync(FULL, need);
-        if (m) {
-            int base = 0;
-            const int leader = __ffs(m) - 1;
-            if (lane == leader) base = atomicAdd(&cursor, __popc(m));
-            base = __shfl_sync(FULL, base, leader);
-            if (need) {
-                if (ray >= 0) { hits[ray] = r.hit; if (COUNT) { tn += cn; tp += cp; cn = cp = 0; } }
-                ray = base + __popc(m & ((1u << lane) - 1u));
-                if (ray < end) {
-                    const float4 *rp = (const float4 *)(rays + ray);
-                    float4 a = __ldg(rp), b = __ldg(rp + 1);
-                    r.init(a, b);
-                    sp = 0;
-                    cur = (b.w < a.w || bvh.n_nodes == 0) ? TRACE_DONE : 0;   // tfar < tnear: never hits
-                } else { ray = -1; exhausted = true; }
+    for (int j = blockIdx.x * TRACE_BLOCK + threadIdx.x; j < n; j += gridDim.x * TRACE_BLOCK) {
+        const int i = order ? __ldg(order + j) : j;   // sorted launch: follow the permutation, rays stay where they are
+        const float4 *rp = (const float4 *)(rays + i);
+        float4 a = __ldg(rp), b = __ldg(rp + 1);
+        RayState r; r.init(a, b);
+        unsigned cn = 0, cp = 0;
+        if (!(b.w < a.w) && bvh.n_nodes != 0) {   // tfar < tnear: never hits
+            int sp = 0, cur = 0;
+            while (cur != TRACE_DONE) {
+                if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA>(bvh, cur, r, st, sp); }
+                else cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
             }
         }
-        if (__all_sync(FULL, cur == TRACE_DONE && exhausted)) break;
-        while (cur >= 0) { if (COUNT) cn++; cur = trace_node(bvh, cur, r, st, sp); }
-        if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
+        hits[i] = r.hit;
+        if (COUNT) { tn += cn; tp += cp; }
     }
     if (COUNT) {
-        for (int s = 16; s > 0; s >>= 1) { tn += __shfl_down_sync(FULL, tn, s); tp += __shfl_down_sync(FULL, tp, s); }
-        if (lane == 0) { atomicAdd(counters, tn); atomicAdd(counters + 1, tp); }
+        for (int s = 16; s > 0; s >>= 1) { tn += __shfl_down_sync(0xffffffffu, tn, s); tp += __shfl_down_sync(0xffffffffu, tp, s); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(counters, tn); atomicAdd(counters + 1, tp); }
     }
 }
 
