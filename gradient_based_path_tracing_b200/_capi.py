@@ -54,7 +54,7 @@ class GdptStats(C.Structure):
 # every symbol include/gdpt.h declares
 EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_destroy", "gdpt_scene_bounds", "gdpt_render",
            "gdpt_render_accumulate_device", "gdpt_merge_device", "gdpt_poisson", "gdpt_poisson_device", "gdpt_get_stats",
-           "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill"]
+           "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill"]
 
 _lib = None
 
@@ -80,6 +80,7 @@ def lib():
         L.gdpt_synchronize.argtypes = [vp]
         L.gdpt_set_stream.argtypes = [vp, vp]
         L.gdpt_traversal_counts.argtypes = [vp, C.POINTER(GdptRenderParams), dp]
+        L.gdpt_measure_l2_read.argtypes = [C.c_int, C.c_int, C.c_int, dp]
         L.gdpt_sample_primary.argtypes = [vp, C.c_int, C.c_int, dp, dp]
         L.gdpt_intersect.argtypes = [vp, C.c_int, C.c_int, dp, dp, ip, dp]
         L.gdpt_bsdf.argtypes = [vp, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp]

@@ -151,6 +151,39 @@ int gdpt_traversal_counts(gdpt_ctx *ctx, const gdpt_render_params *params, doubl
     return 0;
 }
 
+// L2 read-bandwidth probe: every SM streams a buffer that fits in L2 with 16-byte ld.global.cg loads.
+static __global__ void __launch_bounds__(256) k_l2_read(const int4 *buf, size_t n16, int iters, int *sink) {
+    int4 acc = make_int4(0, 0, 0, 0);
+    for (int it = 0; it < iters; it++)
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) {
+            int4 v = __ldcg(buf + i);
+            acc.x ^= v.x; acc.y ^= v.y; acc.z ^= v.z; acc.w ^= v.w;
+        }
+    if ((acc.x ^ acc.y ^ acc.z ^ acc.w) == 0x5a5a5a5a) *sink = 1;   // never true for a zeroed buffer: keeps the loads alive
+}
+
+int gdpt_measure_l2_read(int device, int mbytes, int iters, double *gbs) {
+    if (!gbs || mbytes < 1 || iters < 1) return fail(GDPT_ERR_ARG, "bad argument");
+    GD_CUDA(cudaSetDevice(device));
+    size_t bytes = (size_t)mbytes << 20, n16 = bytes / 16;
+    void *buf = nullptr; int *sink = nullptr;
+    GD_CUDA(cudaMalloc(&buf, bytes));
+    GD_CUDA(cudaMalloc(&sink, 4));
+    GD_CUDA(cudaMemset(buf, 0, bytes));
+    cudaEvent_t e0, e1;
+    GD_CUDA(cudaEventCreate(&e0)); GD_CUDA(cudaEventCreate(&e1));
+    k_l2_read<<<148 * 8, 256>>>((const int4 *)buf, n16, 2, sink);   // warm the L2
+    GD_CUDA(cudaEventRecord(e0));
+    k_l2_read<<<148 * 8, 256>>>((const int4 *)buf, n16, iters, sink);
+    GD_CUDA(cudaEventRecord(e1));
+    GD_CUDA(cudaEventSynchronize(e1));
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    *gbs = (double)bytes * iters / (ms * 1e-3) / 1e9;
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(buf); cudaFree(sink);
+    GD_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out) {
     if (!ctx || !out) return fail(GDPT_ERR_ARG, "null argument");
     *out = ctx->stats; return 0;

@@ -121,6 +121,8 @@ int gdpt_set_stream(gdpt_ctx *ctx, void *cuda_stream);
 /* Measurement aid: render `spp` samples with a counting traversal and return the mean number of BVH nodes
  * visited and primitives tested per ray (out[0], out[1]) and the rays traced (out[2]).  Not for timed runs. */
 int gdpt_traversal_counts(gdpt_ctx *ctx, const gdpt_render_params *params, double *out3);
+/* Measurement aid: L2 read bandwidth (GB/s) of `device`, streaming an `mbytes` buffer (< L2) `iters` times. */
+int gdpt_measure_l2_read(int device, int mbytes, int iters, double *gbs);
 int gdpt_synchronize(gdpt_ctx *ctx);
 
 /* ---- parity / validation entry points (same device code as the renderer) ---- */

@@ -90,5 +90,27 @@ def report(path):
             print()
 
 
+def as_json(path):
+    """The handful of per-launch numbers bench.py quotes next to its live measurements."""
+    import json
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hi = next(i for i, r in enumerate(rows) if "Kernel Name" in r)
+    h, units, r = rows[hi], rows[hi + 1], rows[hi + 2]
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}
+    def val(m):
+        i = h.index(m)
+        return float(r[i].replace(",", "")) * scale.get(units[i], 1)
+    d = {"source": path, "kernel": short(r[h.index("Kernel Name")]),
+         "duration_s": val("gpu__time_duration.sum"),
+         "dram_bytes": val("dram__bytes_read.sum") + val("dram__bytes_write.sum"),
+         "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+         "threads_per_inst": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
+         "warps_active_pct": val("sm__warps_active.avg.pct_of_peak_sustained_active"),
+         "l1_hit_pct": val("l1tex__t_sector_hit_rate.pct"), "l2_hit_pct": val("lts__t_sector_hit_rate.pct"),
+         "registers": val("launch__registers_per_thread"), "grid": val("launch__grid_size")}
+    print(json.dumps(d, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "report": report}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "report": report, "json": as_json}[sys.argv[1]](sys.argv[2])
