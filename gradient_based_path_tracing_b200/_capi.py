@@ -48,7 +48,7 @@ class GdptImages(C.Structure):
 class GdptStats(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_trace", C.c_double), ("ms_shade", C.c_double), ("ms_poisson", C.c_double),
                 ("ms_copy", C.c_double), ("kernel_launches", C.c_int64), ("rays_traced", C.c_int64), ("paths", C.c_int64),
-                ("bounce_iterations", C.c_int64)]
+                ("bounce_iterations", C.c_int64), ("tail_paths", C.c_int64)]
 
 
 # every symbol include/gdpt.h declares

@@ -137,6 +137,44 @@ __global__ void __launch_bounds__(128) k_primary(DScene<R> sc, WaveParams wp, co
 }
 
 // ---------------------------------------------------------------- bounce stage
+// One path-tracing iteration for the path in `pr` whose sampled ray came back with hit `h`
+// (path_tracing.h:746-1010).  Returns true and fills `ray` with the next ray when the path goes on;
+// otherwise the path has been accumulated.  `offp` is non-null for the iteration with num_vertices == 3.
+template <typename R, int MS>
+GD_D bool bounce_step(const DScene<R> &sc, const WaveParams &wp, PathRec<R> &pr, const OffRec<R> *offp, const Hit &h, RayF &ray) {
+    bool hit = h.shape_id >= 0;
+    Vertex<R> nv;
+    R G = R(1);
+    if (hit) {
+        make_vertex_ms<R, MS>(sc, pr.org, pr.dir, (float)sc.eps, __int_as_float(0x7f800000), h, R(0), R(0), nv);   // intersect(scene, bsdf_ray): default ray differential
+        G = fabs(dot(pr.dir, nv.gn)) / distance_squared(nv.position, pr.org);
+    }
+    if (pr.p2 <= R(0)) { finish_with_offsets<R>(wp, pr, offp, -1.0); return false; }     // path_tracing.h:766-769 (offset jacobians still 1)
+    R p2 = pr.p2 * G;
+    pr.contrib[0] = pr.contrib[0] * (double)pr.f.x * (double)G; pr.contrib[1] = pr.contrib[1] * (double)pr.f.y * (double)G;
+    pr.contrib[2] = pr.contrib[2] * (double)pr.f.z * (double)G;
+    pr.prob *= (double)p2;
+    if (hit && is_light(sc, nv.shape_id)) {
+        V3<R> L = emission<R>(sc, nv, -pr.dir);
+        V3<R> C2 = (G * pr.f) * L;
+        pr.contrib[0] *= (double)L.x; pr.contrib[1] *= (double)L.y; pr.contrib[2] *= (double)L.z;
+        C2 = C2 / p2;
+        pr.rad = pr.rad + pr.thr * C2;
+    }
+    if (!hit) { finish_with_offsets<R>(wp, pr, offp, (double)p2); return false; }
+    R rr = R(1);
+    if (pr.nv - 1 >= sc.rr_depth) {
+        rr = rmin(max3((R(1) / pr.eta_scale) * pr.thr), R(0.95));
+        if (pcg_real<R>(pr.rng) > rr) { finish_with_offsets<R>(wp, pr, offp, (double)p2); return false; }
+    }
+    pr.thr = (pr.thr * (G * pr.f)) / (p2 * rr);
+    pr.nv++;
+    if (!(sc.max_depth == -1 || pr.nv <= sc.max_depth + 1)) { finish_with_offsets<R>(wp, pr, offp, (double)p2); return false; }
+    // the loop goes on: from here every offset is dropped (garbage-vertex rule, path_tracing.h:607-612,1007-1010)
+    V3<R> dir_view = -pr.dir;
+    return start_iteration<R, MS>(sc, nv, dir_view, pr, ray);
+}
+
 template <typename R, int MS>
 __global__ void __launch_bounds__(128) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
                                                 const Hit *hits, const int *in_count, int in_max,
@@ -149,44 +187,37 @@ __global__ void __launch_bounds__(128) k_bounce(DScene<R> sc, WaveParams wp, con
         load_rec(pr, in + i);
         const bool first = off_in != nullptr;          // iteration with num_vertices == 3
         OffRec<R> off; if (first) load_rec(off, off_in + i);
-        const OffRec<R> *offp = first ? &off : nullptr;
         Hit h = hits[i];
-        bool hit = h.shape_id >= 0;
-        Vertex<R> nv;
-        R G = R(1);
-        if (hit) {
-            make_vertex_ms<R, MS>(sc, pr.org, pr.dir, (float)sc.eps, __int_as_float(0x7f800000), h, R(0), R(0), nv);   // intersect(scene, bsdf_ray): default ray differential
-            G = fabs(dot(pr.dir, nv.gn)) / distance_squared(nv.position, pr.org);
-        }
-        do {
-            if (pr.p2 <= R(0)) { finish_with_offsets<R>(wp, pr, offp, -1.0); break; }     // path_tracing.h:766-769 (offset jacobians still 1)
-            R p2 = pr.p2 * G;
-            pr.contrib[0] = pr.contrib[0] * (double)pr.f.x * (double)G; pr.contrib[1] = pr.contrib[1] * (double)pr.f.y * (double)G;
-            pr.contrib[2] = pr.contrib[2] * (double)pr.f.z * (double)G;
-            pr.prob *= (double)p2;
-            if (hit && is_light(sc, nv.shape_id)) {
-                V3<R> L = emission<R>(sc, nv, -pr.dir);
-                V3<R> C2 = (G * pr.f) * L;
-                pr.contrib[0] *= (double)L.x; pr.contrib[1] *= (double)L.y; pr.contrib[2] *= (double)L.z;
-                C2 = C2 / p2;
-                pr.rad = pr.rad + pr.thr * C2;
-            }
-            if (!hit) { finish_with_offsets<R>(wp, pr, offp, (double)p2); break; }
-            R rr = R(1);
-            if (pr.nv - 1 >= sc.rr_depth) {
-                rr = rmin(max3((R(1) / pr.eta_scale) * pr.thr), R(0.95));
-                if (pcg_real<R>(pr.rng) > rr) { finish_with_offsets<R>(wp, pr, offp, (double)p2); break; }
-            }
-            pr.thr = (pr.thr * (G * pr.f)) / (p2 * rr);
-            pr.nv++;
-            if (!(sc.max_depth == -1 || pr.nv <= sc.max_depth + 1)) { finish_with_offsets<R>(wp, pr, offp, (double)p2); break; }
-            // the loop goes on: from here every offset is dropped (garbage-vertex rule, path_tracing.h:607-612,1007-1010)
-            V3<R> dir_view = -pr.dir;
-            if (start_iteration<R, MS>(sc, nv, dir_view, pr, ray)) alive = true;
-        } while (false);
+        alive = bounce_step<R, MS>(sc, wp, pr, first ? &off : nullptr, h, ray);
     }
     int slot = warp_slot(alive, out_count);
     if (alive) { store_rec(out + slot, pr); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
+}
+
+// ---------------------------------------------------------------- tail
+// When only a few paths of a wave are still alive, the per-bounce launches (trace, shade, count
+// read-back) cost more than the work in them: this kernel walks each remaining path to its end
+// in one launch — trace and shade in the same thread, no queues.
+template <typename R, int MS, bool EXACT>
+__global__ void __launch_bounds__(TRACE_BLOCK) k_tail(DScene<R> sc, WaveParams wp, DBvh bvh, const PathRec<R> *in, const OffRec<R> *off_in,
+                                                      const RayF *rays, int n) {
+    __shared__ int2 stack[STACK_SMEM * TRACE_BLOCK];
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    PathRec<R> pr; RayF ray;
+    load_rec(pr, in + i); load_rec(ray, rays + i);
+    bool first = off_in != nullptr;
+    OffRec<R> off; if (first) load_rec(off, off_in + i);
+    while (true) {
+        Hit h; h.t = ray.tfar; h.u = h.v = 0.f; h.shape_id = -1; h.prim_id = -1;
+        if (!(ray.tfar < ray.tnear)) {
+            const float o[3] = {ray.ox, ray.oy, ray.oz}, d[3] = {ray.dx, ray.dy, ray.dz};
+            h = trace_closest<EXACT, false>(bvh, o, d, ray.tnear, ray.tfar, stack);
+        }
+        bool alive = bounce_step<R, MS>(sc, wp, pr, first ? &off : nullptr, h, ray);
+        first = false;
+        if (!alive) break;
+    }
 }
 
 } // namespace gdpt

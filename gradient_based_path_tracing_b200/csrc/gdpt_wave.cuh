@@ -19,8 +19,8 @@ constexpr int SORT_MIN_RAYS = 1 << 17;   // below this a launch is too small for
 
 template <bool EXACT, bool COUNT, int V>
 inline void launch_trace_v(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const int *order) {
-    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
-    k_trace<EXACT, COUNT, V><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, order, n, COUNT ? c->trav_counters.as<unsigned long long>() : nullptr);
+    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * (V >= 10000 ? trace_variant_blocks(V) : 16));
+    k_trace<EXACT, COUNT, V><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, order, n, c->counters.as<int>() + 8, COUNT ? c->trav_counters.as<unsigned long long>() : nullptr);
 }
 
 template <bool EXACT>
@@ -30,7 +30,7 @@ inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const 
     else if constexpr (EXACT) launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
     else switch (c->trace_variant) {
 #define GD_V(v) case v: launch_trace_v<EXACT, false, v>(c, rays, hits, n, order); break;
-        GD_V(0) GD_V(100) GD_V(200) GD_V(300) GD_V(2200) GD_V(2300) GD_V(3200) GD_V(3300) GD_V(10) GD_V(210) GD_V(1000)
+        GD_V(0) GD_V(200) GD_V(10) GD_V(1000) GD_V(10000) GD_V(20000) GD_V(30000) GD_V(11000) GD_V(21000)
 #undef GD_V
         default: launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
     }
@@ -88,6 +88,15 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     c->stats.paths += N;
     int which = 0; bool first = true;
     while (count > 0) {
+        if (count <= c->tail_paths) {   // few paths left: finish them in one launch
+            GD_CUDA(cudaEventRecord(e0, st));
+            k_tail<R, MS, ModeSel<R>::exact><<<blocks_for(count, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(sc, wp, c->bvh, cur, first ? off : nullptr, rays, count);
+            GD_CUDA(cudaEventRecord(e1, st));
+            c->stats.kernel_launches++; c->stats.tail_paths += count;
+            GD_CUDA(cudaEventSynchronize(e1));
+            cudaEventElapsedTime(&ms, e0, e1); c->stats.ms_shade += ms;
+            break;
+        }
         GD_CUDA(cudaEventRecord(e0, st));
         const int *order = nullptr;
         if (sorting && count >= SORT_MIN_RAYS) {   // histogram was filled by the kernel that emitted these rays

@@ -91,6 +91,7 @@ typedef struct { double *primal, *dx, *dy, *poisson; } gdpt_images;
 typedef struct {
     double ms_total, ms_trace, ms_shade, ms_poisson, ms_copy;
     int64_t kernel_launches, rays_traced, paths, bounce_iterations;
+    int64_t tail_paths;       /* paths finished by the single-launch tail kernel (their rays are not in rays_traced) */
 } gdpt_stats;
 
 const char *gdpt_last_error(void);

@@ -216,6 +216,35 @@ def test_row_bands_compose_to_the_full_image(g, scenes):
     assert np.allclose(acc, full, rtol=1e-12, atol=1e-15)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["cbox_gdpt_64", "veach_mi_small"])
+def test_wavefront_queues_and_tail_kernel_agree(g, name, monkeypatch):
+    """The per-bounce queue kernels (k_trace/k_bounce, with and without ray sorting) and the single-launch
+    tail kernel are the same arithmetic: FP64 records must agree bit for bit, and with the reference."""
+    z = golden("records_%s.npz" % name)
+    out = {}
+    for tag, env in (("tail", {"GDPT_TAIL_PATHS": str(1 << 30)}), ("queues", {"GDPT_TAIL_PATHS": "0"})):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        sc = g.Scene.named(name)
+        out[tag] = g.grad_samples(sc, z["xs"], z["ys"], z["streams"], precision="f64")
+        sc.close()
+    a, b = np.nan_to_num(out["tail"]), np.nan_to_num(out["queues"])
+    assert np.array_equal(a, b)
+    # and the image path with sorting forced on/off on a film large enough to take the queue kernels
+    imgs = {}
+    for tag, env in (("sorted", {"GDPT_TAIL_PATHS": "0", "GDPT_SORT_RAYS": "1"}), ("plain", {"GDPT_TAIL_PATHS": "0", "GDPT_SORT_RAYS": "0"}),
+                     ("tail", {"GDPT_TAIL_PATHS": str(1 << 30), "GDPT_SORT_RAYS": "0"})):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        sc = g.Scene.named("cbox_gdpt")
+        imgs[tag] = g.gradient_path_render(sc, spp=1, precision="f64")
+        sc.close()
+    for tag in ("plain", "tail"):
+        for f in ("primal", "dx", "dy"):
+            assert np.allclose(getattr(imgs["sorted"], f), getattr(imgs[tag], f), rtol=1e-9, atol=1e-12), (tag, f)
+
+
 def test_wave_split_does_not_change_the_estimate(g, scenes):
     sc = scenes("cbox_gdpt_64")
     a = g.gradient_path_render(sc, spp=6, precision="f64", outputs=("primal",), wave_samples=1).primal
