@@ -98,7 +98,7 @@ def run_reference(args):
     from oracle import ref
     import numpy as np
     if not ref.scenes_available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref (compiled reference + staged scenes) is missing"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref (compiled reference + staged scenes) is missing"})
         return
     cores = os.cpu_count() or 1
     ref.init(cores)
@@ -124,7 +124,7 @@ def run_reference(args):
             "config": {"workload": "%s gradpath %dx%d %d spp (reference semantics)" % (args.scene, w, h, full_spp)},
             "cpu_baseline": {"value": mpaths, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
             "e2e": {"value": mpaths, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def cpu_baseline(args, scene_name, full_spp):
@@ -293,13 +293,27 @@ def run_native(args):
                 "msamples_per_s": value / 5.0}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, args.scene, spp)
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_STDOUT_FD = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else printed by libraries during the run
+    (NCCL's version banner, the reference's progress bar) was sent to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_STDOUT_FD if _STDOUT_FD is not None else 1, data)
+
+
 def main():
+    global _STDOUT_FD
     args = parse()
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

