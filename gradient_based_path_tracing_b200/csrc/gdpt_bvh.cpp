@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <limits>
 
 namespace gdpt {
@@ -28,6 +29,8 @@ struct BNode { Box b; int left = -1, right = -1, first = 0, count = 0; };
 struct Builder {
     std::vector<Ref> refs;
     std::vector<BNode> nodes;
+    double ci = 1.0;      // SAH cost of one primitive test relative to one (binary) node step
+    int max_leaf = 4;     // <= 7 (3-bit count in the leaf encoding)
 
     int build(int first, int count) {
         BNode n; n.b.reset();
@@ -63,12 +66,12 @@ struct Builder {
         }
         int mid;
         if (bax < 0) {
-            if (count <= 4) return id;
+            if (count <= max_leaf) return id;
             mid = first + count / 2;
         } else {
             // leaf cost vs split cost (traversal cost 1, intersection cost 1 per primitive)
-            double leaf = n.b.area() * count, split = n.b.area() * 1.0 + best;
-            if (count <= 4 && leaf <= split) return id;
+            double leaf = n.b.area() * count * ci, split = n.b.area() * 1.0 + best * ci;
+            if (count <= max_leaf && leaf <= split) return id;
             double ext = (double)cb.hi[bax] - cb.lo[bax];
             auto it = std::partition(refs.begin() + first, refs.begin() + first + count, [&](const Ref &r) {
                 int b = std::min(NB - 1, (int)(NB * ((double)r.c[bax] - cb.lo[bax]) / ext));
@@ -83,6 +86,82 @@ struct Builder {
         return id;
     }
 };
+
+// ---- triangle pre-splitting (spatial splits before the build, as in Embree's HIGH-quality mode the
+// reference asks for, scene.cpp:22): the boxes of large triangles are cut at the spatial median of
+// their longest axis and re-fitted to the clipped triangle, so a long wall or floor triangle stops
+// inflating every node above it.  A triangle may then sit in several leaves; the closest-hit rule
+// is unaffected (same triangle, same t, same ids).
+struct Poly { double v[10][3]; int n; };
+
+inline void clip_poly(const Poly &in, int axis, double plane, bool keep_below, Poly &out) {
+    out.n = 0;
+    for (int i = 0; i < in.n; i++) {
+        const double *a = in.v[i], *b = in.v[(i + 1) % in.n];
+        bool ia = keep_below ? a[axis] <= plane : a[axis] >= plane, ib = keep_below ? b[axis] <= plane : b[axis] >= plane;
+        if (ia) { for (int k = 0; k < 3; k++) out.v[out.n][k] = a[k]; out.n++; }
+        if (ia != ib) {
+            double t = (plane - a[axis]) / (b[axis] - a[axis]);
+            for (int k = 0; k < 3; k++) out.v[out.n][k] = a[k] + t * (b[k] - a[k]);
+            out.v[out.n][axis] = plane; out.n++;
+        }
+    }
+}
+
+// tight float box of (triangle ∩ box), rounded outwards; false if empty
+inline bool clipped_box(const float tri[3][3], const Box &box, Box &out) {
+    Poly p, q; p.n = 3;
+    for (int c = 0; c < 3; c++) for (int k = 0; k < 3; k++) p.v[c][k] = tri[c][k];
+    for (int ax = 0; ax < 3; ax++) {
+        clip_poly(p, ax, (double)box.lo[ax], false, q); if (q.n == 0) return false;
+        clip_poly(q, ax, (double)box.hi[ax], true, p); if (p.n == 0) return false;
+    }
+    const float inf = std::numeric_limits<float>::infinity();
+    for (int k = 0; k < 3; k++) {
+        double lo = p.v[0][k], hi = p.v[0][k];
+        for (int i = 1; i < p.n; i++) { lo = std::min(lo, p.v[i][k]); hi = std::max(hi, p.v[i][k]); }
+        float flo = (float)lo, fhi = (float)hi;
+        if ((double)flo > lo) flo = std::nextafter(flo, -inf);
+        if ((double)fhi < hi) fhi = std::nextafter(fhi, inf);
+        flo = std::nextafter(flo, -inf); fhi = std::nextafter(fhi, inf);        // one more ulp for the interpolation error
+        out.lo[k] = std::max(flo, box.lo[k]); out.hi[k] = std::min(fhi, box.hi[k]);
+        if (out.lo[k] > out.hi[k]) return false;
+    }
+    return true;
+}
+
+// Split the largest boxes first until the reference count reaches `budget`.
+inline void presplit(std::vector<Ref> &refs, const std::vector<BvhPrim> &src, size_t budget) {
+    auto cmp = [&](int a, int b) { return refs[a].b.area() < refs[b].b.area(); };
+    std::vector<int> heap;
+    for (int i = 0; i < (int)refs.size(); i++) if (src[refs[i].idx].kind == 0) heap.push_back(i);
+    std::make_heap(heap.begin(), heap.end(), cmp);
+    while (!heap.empty() && refs.size() < budget) {
+        std::pop_heap(heap.begin(), heap.end(), cmp);
+        int i = heap.back(); heap.pop_back();
+        Ref r = refs[i];
+        int ax = 0; float ext = r.b.hi[0] - r.b.lo[0];
+        for (int k = 1; k < 3; k++) if (r.b.hi[k] - r.b.lo[k] > ext) { ext = r.b.hi[k] - r.b.lo[k]; ax = k; }
+        if (!(ext > 0.f)) break;      // the largest box is a point: nothing left to split
+        float mid = 0.5f * (r.b.lo[ax] + r.b.hi[ax]);
+        if (!(mid > r.b.lo[ax] && mid < r.b.hi[ax])) continue;
+        const BvhPrim &p = src[r.idx];
+        const float tri[3][3] = {{p.v0[0], p.v0[1], p.v0[2]}, {p.v1[0], p.v1[1], p.v1[2]}, {p.v2[0], p.v2[1], p.v2[2]}};
+        Box lb = r.b, rb = r.b; lb.hi[ax] = mid; rb.lo[ax] = mid;
+        Box lt, rt;
+        bool hl = clipped_box(tri, lb, lt), hr = clipped_box(tri, rb, rt);
+        if (!hl || !hr) {             // the triangle only touches one half: just tighten
+            if (hl || hr) { refs[i].b = hl ? lt : rt; for (int k = 0; k < 3; k++) refs[i].c[k] = 0.5f * (refs[i].b.lo[k] + refs[i].b.hi[k]); }
+            continue;
+        }
+        Ref a = r, b = r;
+        a.b = lt; b.b = rt;
+        for (int k = 0; k < 3; k++) { a.c[k] = 0.5f * (lt.lo[k] + lt.hi[k]); b.c[k] = 0.5f * (rt.lo[k] + rt.hi[k]); }
+        refs[i] = a; refs.push_back(b);
+        heap.push_back(i); std::push_heap(heap.begin(), heap.end(), cmp);
+        heap.push_back((int)refs.size() - 1); std::push_heap(heap.begin(), heap.end(), cmp);
+    }
+}
 
 } // namespace
 
@@ -146,6 +225,11 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
             }
         }
     }
+    if (const char *e = getenv("GDPT_BVH_CI")) B.ci = atof(e);                                   // tuning knobs (tools/gpu_bvh_sweep.py)
+    if (const char *e = getenv("GDPT_BVH_MAX_LEAF")) B.max_leaf = std::min(7, std::max(1, atoi(e)));
+    double split_budget = 2.0;      // extra references allowed, as a fraction of the primitive count (B200 sweep: profiles/r1_bvh_sweep.txt)
+    if (const char *e = getenv("GDPT_BVH_SPLIT")) split_budget = atof(e);
+    if (split_budget > 0.0) presplit(B.refs, src, (size_t)((1.0 + split_budget) * B.refs.size()));
     B.nodes.reserve(2 * B.refs.size());
     B.build(0, (int)B.refs.size());
     out.prims.resize(B.refs.size());

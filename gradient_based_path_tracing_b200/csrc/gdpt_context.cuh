@@ -2,6 +2,8 @@
 // arithmetic modes, mip chains, the BVH, wavefront queues and Poisson work buffers.
 #pragma once
 #include <cstdlib>
+#include <chrono>
+#include <cstdio>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -144,6 +146,14 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     for (auto &e : c->ev) GD_CUDA(cudaEventCreate(&e));
     GD_CUDA(cudaMallocHost((void **)&c->h_counts, 64));
 
+    const bool verbose = getenv("GDPT_VERBOSE") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        auto now = std::chrono::steady_clock::now();
+        if (verbose) fprintf(stderr, "[gdpt_create] %-18s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
+    lap("cuda init");
     // ---- shapes + BVH
     std::vector<DShape> shapes(d->n_shapes);
     std::vector<HostShape> hs(d->n_shapes);
@@ -161,6 +171,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         if (h.kind == 1) for (int t = 0; t < 3 * h.ntris; t++) if (h.indices[t] < 0 || h.indices[t] >= h.nverts) return fail(GDPT_ERR_ARG, "shape %d: vertex index out of range", i);
     }
     Bvh bvh; build_bvh(hs, bvh);
+    lap("bvh build");
     if (3 * bvh.max_depth + 1 > STACK_TOTAL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
     c->bvh_depth = bvh.max_depth;
     for (int k = 0; k < 3; k++) { c->box_lo[k] = bvh.lo[k]; c->box_hi[k] = bvh.hi[k]; }
@@ -179,6 +190,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     }
     double eps = std::min(c->bounds[0] * 1e-5, 0.01);   // scene.h:104-106
 
+    lap("bvh upload");
     // ---- geometry pools
     std::vector<double> pos(d->positions, d->positions + 3 * (size_t)d->n_positions), nrm(d->normals, d->normals + 3 * (size_t)d->n_normals),
         uv(d->uvs, d->uvs + 2 * (size_t)d->n_uvs);
@@ -188,6 +200,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     if (int r = upload(c->pos_f, to_f(pos))) return r; if (int r = upload(c->nrm_f, to_f(nrm))) return r; if (int r = upload(c->uv_f, to_f(uv))) return r;
     if (int r = upload(c->indices, idx)) return r;
 
+    lap("geometry upload");
     // ---- materials / textures / images
     std::vector<DMaterial> mats(d->n_materials);
     for (int i = 0; i < d->n_materials; i++) {
@@ -219,6 +232,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     std::vector<double> pool3, pool1, tmp;
     for (int i = 0; i < d->n_images3; i++) { if (int r = decode_image(d->images3[i], 3, tmp)) return r; build_mips(d->images3[i].width, d->images3[i].height, 3, tmp, im3[i], pool3); }
     for (int i = 0; i < d->n_images1; i++) { if (int r = decode_image(d->images1[i], 1, tmp)) return r; build_mips(d->images1[i].width, d->images1[i].height, 1, tmp, im1[i], pool1); }
+    lap("decode + mips");
     if (int r = upload(c->img3, im3)) return r; if (int r = upload(c->img1, im1)) return r;
     if (int r = upload(c->texels3_d, pool3)) return r; if (int r = upload(c->texels1_d, pool1)) return r;
     { std::vector<float4> p4(pool3.size() / 3); for (size_t i = 0; i < p4.size(); i++) p4[i] = make_float4((float)pool3[3 * i], (float)pool3[3 * i + 1], (float)pool3[3 * i + 2], 0.f);
@@ -227,6 +241,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     for (int i = 0; i < d->n_lights; i++) for (int k = 0; k < 3; k++) li[3 * i + k] = d->lights[5 * i + 2 + k];
     if (int r = upload(c->light_d, li)) return r; if (int r = upload(c->light_f, to_f(li))) return r;
 
+    lap("texel upload");
     fill_scene_common(c->sc_d, d); fill_scene_common(c->sc_f, d);
     c->sc_d.eps = eps; c->sc_f.eps = (float)eps;
     c->sc_d.shapes = c->sc_f.shapes = c->shapes.as<DShape>();

@@ -121,12 +121,30 @@ GD_D int trace_pop(const ST &st, int &sp, float best) {
 template <int SORT = 0, int FMA = 0, typename ST>
 GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, ST &st, int &sp) {
     const float4 *n = bvh.nodes + 8 * (size_t)cur;
+    const float INF = __int_as_float(0x7f800000);
+    float dist[4]; int cid[4];
+    if (FMA == 2) {
+        // near/far planes picked by the sign of 1/d at load time (no min/max per axis), one FMA per plane
+        const int sx = __float_as_int(r.id[0]) < 0 ? 3 : 0, sy = __float_as_int(r.id[1]) < 0 ? 3 : 0, sz = __float_as_int(r.id[2]) < 0 ? 3 : 0;
+        float4 nx = __ldg(n + sx), ny = __ldg(n + 1 + sy), nz = __ldg(n + 2 + sz);
+        float4 fx = __ldg(n + 3 - sx), fy = __ldg(n + 4 - sy), fz = __ldg(n + 5 - sz);
+        int4 ch = __ldg((const int4 *)(n + 6));
+        cid[0] = ch.x; cid[1] = ch.y; cid[2] = ch.z; cid[3] = ch.w;
+        const float anx[4] = {nx.x, nx.y, nx.z, nx.w}, any[4] = {ny.x, ny.y, ny.z, ny.w}, anz[4] = {nz.x, nz.y, nz.z, nz.w};
+        const float afx[4] = {fx.x, fx.y, fx.z, fx.w}, afy[4] = {fy.x, fy.y, fy.z, fy.w}, afz[4] = {fz.x, fz.y, fz.z, fz.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            float tmn = fmaxf(fmaxf(fmaf(anx[k], r.id[0], -r.oid[0]), fmaf(any[k], r.id[1], -r.oid[1])), fmaxf(fmaf(anz[k], r.id[2], -r.oid[2]), r.tnear));
+            float tmx = fminf(fminf(fmaf(afx[k], r.id[0], -r.oid[0]), fmaf(afy[k], r.id[1], -r.oid[1])), fminf(fmaf(afz[k], r.id[2], -r.oid[2]), r.best));
+            tmx = fmaf(tmx, 1.0000005f, r.slack + r.slack);   // conservative: product rounding + the FMA form's cancellation error
+            dist[k] = (cid[k] != 0 && tmn <= tmx) ? tmn : INF;
+        }
+    } else {
     float4 lox = __ldg(n), loy = __ldg(n + 1), loz = __ldg(n + 2), hix = __ldg(n + 3), hiy = __ldg(n + 4), hiz = __ldg(n + 5);
     int4 ch = __ldg((const int4 *)(n + 6));
-    float dist[4]; int cid[4] = {ch.x, ch.y, ch.z, ch.w};
+    cid[0] = ch.x; cid[1] = ch.y; cid[2] = ch.z; cid[3] = ch.w;
     const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
     const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
-    const float INF = __int_as_float(0x7f800000);
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         float t0x, t1x, t0y, t1y, t0z, t1z;
@@ -144,6 +162,7 @@ GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, ST &st, int &sp
         tmx *= 1.0000005f;   // conservative slab (rounding of the three products)
         if (FMA) tmx += r.slack + r.slack;
         dist[k] = (cid[k] != 0 && tmn <= tmx) ? tmn : INF;
+    }
     }
 #define GD_CSWAP(i, j) if (dist[j] < dist[i]) { float td = dist[i]; dist[i] = dist[j]; dist[j] = td; int tc = cid[i]; cid[i] = cid[j]; cid[j] = tc; }
     if (SORT == 0) {   // sort the 4 candidates by distance (network), nearest first

@@ -19,8 +19,8 @@ constexpr int SORT_MIN_RAYS = 1 << 17;   // below this a launch is too small for
 
 template <bool EXACT, bool COUNT, int V>
 inline void launch_trace_v(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const int *order) {
-    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * (V >= 10000 ? trace_variant_blocks(V) : 16));
-    k_trace<EXACT, COUNT, V><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, order, n, c->counters.as<int>() + 8, COUNT ? c->trav_counters.as<unsigned long long>() : nullptr);
+    int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
+    k_trace<EXACT, COUNT, V><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, order, n, COUNT ? c->trav_counters.as<unsigned long long>() : nullptr);
 }
 
 template <bool EXACT>
@@ -30,7 +30,7 @@ inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const 
     else if constexpr (EXACT) launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
     else switch (c->trace_variant) {
 #define GD_V(v) case v: launch_trace_v<EXACT, false, v>(c, rays, hits, n, order); break;
-        GD_V(0) GD_V(200) GD_V(10) GD_V(1000) GD_V(10000) GD_V(20000) GD_V(30000) GD_V(11000) GD_V(21000)
+        GD_V(0) GD_V(10) GD_V(20) GD_V(1000)
 #undef GD_V
         default: launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
     }

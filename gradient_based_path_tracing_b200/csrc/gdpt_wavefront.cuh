@@ -188,7 +188,8 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 // lanes better than forced reconvergence does; DESIGN.md, "what was tried".)
 // Tunables V = SORT + 10*FMA + 100*STACKSEL + 1000*OCC (GDPT_TRACE_VARIANT for sweeps):
 //   SORT 0 children fully sorted by distance / 1 nearest first only
-//   FMA  0 (l-o)*id slabs / 1 fma(l, id, -o*id) with an absolute slack
+//   FMA  0 (l-o)*id slabs / 1 fma(l, id, -o*id) with an absolute slack / 2 the same with near/far planes
+//        selected by the ray octant at load time (6 instead of 12 min/max per child)
 //   STACKSEL 0: 20, 1: 16, 2: 12, 3: 8 shared-memory stack entries per thread (rest spills)
 //   OCC  0: launch bound 8 blocks/SM (64 regs), 1: 7 (72), 2: 9 (56), 3: 10 (48)
 // COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
@@ -198,75 +199,27 @@ constexpr int trace_variant_blocks(int v) { return ((v / 1000) % 10) == 0 ? 8 : 
 
 template <bool EXACT, bool COUNT, int V>
 __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(DBvh bvh, const RayF *rays, Hit *hits, const int *order, int count_max,
-                                                                               int *cursors, unsigned long long *counters) {
-    constexpr int SORT = V % 10, FMA = (V / 10) % 10, DEPTH = trace_variant_depth(V), LOOP = V / 10000;
+                                                                               unsigned long long *counters) {
+    constexpr int SORT = V % 10, FMA = (V / 10) % 10, DEPTH = trace_variant_depth(V);
     __shared__ int2 stack[DEPTH * TRACE_BLOCK];
     const int n = count_max;
     TraceStackT<DEPTH> st; st.smem = stack;
     unsigned long long tn = 0, tp = 0;
-    if (LOOP == 0) {
-        for (int j = blockIdx.x * TRACE_BLOCK + threadIdx.x; j < n; j += gridDim.x * TRACE_BLOCK) {
-            const int i = order ? __ldg(order + j) : j;   // sorted launch: follow the permutation, rays stay where they are
-            const float4 *rp = (const float4 *)(rays + i);
-            float4 a = __ldg(rp), b = __ldg(rp + 1);
-            RayState r; r.init(a, b);
-            unsigned cn = 0, cp = 0;
-            if (!(b.w < a.w) && bvh.n_nodes != 0) {   // tfar < tnear: never hits
-                int sp = 0, cur = 0;
-                while (cur != TRACE_DONE) {
-                    if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA>(bvh, cur, r, st, sp); }
-                    else cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
-                }
-            }
-            hits[i] = r.hit;
-            if (COUNT) { tn += cn; tp += cp; }
-        }
-    } else {
-        // Experimental: persistent warps, dynamic ray fetch, node steps in lockstep, leaves postponed until
-        // LEAF_MIN lanes hold one (or no lane holds a node).  cursors[0] = next slice, cursors[1] = retired warps.
-        constexpr int LEAF_MIN = LOOP == 1 ? 8 : LOOP == 2 ? 16 : 24;
-        const unsigned FULL = 0xffffffffu;
-        const int lane = threadIdx.x & 31;
-        RayState r;
-        int ray = -1, cur = TRACE_DONE, sp = 0;
-        int wcur = 0, wend = 0;
-        bool exhausted = false;
+    for (int j = blockIdx.x * TRACE_BLOCK + threadIdx.x; j < n; j += gridDim.x * TRACE_BLOCK) {
+        const int i = order ? __ldg(order + j) : j;   // sorted launch: follow the permutation, rays stay where they are
+        const float4 *rp = (const float4 *)(rays + i);
+        float4 a = __ldg(rp), b = __ldg(rp + 1);
+        RayState r; r.init(a, b);
         unsigned cn = 0, cp = 0;
-        while (true) {
-            const bool need = cur == TRACE_DONE;
-            if (need && ray >= 0) { hits[ray] = r.hit; ray = -1; if (COUNT) { tn += cn; tp += cp; cn = cp = 0; } }
-            const unsigned m = __ballot_sync(FULL, need);
-            if (m && !exhausted) {
-                if (wcur >= wend) {
-                    if (lane == 0) wcur = atomicAdd(cursors, 256);
-                    wcur = __shfl_sync(FULL, wcur, 0);
-                    wend = min(wcur + 256, n);
-                    if (wcur >= n) { exhausted = true; wcur = wend = 0; }
-                }
-                const int idx = wcur + __popc(m & ((1u << lane) - 1u));
-                if (need && idx < wend) {
-                    ray = order ? __ldg(order + idx) : idx;
-                    const float4 *rp = (const float4 *)(rays + ray);
-                    float4 a = __ldg(rp), b = __ldg(rp + 1);
-                    r.init(a, b);
-                    sp = 0;
-                    cur = (b.w < a.w || bvh.n_nodes == 0) ? TRACE_DONE : 0;
-                }
-                wcur = min(wend, wcur + __popc(m));
-            }
-            if (exhausted && __all_sync(FULL, cur == TRACE_DONE && ray < 0)) break;
-            if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA>(bvh, cur, r, st, sp); }
-            const bool leaf = cur < 0 && cur != TRACE_DONE;
-            const unsigned ml = __ballot_sync(FULL, leaf), mn = __ballot_sync(FULL, cur >= 0);
-            if (__popc(ml) >= LEAF_MIN || (ml && !mn)) {
-                if (leaf) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
+        if (!(b.w < a.w) && bvh.n_nodes != 0) {   // tfar < tnear: never hits
+            int sp = 0, cur = 0;
+            while (cur != TRACE_DONE) {
+                if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA>(bvh, cur, r, st, sp); }
+                else cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
             }
         }
-        if (lane == 0) {
-            const int warps = gridDim.x * (TRACE_BLOCK / 32);
-            __threadfence();
-            if (atomicAdd(cursors + 1, 1) == warps - 1) { cursors[0] = 0; cursors[1] = 0; __threadfence(); }
-        }
+        hits[i] = r.hit;
+        if (COUNT) { tn += cn; tp += cp; }
     }
     if (COUNT) {
         for (int s = 16; s > 0; s >>= 1) { tn += __shfl_down_sync(0xffffffffu, tn, s); tp += __shfl_down_sync(0xffffffffu, tp, s); }
