@@ -79,6 +79,7 @@ struct gdpt_ctx {
     float box_lo[3] = {0, 0, 0}, box_hi[3] = {0, 0, 0};   // float scene box (BVH root)
     gdpt::DevBuf sort_keys, sort_order, sort_hist;
     int tail_paths = 1 << 16;         // finish a wave in one launch once this few paths are alive (GDPT_TAIL_PATHS)
+    int shade_variant = 0;            // tuning knob (GDPT_SHADE_VARIANT): launch bounds of the diffuse-only float shade kernels
     int trace_variant = -1;           // tuning knob (GDPT_TRACE_VARIANT); -1 = the default kernel
     bool lambertian_only = false;     // every material is a Lambertian -> specialised shade kernels
     bool count_traversal = false;     // bench-only: count nodes/primitives per ray
@@ -212,6 +213,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     if (const char *tv = getenv("GDPT_TRACE_VARIANT")) c->trace_variant = atoi(tv);
     if (const char *sv = getenv("GDPT_SORT_RAYS")) c->sort_rays = atoi(sv) != 0;
     if (const char *tp = getenv("GDPT_TAIL_PATHS")) c->tail_paths = atoi(tp);
+    if (const char *sv = getenv("GDPT_SHADE_VARIANT")) c->shade_variant = atoi(sv);
     c->lambertian_only = !mats.empty();
     for (const DMaterial &m : mats) if (m.type != MAT_LAMBERTIAN) c->lambertian_only = false;
     if (int r = upload(c->materials, mats)) return r;

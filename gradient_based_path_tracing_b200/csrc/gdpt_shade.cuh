@@ -74,8 +74,8 @@ GD_D bool start_iteration(const DScene<R> &sc, const Vertex<R> &vtx, const V3<R>
 }
 
 // ---------------------------------------------------------------- primary stage
-template <typename R, int MS>
-__global__ void __launch_bounds__(128) k_primary(DScene<R> sc, WaveParams wp, const GenRec<R> *gen, const Hit *hits,
+template <typename R, int MS, int MINB = 1>
+__global__ void __launch_bounds__(128, MINB) k_primary(DScene<R> sc, WaveParams wp, const GenRec<R> *gen, const Hit *hits,
                                                  PathRec<R> *out, OffRec<R> *off_out, RayF *rays_out, int *out_count) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     bool alive = false;
@@ -175,8 +175,8 @@ GD_D bool bounce_step(const DScene<R> &sc, const WaveParams &wp, PathRec<R> &pr,
     return start_iteration<R, MS>(sc, nv, dir_view, pr, ray);
 }
 
-template <typename R, int MS>
-__global__ void __launch_bounds__(128) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
+template <typename R, int MS, int MINB = 1>
+__global__ void __launch_bounds__(128, MINB) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
                                                 const Hit *hits, const int *in_count, int in_max,
                                                 PathRec<R> *out, RayF *rays_out, int *out_count) {
     int n = min(*in_count, in_max);

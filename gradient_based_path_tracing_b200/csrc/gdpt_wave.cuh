@@ -77,7 +77,17 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     launch_trace<ModeSel<R>::exact>(c, rays, hits, 5 * N);
     GD_CUDA(cudaEventRecord(e1, st));
     if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)SORT_BINS * sizeof(int), st));
-    k_primary<R, MS><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, hits, cur, off, rays, cnt);
+    {
+        auto args = [&](auto kern) { kern<<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, hits, cur, off, rays, cnt); };
+        if constexpr (MS == MS_LAMBERTIAN && sizeof(R) == 4) {   // occupancy variants of the diffuse-only float kernels (GDPT_SHADE_VARIANT)
+            switch (c->shade_variant / 10) {
+                case 1: args(k_primary<R, MS, 5>); break;
+                case 2: args(k_primary<R, MS, 6>); break;
+                case 3: args(k_primary<R, MS, 8>); break;
+                default: args(k_primary<R, MS, 1>);
+            }
+        } else args(k_primary<R, MS, 1>);
+    }
     c->stats.kernel_launches++;
     GD_CUDA(cudaEventRecord(e2, st));
     GD_CUDA(cudaMemcpyAsync(c->h_counts, cnt, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -110,7 +120,17 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
         if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)SORT_BINS * sizeof(int), st));
         int *cin = cnt + which, *cout = cnt + (which ^ 1);
         GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
-        k_bounce<R, MS><<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout);
+        {
+            auto args = [&](auto kern) { kern<<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout); };
+            if constexpr (MS == MS_LAMBERTIAN && sizeof(R) == 4) {
+                switch (c->shade_variant % 10) {
+                    case 1: args(k_bounce<R, MS, 5>); break;
+                    case 2: args(k_bounce<R, MS, 6>); break;
+                    case 3: args(k_bounce<R, MS, 8>); break;
+                    default: args(k_bounce<R, MS, 1>);
+                }
+            } else args(k_bounce<R, MS, 1>);
+        }
         c->stats.kernel_launches++; c->stats.bounce_iterations++;
         GD_CUDA(cudaEventRecord(e2, st));
         GD_CUDA(cudaMemcpyAsync(c->h_counts, cout, sizeof(int), cudaMemcpyDeviceToHost, st));
