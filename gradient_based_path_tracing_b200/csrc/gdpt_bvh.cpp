@@ -5,8 +5,11 @@
 #include "gdpt_bvh.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
+#include <thread>
+#include <utility>
 #include <limits>
 
 namespace gdpt {
@@ -28,11 +31,13 @@ struct BNode { Box b; int left = -1, right = -1, first = 0, count = 0; };
 
 struct Builder {
     std::vector<Ref> refs;
-    std::vector<BNode> nodes;
+    std::vector<BNode> nodes;          // preallocated (2n); slots handed out by `next` so subtrees can be built concurrently
+    std::atomic<int> next{0};
     double ci = 1.0;      // SAH cost of one primitive test relative to one (binary) node step
     int max_leaf = 4;     // <= 7 (3-bit count in the leaf encoding)
+    int fork_levels = 0;  // subtrees down to this depth are built on their own threads
 
-    int build(int first, int count) {
+    int build(int first, int count, int depth = 0) {
         BNode n; n.b.reset();
         Box cb; cb.reset();
         for (int i = first; i < first + count; i++) {
@@ -40,8 +45,8 @@ struct Builder {
             for (int k = 0; k < 3; k++) { cb.lo[k] = std::min(cb.lo[k], refs[i].c[k]); cb.hi[k] = std::max(cb.hi[k], refs[i].c[k]); }
         }
         n.first = first; n.count = count;
-        int id = (int)nodes.size();
-        nodes.push_back(n);
+        int id = next.fetch_add(1);
+        nodes[id] = n;
         if (count <= 1) return id;
         const int NB = 16;
         double best = std::numeric_limits<double>::infinity(); int bax = -1, bbin = -1;
@@ -80,8 +85,15 @@ struct Builder {
             mid = (int)(it - refs.begin());
             if (mid == first || mid == first + count) mid = first + count / 2;
         }
-        int l = build(first, mid - first);
-        int r = build(mid, first + count - mid);
+        int l, r;
+        if (depth < fork_levels && count > 8192) {   // disjoint reference ranges, disjoint node slots: no sharing between the two halves
+            std::thread th([&] { l = build(first, mid - first, depth + 1); });
+            r = build(mid, first + count - mid, depth + 1);
+            th.join();
+        } else {
+            l = build(first, mid - first, depth + 1);
+            r = build(mid, first + count - mid, depth + 1);
+        }
         nodes[id].left = l; nodes[id].right = r; nodes[id].count = 0;
         return id;
     }
@@ -230,7 +242,8 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
     double split_budget = 2.0;      // extra references allowed, as a fraction of the primitive count (B200 sweep: profiles/r1_bvh_sweep.txt)
     if (const char *e = getenv("GDPT_BVH_SPLIT")) split_budget = atof(e);
     if (split_budget > 0.0) presplit(B.refs, src, (size_t)((1.0 + split_budget) * B.refs.size()));
-    B.nodes.reserve(2 * B.refs.size());
+    B.nodes.resize(2 * B.refs.size());
+    { unsigned hc = std::max(1u, std::thread::hardware_concurrency()); while ((1u << (B.fork_levels + 1)) <= std::min(16u, hc)) B.fork_levels++; }
     B.build(0, (int)B.refs.size());
     out.prims.resize(B.refs.size());
     for (size_t i = 0; i < B.refs.size(); i++) out.prims[i] = src[B.refs[i].idx];

@@ -3,6 +3,8 @@
 #pragma once
 #include <cstdlib>
 #include <chrono>
+#include <atomic>
+#include <thread>
 #include <cstdio>
 #include <cstdarg>
 #include <cstdio>
@@ -171,27 +173,10 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         for (int k = 0; k < 4; k++) h.sphere[k] = d->spheres[4 * i + k];
         if (h.kind == 1) for (int t = 0; t < 3 * h.ntris; t++) if (h.indices[t] < 0 || h.indices[t] >= h.nverts) return fail(GDPT_ERR_ARG, "shape %d: vertex index out of range", i);
     }
-    Bvh bvh; build_bvh(hs, bvh);
-    lap("bvh build");
-    if (3 * bvh.max_depth + 1 > STACK_TOTAL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
-    c->bvh_depth = bvh.max_depth;
-    for (int k = 0; k < 3; k++) { c->box_lo[k] = bvh.lo[k]; c->box_hi[k] = bvh.hi[k]; }
-    if (int r = upload(c->shapes, shapes)) return r;
-    { std::vector<double> sp(d->spheres, d->spheres + 4 * (size_t)d->n_shapes); if (int r = upload(c->spheres, sp)) return r; }
-    if (int r = upload(c->bvh_nodes, bvh.nodes)) return r;
-    if (int r = upload(c->bvh_prims, bvh.prims)) return r;
-    c->bvh.nodes = c->bvh_nodes.as<float4>(); c->bvh.prims = c->bvh_prims.as<float4>(); c->bvh.spheres = c->spheres.as<double>();
-    c->bvh.n_nodes = bvh.prims.empty() ? 0 : (int)bvh.nodes.size(); c->bvh.n_prims = (int)bvh.prims.size();
-    // bounds sphere (scene.cpp:30-34): float box from the "Embree" scene, arithmetic in double
-    {
-        double lb[3] = {bvh.lo[0], bvh.lo[1], bvh.lo[2]}, ub[3] = {bvh.hi[0], bvh.hi[1], bvh.hi[2]};
-        double dx = ub[0] - lb[0], dy = ub[1] - lb[1], dz = ub[2] - lb[2];
-        c->bounds[0] = sqrt(dx * dx + dy * dy + dz * dz) / 2;
-        for (int k = 0; k < 3; k++) c->bounds[1 + k] = (lb[k] + ub[k]) / 2.0;
-    }
-    double eps = std::min(c->bounds[0] * 1e-5, 0.01);   // scene.h:104-106
-
-    lap("bvh upload");
+    // the BVH is built on its own host thread(s) while this one decodes textures and uploads the pools
+    Bvh bvh;
+    std::thread bvh_thread([&] { build_bvh(hs, bvh); });
+    struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } bvh_joiner{bvh_thread};
     // ---- geometry pools
     std::vector<double> pos(d->positions, d->positions + 3 * (size_t)d->n_positions), nrm(d->normals, d->normals + 3 * (size_t)d->n_normals),
         uv(d->uvs, d->uvs + 2 * (size_t)d->n_uvs);
@@ -231,9 +216,37 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     }
     if (int r = upload(c->tex_d, td)) return r; if (int r = upload(c->tex_f, tf)) return r;
     std::vector<DImage> im3(d->n_images3), im1(d->n_images1);
-    std::vector<double> pool3, pool1, tmp;
-    for (int i = 0; i < d->n_images3; i++) { if (int r = decode_image(d->images3[i], 3, tmp)) return r; build_mips(d->images3[i].width, d->images3[i].height, 3, tmp, im3[i], pool3); }
-    for (int i = 0; i < d->n_images1; i++) { if (int r = decode_image(d->images1[i], 1, tmp)) return r; build_mips(d->images1[i].width, d->images1[i].height, 1, tmp, im1[i], pool1); }
+    std::vector<double> pool3, pool1;
+    {   // one task per image: decode + mip chain into a private pool, then splice the pools in image order
+        const int n3 = d->n_images3, n1 = d->n_images1, nimg = n3 + n1;
+        std::vector<std::vector<double>> local(nimg);
+        std::vector<int> rc(nimg, 0);
+        std::atomic<int> cursor{0};
+        auto task = [&] {
+            std::vector<double> t;
+            for (;;) {
+                int i = cursor.fetch_add(1);
+                if (i >= nimg) break;
+                const gdpt_image &gi = i < n3 ? d->images3[i] : d->images1[i - n3];
+                const int C = i < n3 ? 3 : 1;
+                rc[i] = decode_image(gi, C, t);
+                if (!rc[i]) build_mips(gi.width, gi.height, C, t, i < n3 ? im3[i] : im1[i - n3], local[i]);
+            }
+        };
+        unsigned nt = std::max(1u, std::min({8u, std::thread::hardware_concurrency(), (unsigned)std::max(nimg, 1)}));
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < nt; t++) pool.emplace_back(task);
+        task();
+        for (auto &t : pool) t.join();
+        for (int i = 0; i < nimg; i++) if (rc[i]) return rc[i];
+        for (int i = 0; i < nimg; i++) {
+            std::vector<double> &dst = i < n3 ? pool3 : pool1;
+            DImage &im = i < n3 ? im3[i] : im1[i - n3];
+            const long long base = (long long)(dst.size() / (i < n3 ? 3 : 1));
+            for (int l = 0; l < im.n_levels; l++) im.off[l] += base;
+            dst.insert(dst.end(), local[i].begin(), local[i].end());
+        }
+    }
     lap("decode + mips");
     if (int r = upload(c->img3, im3)) return r; if (int r = upload(c->img1, im1)) return r;
     if (int r = upload(c->texels3_d, pool3)) return r; if (int r = upload(c->texels1_d, pool1)) return r;
@@ -244,6 +257,27 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     if (int r = upload(c->light_d, li)) return r; if (int r = upload(c->light_f, to_f(li))) return r;
 
     lap("texel upload");
+    bvh_thread.join();
+    lap("bvh build (rest)");
+    if (3 * bvh.max_depth + 1 > STACK_TOTAL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
+    c->bvh_depth = bvh.max_depth;
+    for (int k = 0; k < 3; k++) { c->box_lo[k] = bvh.lo[k]; c->box_hi[k] = bvh.hi[k]; }
+    if (int r = upload(c->shapes, shapes)) return r;
+    { std::vector<double> sp(d->spheres, d->spheres + 4 * (size_t)d->n_shapes); if (int r = upload(c->spheres, sp)) return r; }
+    if (int r = upload(c->bvh_nodes, bvh.nodes)) return r;
+    if (int r = upload(c->bvh_prims, bvh.prims)) return r;
+    c->bvh.nodes = c->bvh_nodes.as<float4>(); c->bvh.prims = c->bvh_prims.as<float4>(); c->bvh.spheres = c->spheres.as<double>();
+    c->bvh.n_nodes = bvh.prims.empty() ? 0 : (int)bvh.nodes.size(); c->bvh.n_prims = (int)bvh.prims.size();
+    // bounds sphere (scene.cpp:30-34): float box from the "Embree" scene, arithmetic in double
+    {
+        double lb[3] = {bvh.lo[0], bvh.lo[1], bvh.lo[2]}, ub[3] = {bvh.hi[0], bvh.hi[1], bvh.hi[2]};
+        double dx = ub[0] - lb[0], dy = ub[1] - lb[1], dz = ub[2] - lb[2];
+        c->bounds[0] = sqrt(dx * dx + dy * dy + dz * dz) / 2;
+        for (int k = 0; k < 3; k++) c->bounds[1 + k] = (lb[k] + ub[k]) / 2.0;
+    }
+    double eps = std::min(c->bounds[0] * 1e-5, 0.01);   // scene.h:104-106
+
+    lap("bvh upload");
     fill_scene_common(c->sc_d, d); fill_scene_common(c->sc_f, d);
     c->sc_d.eps = eps; c->sc_f.eps = (float)eps;
     c->sc_d.shapes = c->sc_f.shapes = c->shapes.as<DShape>();
