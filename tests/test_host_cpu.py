@@ -100,3 +100,48 @@ def test_row_band_partition(g):
             sizes = [b1 - b0 for b0, b1 in bands if b1 > b0]
             if h >= 4 * n:
                 assert max(sizes) - min(sizes) <= 4 + h % 4
+
+
+# ------------------------------------------------------------------ host BVH builder (product code, CPU-only part)
+def _bvh_check(tmp_path, scene_name, env=None):
+    import json
+    import subprocess
+    import gradient_based_path_tracing_b200 as g
+    exe = tmp_path / "bvh_check"
+    if not exe.exists():
+        csrc = os.path.join(ROOT, "gradient_based_path_tracing_b200", "csrc")
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", csrc, os.path.join(ROOT, "tests", "host", "bvh_check.cpp"),
+                               os.path.join(csrc, "gdpt_bvh.cpp"), "-o", str(exe), "-lpthread"])
+    a = g.Scene.named(scene_name).a
+    files = []
+    for key, dt in (("shapes", np.int32), ("shape_offsets", np.int64), ("spheres", np.float64), ("positions", np.float64), ("indices", np.int32)):
+        f = tmp_path / (scene_name + "." + key + ".bin")
+        np.ascontiguousarray(a[key], dtype=dt).tofile(f)
+        files.append(str(f))
+    e = dict(os.environ)
+    e.update(env or {})
+    return json.loads(subprocess.check_output([str(exe)] + files, env=e, timeout=300)), a
+
+
+@pytest.mark.parametrize("scene_name", ["cbox_gdpt", "veach_mi_gradpath", "sponza_1080p"])
+def test_bvh_builder_invariants(tmp_path, scene_name):
+    """Every primitive reachable, leaf ranges valid, depth within the traversal stack, bounds = float min/max of the geometry
+    (what rtcGetSceneBounds reports), two builds identical (the parallel subtree build must stay deterministic)."""
+    r, a = _bvh_check(tmp_path, scene_name)
+    assert r["bad_range"] == 0 and r["bad_child"] == 0 and r["unvisited"] == 0 and r["uncovered"] == 0
+    assert r["distinct_prims"] == r["scene_prims"]
+    assert r["prim_records"] >= r["scene_prims"] and r["max_leaf"] <= 7
+    assert r["depth"] == r["reported_depth"] and 3 * r["depth"] + 1 <= 64
+    assert r["deterministic"] is True
+    tri = a["shapes"][:, 0] == 1
+    if tri.all():
+        p = np.asarray(a["positions"], dtype=np.float64).astype(np.float32)
+        assert np.array_equal(np.float32(r["lo"]), p.min(axis=0)) and np.array_equal(np.float32(r["hi"]), p.max(axis=0))
+
+
+def test_bvh_presplit_only_adds_references(tmp_path):
+    r0, _ = _bvh_check(tmp_path, "sponza_1080p", {"GDPT_BVH_SPLIT": "0"})
+    r2, _ = _bvh_check(tmp_path, "sponza_1080p", {"GDPT_BVH_SPLIT": "2"})
+    assert r0["prim_records"] == r0["scene_prims"] == r2["scene_prims"] == r2["distinct_prims"]
+    assert r0["scene_prims"] < r2["prim_records"] <= 3 * r0["scene_prims"] + 1
+    assert r0["lo"] == r2["lo"] and r0["hi"] == r2["hi"]
