@@ -29,3 +29,10 @@ fi
 for p in "${pids[@]:-}"; do [ -n "$p" ] && wait "$p"; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT" "${OBJS[@]}" -lcudart
 echo "built $OUT"
+# the C++ host over the C ABI: lajolla_b200 (container reader, flattening, PFM writers)
+CLI="$HERE/../lajolla_b200"
+if [ ! -f "$CLI" ] || [ "$OUT" -nt "$CLI" ] || [ -n "$(find "$HERE/host" -newer "$CLI" -type f | head -1)" ]; then
+  g++ -O2 -std=c++17 -I "$HERE/../../include" "$HERE/host/lajolla_b200.cpp" "$HERE/host/gdpt_container.cpp" -o "$CLI" \
+      -L "$HERE/.." -lgdpt -lz -Wl,-rpath,'$ORIGIN'
+  echo "built $CLI"
+fi

@@ -145,3 +145,66 @@ def test_bvh_presplit_only_adds_references(tmp_path):
     assert r0["prim_records"] == r0["scene_prims"] == r2["scene_prims"] == r2["distinct_prims"]
     assert r0["scene_prims"] < r2["prim_records"] <= 3 * r0["scene_prims"] + 1
     assert r0["lo"] == r2["lo"] and r0["hi"] == r2["hi"]
+
+
+# ------------------------------------------------------------------ C++ host (lajolla_b200): container reader + flattening
+def _fnv(buf, h=1469598103934665603):
+    # same 64-bit FNV-1a as lajolla_b200 -describe (vectorised per byte would be slow in Python: hash via numpy loop-free trick is
+    # not possible for FNV, so hash a strided sample of large arrays the same way on both sides is not an option either) -> plain loop on bytes
+    for b in bytes(buf):
+        h = ((h ^ b) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+@pytest.mark.parametrize("name,overlay", [("cbox_gdpt_64", None), ("veach_mi_small", None), ("disney_small", "disney_gradpath")])
+def test_cpp_host_flattens_scenes_like_the_python_host(name, overlay):
+    """lajolla_b200 (C++ host over the C ABI) must hand gdpt_create the same scene as scene.py does."""
+    import json
+    import subprocess
+    import gradient_based_path_tracing_b200 as g
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "lajolla_b200")
+    if not os.path.exists(exe):
+        pytest.skip("lajolla_b200 not built")
+    sdir = os.path.join(ROOT, "scenes")
+    if overlay:
+        cmd = [exe, "-describe", "-overlay", os.path.join(sdir, name + ".camera.gdpt"), os.path.join(sdir, overlay + ".gdpt.z")]
+    else:
+        cmd = [exe, "-describe", os.path.join(sdir, name + ".gdpt.z")]
+    got = json.loads(subprocess.check_output(cmd, timeout=120).decode().strip().splitlines()[-1])
+    sc = g.Scene.named(name)
+    d = sc.desc()
+    for k, v in (("width", d.width), ("height", d.height), ("filter_kind", d.filter_kind), ("filter_param", d.filter_param),
+                 ("spp", d.samples_per_pixel), ("max_depth", d.max_depth), ("rr_depth", d.rr_depth), ("integrator", int(sc.options.integrator)),
+                 ("n_shapes", d.n_shapes), ("n_positions", d.n_positions), ("n_triangles", d.n_triangles), ("n_normals", d.n_normals),
+                 ("n_uvs", d.n_uvs), ("n_materials", d.n_materials), ("n_textures", d.n_textures), ("n_images3", d.n_images3),
+                 ("n_images1", d.n_images1), ("n_lights", d.n_lights)):
+        assert got[k] == v, k
+    a = sc.a
+    f8 = lambda k: np.ascontiguousarray(a[k], dtype=np.float64)
+    assert got["h_camera"] == _fnv(f8("camera.cam_to_world"), _fnv(f8("camera.sample_to_cam")))
+    assert got["h_shapes"] == _fnv(np.ascontiguousarray(a["shapes"], dtype=np.int32))
+    assert got["h_offsets"] == _fnv(np.ascontiguousarray(a["shape_offsets"], dtype=np.int64))
+    assert got["h_spheres"] == _fnv(f8("spheres"))
+    assert got["h_positions"] == _fnv(f8("positions"))
+    assert got["h_indices"] == _fnv(np.ascontiguousarray(a["indices"], dtype=np.int32))
+    assert got["h_materials"] == _fnv(f8("materials")) and got["h_textures"] == _fnv(f8("textures")) and got["h_lights"] == _fnv(f8("lights"))
+    himg = 1469598103934665603
+    for prefix in ("img3", "img1"):
+        for i in range(sc.n_images(prefix)):
+            base = "%s.%d" % (prefix, i)
+            px = f8(base + ".data") if base + ".data" in a else f8(base + ".palette")[np.asarray(a[base + ".index"])]
+            himg = _fnv(np.ascontiguousarray(px, dtype=np.float64), himg)
+    assert got["h_images"] == himg
+
+
+def test_cpp_host_rejects_bad_input(tmp_path):
+    import subprocess
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "lajolla_b200")
+    if not os.path.exists(exe):
+        pytest.skip("lajolla_b200 not built")
+    bad = tmp_path / "bad.gdpt"
+    bad.write_bytes(b"not a container")
+    r = subprocess.run([exe, "-describe", str(bad)], capture_output=True, timeout=60)
+    assert r.returncode == 1 and b"not a GDPT1 container" in r.stderr
+    r = subprocess.run([exe, "-describe", str(tmp_path / "missing.gdpt")], capture_output=True, timeout=60)
+    assert r.returncode == 1 and b"cannot open" in r.stderr

@@ -291,3 +291,32 @@ def test_full_size_sponza_smoke_and_energy(g, scenes):
     dc_p = (r.primal * m[..., None]).sum(axis=(0, 1))
     dc_o = (r.poisson * m[..., None]).sum(axis=(0, 1))
     assert np.allclose(dc_p, dc_o, rtol=1e-6, atol=1e-6)
+
+
+# ------------------------------------------------------------------ the C++ host over the same C ABI
+def _read_pfm(path):
+    with open(path, "rb") as f:
+        assert f.readline().strip() == b"PF"
+        w, h = (int(v) for v in f.readline().split())
+        assert f.readline().strip() == b"-1"          # little-endian; rows top-down exactly as lajolla's imwrite leaves them
+        return np.frombuffer(f.read(), dtype="<f4").reshape(h, w, 3)
+
+
+def test_cpp_host_cli_writes_the_same_images(g, scenes, tmp_path):
+    """lajolla_b200 scene -o out.pfm == render(scene) of the Python host: Poisson image in the -o file (what ./lajolla writes),
+    primal/dx/dy beside it, float32 PFM (src/image.cpp:135-150), and the reference's console lines (src/main.cpp:36-46)."""
+    import os
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "lajolla_b200")
+    out = tmp_path / "cb.pfm"
+    r = subprocess.run([exe, "-o", str(out), "-spp", "2", "-precision", "f64", os.path.join(ROOT, "scenes", "cbox_gdpt_64.gdpt.z")],
+                       capture_output=True, timeout=600)
+    assert r.returncode == 0, r.stderr.decode()
+    text = r.stdout.decode()
+    for line in ("Parsing and constructing scene", "Rendering...", "Done. Took", "Image written to " + str(out)):
+        assert line in text
+    want = g.gradient_path_render(scenes("cbox_gdpt_64"), spp=2, precision="f64")
+    for suffix, img in (("", want.poisson), ("_primal", want.primal), ("_dx", want.dx), ("_dy", want.dy)):
+        got = _read_pfm(str(out)[:-4] + suffix + ".pfm")
+        assert np.allclose(got, img.astype(np.float32), rtol=1e-6, atol=1e-9), suffix
