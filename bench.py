@@ -280,7 +280,7 @@ def run_native(args):
                         "exceed 1; the binding limits are issue rate and L1/L2 latency under divergence (`issue`, DESIGN.md 4.1)",
                 "share_of_step": {"k_trace": ms_trace / (ms_step * args.steps), "shade_kernels": ms_shade / (ms_step * args.steps)},
                 "mrays_per_s": rays / (ms_trace * 1e-3) / 1e6 if ms_trace > 0 else None}
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        line = {"metric": METRIC if (w, h) == (1920, 1080) else METRIC.replace("1920x1080", "%dx%d" % (w, h)), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": args.precision, "data": "synthetic",
                 "config": {"workload": "%s gradpath %dx%d %d spp, reference offset semantics, image split into %d row band(s)" % (args.scene, w, h, spp, world),

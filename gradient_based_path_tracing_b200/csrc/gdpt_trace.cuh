@@ -40,7 +40,7 @@ struct TraceStackT {
 };
 using TraceStack = TraceStackT<STACK_SMEM>;
 
-template <bool EXACT>
+template <bool EXACT, bool FLAT = false>
 GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3], float tnear, float &best, Hit &hit) {
     float4 a = __ldg(bvh.prims + 3 * pi), b = __ldg(bvh.prims + 3 * pi + 1), c = __ldg(bvh.prims + 3 * pi + 2);
     int prim_id = __float_as_int(a.w), shape_id = __float_as_int(b.w), kind = __float_as_int(c.w);
@@ -50,7 +50,23 @@ GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3],
         return;
     }
     float t, u, v;
-    if (EXACT) {
+    if (!EXACT && FLAT) {
+        // same arithmetic as below without the early exits: one predicate at the end (a zero or NaN determinant
+        // turns u, v, t into inf/NaN and fails the comparisons), so a leaf costs one straight run of instructions
+        float e1x = b.x - a.x, e1y = b.y - a.y, e1z = b.z - a.z;
+        float e2x = c.x - a.x, e2y = c.y - a.y, e2z = c.z - a.z;
+        float px = d[1] * e2z - d[2] * e2y, py = d[2] * e2x - d[0] * e2z, pz = d[0] * e2y - d[1] * e2x;
+        float det = e1x * px + e1y * py + e1z * pz;
+        float inv = 1.0f / det;
+        float sx = o[0] - a.x, sy = o[1] - a.y, sz = o[2] - a.z;
+        u = (sx * px + sy * py + sz * pz) * inv;
+        float qx = sy * e1z - sz * e1y, qy = sz * e1x - sx * e1z, qz = sx * e1y - sy * e1x;
+        v = (d[0] * qx + d[1] * qy + d[2] * qz) * inv;
+        t = (e2x * qx + e2y * qy + e2z * qz) * inv;
+        bool ok = det != 0.f && u >= 0.f && u <= 1.f && v >= 0.f && u + v <= 1.f && t > tnear && t <= best;
+        ok = ok && !(t == best && hit.shape_id >= 0 && !(shape_id < hit.shape_id || (shape_id == hit.shape_id && prim_id < hit.prim_id)));
+        if (!ok) return;
+    } else if (EXACT) {
         double e1x = (double)b.x - a.x, e1y = (double)b.y - a.y, e1z = (double)b.z - a.z;
         double e2x = (double)c.x - a.x, e2y = (double)c.y - a.y, e2z = (double)c.z - a.z;
         double dx = d[0], dy = d[1], dz = d[2];
@@ -179,12 +195,12 @@ GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, ST &st, int &sp
 }
 
 // Leaf (cur < 0, != TRACE_DONE): test its primitives, then pop.
-template <bool EXACT, typename ST>
+template <bool EXACT, bool FLAT = false, typename ST>
 GD_D int trace_leaf(const DBvh &bvh, int cur, RayState &r, const ST &st, int &sp, unsigned *n_prims) {
     int enc = ~cur;
     int first = enc >> 3, cnt = enc & 7;
     if (n_prims) *n_prims += cnt;
-    for (int i = 0; i < cnt; i++) test_prim<EXACT>(bvh, first + i, r.o, r.d, r.tnear, r.best, r.hit);
+    for (int i = 0; i < cnt; i++) test_prim<EXACT, FLAT>(bvh, first + i, r.o, r.d, r.tnear, r.best, r.hit);
     return trace_pop(st, sp, r.best);
 }
 

@@ -30,7 +30,7 @@ inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const 
     else if constexpr (EXACT) launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
     else switch (c->trace_variant) {
 #define GD_V(v) case v: launch_trace_v<EXACT, false, v>(c, rays, hits, n, order); break;
-        GD_V(0) GD_V(10) GD_V(20) GD_V(1000)
+        GD_V(0) GD_V(10000) GD_V(20000) GD_V(30000)
 #undef GD_V
         default: launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
     }

@@ -192,6 +192,7 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 //        selected by the ray octant at load time (6 instead of 12 min/max per child)
 //   STACKSEL 0: 20, 1: 16, 2: 12, 3: 8 shared-memory stack entries per thread (rest spills)
 //   OCC  0: launch bound 8 blocks/SM (64 regs), 1: 7 (72), 2: 9 (56), 3: 10 (48)
+//   LOOP (x10000) bit 0: a node step that lands on a leaf tests it in the same trip; bit 1: triangle test without early exits
 // COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
 // (bench.py derives the algorithmic bytes per ray from them; never in timed runs).
 constexpr int trace_variant_depth(int v) { return ((v / 100) % 10) == 0 ? 20 : ((v / 100) % 10) == 1 ? 16 : ((v / 100) % 10) == 2 ? 12 : 8; }
@@ -200,7 +201,7 @@ constexpr int trace_variant_blocks(int v) { return ((v / 1000) % 10) == 0 ? 8 : 
 template <bool EXACT, bool COUNT, int V>
 __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(DBvh bvh, const RayF *rays, Hit *hits, const int *order, int count_max,
                                                                                unsigned long long *counters) {
-    constexpr int SORT = V % 10, FMA = (V / 10) % 10, DEPTH = trace_variant_depth(V);
+    constexpr int SORT = V % 10, FMA = (V / 10) % 10, DEPTH = trace_variant_depth(V), LOOP = V / 10000;
     __shared__ int2 stack[DEPTH * TRACE_BLOCK];
     const int n = count_max;
     TraceStackT<DEPTH> st; st.smem = stack;
@@ -214,8 +215,8 @@ __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(
         if (!(b.w < a.w) && bvh.n_nodes != 0) {   // tfar < tnear: never hits
             int sp = 0, cur = 0;
             while (cur != TRACE_DONE) {
-                if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA>(bvh, cur, r, st, sp); }
-                else cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
+                if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA>(bvh, cur, r, st, sp); if ((LOOP & 1) == 0) continue; }
+                if (cur < 0 && cur != TRACE_DONE) cur = trace_leaf<EXACT, (LOOP & 2) != 0>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
             }
         }
         hits[i] = r.hit;
