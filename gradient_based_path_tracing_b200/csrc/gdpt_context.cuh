@@ -77,6 +77,7 @@ struct gdpt_ctx {
     gdpt::PoissonCache pc;
     gdpt_stats stats;
     cudaEvent_t ev[8];
+    int sort_cell_bits = 5, sort_dir_bits = 3;   // ray-sort key: 2^5 cells per axis, 2^3 x 2^3 direction bins (GDPT_SORT_BITS="cell,dir"; gdpt_wavefront.cuh)
     bool sort_rays = true;            // re-order bounce-ray queues by origin cell + direction octant (GDPT_SORT_RAYS=0 disables)
     float box_lo[3] = {0, 0, 0}, box_hi[3] = {0, 0, 0};   // float scene box (BVH root)
     gdpt::DevBuf sort_keys, sort_order, sort_hist;
@@ -198,6 +199,10 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     if (const char *tv = getenv("GDPT_TRACE_VARIANT")) c->trace_variant = atoi(tv);
     if (const char *sv = getenv("GDPT_SORT_RAYS")) c->sort_rays = atoi(sv) != 0;
     if (const char *tp = getenv("GDPT_TAIL_PATHS")) c->tail_paths = atoi(tp);
+    if (const char *sb = getenv("GDPT_SORT_BITS")) {
+        int cb = 0, db = 0;
+        if (sscanf(sb, "%d,%d", &cb, &db) == 2 && cb >= 2 && db >= 0 && 3 * cb + 2 * db >= 15 && 3 * cb + 2 * db <= 25) { c->sort_cell_bits = cb; c->sort_dir_bits = db; }
+    }
     if (const char *sv = getenv("GDPT_SHADE_VARIANT")) c->shade_variant = atoi(sv);
     c->lambertian_only = !mats.empty();
     for (const DMaterial &m : mats) if (m.type != MAT_LAMBERTIAN) c->lambertian_only = false;

@@ -53,15 +53,17 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     if (sorting) {
         if (int r = c->sort_keys.ensure((size_t)N * sizeof(int))) return r;
         if (int r = c->sort_order.ensure((size_t)N * sizeof(int))) return r;
-        if (int r = c->sort_hist.ensure((size_t)SORT_BINS * sizeof(int))) return r;
+        if (int r = c->sort_hist.ensure((size_t)(sort_bins(c->sort_cell_bits, c->sort_dir_bits) + 1024) * sizeof(int))) return r;   // histogram + chunk totals
         wp.sort_keys = c->sort_keys.as<int>(); wp.sort_hist = c->sort_hist.as<int>();
-        const int cells = 1 << SORT_CELL_BITS;
+        wp.sort_cell_bits = c->sort_cell_bits; wp.sort_dir_bits = c->sort_dir_bits;
+        const int cells = 1 << c->sort_cell_bits;
         for (int k = 0; k < 3; k++) {
             float ext = c->box_hi[k] - c->box_lo[k];
             wp.sort_lo[k] = c->box_lo[k]; wp.sort_scale[k] = ext > 0.f ? cells / ext : 0.f;
         }
     } else { wp.sort_keys = nullptr; wp.sort_hist = nullptr; }
     int *cnt = c->counters.as<int>();
+    const int n_bins = sorting ? sort_bins(c->sort_cell_bits, c->sort_dir_bits) : 0, n_chunks = std::max(1, n_bins / SORT_CHUNK);
     GenRec<R> *gen = c->gen.as<GenRec<R>>();
     RayF *rays = c->rays.as<RayF>(); Hit *hits = c->hits.as<Hit>();
     PathRec<R> *cur = c->rec_a.as<PathRec<R>>(), *nxt = c->rec_b.as<PathRec<R>>();
@@ -76,7 +78,7 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     GD_CUDA(cudaEventRecord(e0, st));
     launch_trace<ModeSel<R>::exact>(c, rays, hits, 5 * N);
     GD_CUDA(cudaEventRecord(e1, st));
-    if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)SORT_BINS * sizeof(int), st));
+    if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)n_bins * sizeof(int), st));
     {
         auto args = [&](auto kern) { kern<<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, hits, cur, off, rays, cnt); };
         if constexpr (MS == MS_LAMBERTIAN && sizeof(R) == 4) {   // occupancy variants of the diffuse-only float kernels (GDPT_SHADE_VARIANT)
@@ -110,14 +112,15 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
         GD_CUDA(cudaEventRecord(e0, st));
         const int *order = nullptr;
         if (sorting && count >= SORT_MIN_RAYS) {   // histogram was filled by the kernel that emitted these rays
-            k_sort_scan<<<1, 1024, 0, st>>>(wp.sort_hist);
-            k_sort_scatter<<<blocks_for(count, 256), 256, 0, st>>>(wp.sort_keys, wp.sort_hist, count, c->sort_order.as<int>());
-            c->stats.kernel_launches += 2;
+            k_sort_scan<<<n_chunks, 1024, 0, st>>>(wp.sort_hist, wp.sort_hist + n_bins);
+            k_sort_chunks<<<1, 1024, 0, st>>>(wp.sort_hist + n_bins, n_chunks);
+            k_sort_scatter<<<blocks_for(count, 256), 256, 0, st>>>(wp.sort_keys, wp.sort_hist, wp.sort_hist + n_bins, count, c->sort_order.as<int>());
+            c->stats.kernel_launches += 3;
             order = c->sort_order.as<int>();
         }
         launch_trace<ModeSel<R>::exact>(c, rays, hits, count, order);
         GD_CUDA(cudaEventRecord(e1, st));
-        if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)SORT_BINS * sizeof(int), st));
+        if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)n_bins * sizeof(int), st));
         int *cin = cnt + which, *cout = cnt + (which ^ 1);
         GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
         {

@@ -57,37 +57,51 @@ struct WaveParams {
     // ray sorting (set by run_wave when enabled): per-slot key + histogram, origin grid over the scene box
     int *sort_keys, *sort_hist;
     float sort_lo[3], sort_scale[3];
+    int sort_cell_bits, sort_dir_bits;
 };
 
 // ---------------------------------------------------------------- ray sorting
 // Bounce rays are incoherent; before they are traced the queue is re-ordered by
-// key = Morton(origin cell in a 2^B-per-axis grid over the scene box) : direction octant
+// key = (coarse origin cell, Morton) : (direction, 8x8 octahedral bins) : (fine cell bit per axis)
 // with a counting sort: the shade kernel that emits a ray also bumps the key's histogram
 // bin, k_sort_scan turns the histogram into start offsets, k_sort_scatter writes the
 // permutation `order` that k_trace follows.  Rays themselves never move.
-constexpr int SORT_CELL_BITS = 4;
-constexpr int SORT_BINS = 1 << (3 * SORT_CELL_BITS + 3);
+constexpr int SORT_CELL_BITS = 5;                       // default origin grid: 32 cells per axis over the scene box
+constexpr int SORT_DIR_BITS = 3;                        // default direction grid: 8 x 8 octahedral bins
+constexpr int SORT_CHUNK = 32768;                       // histogram bins scanned by one block
+constexpr int SORT_MAX_KEY_BITS = 25;                   // 3*cell + 2*dir may not exceed this (1024 chunks)
+inline int sort_bins(int cell_bits, int dir_bits) { return 1 << (3 * cell_bits + 2 * dir_bits); }
 
-GD_D unsigned sort_spread(unsigned x) {   // abcd -> a00b00c00d
+GD_D unsigned sort_spread(unsigned x, int bits) {   // abcd -> a00b00c00d
     unsigned r = 0;
-#pragma unroll
-    for (int b = 0; b < SORT_CELL_BITS; b++) r |= ((x >> b) & 1u) << (3 * b);
+    for (int b = 0; b < bits; b++) r |= ((x >> b) & 1u) << (3 * b);
     return r;
 }
+// key = [coarse cell Morton : direction bin : lowest cell bit per axis] — a warp of the sorted queue shares a
+// 2^(CELL_BITS-1) cell and a ~22 degree direction bin and differs in the fine cell
 GD_D void sort_emit(const WaveParams &wp, int slot, const RayF &r) {
     if (!wp.sort_hist) return;
-    const int top = (1 << SORT_CELL_BITS) - 1;
+    const int cb = wp.sort_cell_bits, db = wp.sort_dir_bits;
+    const int top = (1 << cb) - 1;
     int cx = min(top, max(0, (int)((r.ox - wp.sort_lo[0]) * wp.sort_scale[0])));
     int cy = min(top, max(0, (int)((r.oy - wp.sort_lo[1]) * wp.sort_scale[1])));
     int cz = min(top, max(0, (int)((r.oz - wp.sort_lo[2]) * wp.sort_scale[2])));
-    unsigned key = ((sort_spread(cx) | (sort_spread(cy) << 1) | (sort_spread(cz) << 2)) << 3) |
-                   (r.dx < 0.f ? 1u : 0u) | (r.dy < 0.f ? 2u : 0u) | (r.dz < 0.f ? 4u : 0u);
+    // octahedral map of the direction to [-1,1]^2
+    float inv = 1.0f / (fabsf(r.dx) + fabsf(r.dy) + fabsf(r.dz));
+    float u = r.dx * inv, v = r.dy * inv;
+    if (r.dz < 0.f) { float tu = (1.f - fabsf(v)) * (u >= 0.f ? 1.f : -1.f), tv = (1.f - fabsf(u)) * (v >= 0.f ? 1.f : -1.f); u = tu; v = tv; }
+    const int dtop = (1 << db) - 1;
+    int du = min(dtop, max(0, (int)((u * 0.5f + 0.5f) * (float)(1 << db)))), dv = min(dtop, max(0, (int)((v * 0.5f + 0.5f) * (float)(1 << db))));
+    unsigned coarse = sort_spread(cx >> 1, cb - 1) | (sort_spread(cy >> 1, cb - 1) << 1) | (sort_spread(cz >> 1, cb - 1) << 2);
+    unsigned key = (((coarse << (2 * db)) | (unsigned)(du << db) | (unsigned)dv) << 3) | (unsigned)((cx & 1) | ((cy & 1) << 1) | ((cz & 1) << 2));
     wp.sort_keys[slot] = (int)key;
     atomicAdd(wp.sort_hist + key, 1);
 }
-// exclusive scan of the SORT_BINS histogram, one block of 1024 threads
-static __global__ void __launch_bounds__(1024) k_sort_scan(int *hist) {
-    constexpr int PER = SORT_BINS / 1024;
+// exclusive scan of the histogram: every block scans one SORT_CHUNK-bin chunk in place and leaves its total in
+// chunk_sum; k_sort_chunks then scans the totals; k_sort_scatter adds the two
+static __global__ void __launch_bounds__(1024) k_sort_scan(int *hist_all, int *chunk_sum) {
+    constexpr int PER = SORT_CHUNK / 1024;
+    int *hist = hist_all + (size_t)blockIdx.x * SORT_CHUNK;
     __shared__ int warp_sum[32];
     int v[PER], sum = 0;
     int4 *h4 = reinterpret_cast<int4 *>(hist + threadIdx.x * PER);
@@ -103,15 +117,31 @@ static __global__ void __launch_bounds__(1024) k_sort_scan(int *hist) {
         int ws = warp_sum[lane], wi = ws;
         for (int s = 1; s < 32; s <<= 1) { int t = __shfl_up_sync(0xffffffffu, wi, s); if (lane >= s) wi += t; }
         warp_sum[lane] = wi - ws;
+        if (lane == 31) chunk_sum[blockIdx.x] = wi;
     }
     __syncthreads();
     int base = warp_sum[wid] + incl - sum;
 #pragma unroll
     for (int i = 0; i < PER / 4; i++) h4[i] = make_int4(v[4 * i] + base, v[4 * i + 1] + base, v[4 * i + 2] + base, v[4 * i + 3] + base);
 }
-static __global__ void __launch_bounds__(256) k_sort_scatter(const int *keys, int *offsets, int n, int *order) {
+static __global__ void __launch_bounds__(1024) k_sort_chunks(int *chunk_sum, int n_chunks) {   // exclusive scan of <= 1024 chunk totals, one block
+    __shared__ int warp_sum[32];
+    int t = threadIdx.x < n_chunks ? chunk_sum[threadIdx.x] : 0;
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, incl = t;
+    for (int s = 1; s < 32; s <<= 1) { int q = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += q; }
+    if (lane == 31) warp_sum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int ws = warp_sum[lane], wi = ws;
+        for (int s = 1; s < 32; s <<= 1) { int q = __shfl_up_sync(0xffffffffu, wi, s); if (lane >= s) wi += q; }
+        warp_sum[lane] = wi - ws;
+    }
+    __syncthreads();
+    if (threadIdx.x < n_chunks) chunk_sum[threadIdx.x] = warp_sum[wid] + incl - t;
+}
+static __global__ void __launch_bounds__(256) k_sort_scatter(const int *keys, int *offsets, const int *chunk_off, int n, int *order) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) order[atomicAdd(offsets + keys[i], 1)] = i;
+    if (i < n) { int k = keys[i]; order[atomicAdd(offsets + k, 1) + __ldg(chunk_off + k / SORT_CHUNK)] = i; }
 }
 
 // Records move between registers and HBM as 16-byte vectors (the compiler's own struct copy
