@@ -38,6 +38,8 @@ def parse():
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="target CPU time of one reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--solver", default="auto", choices=["auto", "gather", "distributed"],
+                    help="N>1 Poisson solve: bands summed onto rank 0, or the all-to-all transposed solve (auto: distributed from 4K up)")
     return ap.parse_args()
 
 
@@ -179,7 +181,7 @@ def run_native(args):
     spp = args.spp or sc.options.samples_per_pixel
     w, h = sc.width, sc.height
     lib, check = _capi.lib(), _capi.check
-    R = multi.DistributedRenderer(sc, local, dist_, torch)
+    R = multi.DistributedRenderer(sc, local, dist_, torch, solver=args.solver)
     check(lib.gdpt_set_stream(R.ctx, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
 
     def barrier():
@@ -224,7 +226,7 @@ def run_native(args):
             r = g.gradient_path_render(sc2, device=local, spp=spp, precision=args.precision)
             sc2.close()
             return r
-        R2 = multi.DistributedRenderer(sc2, local, dist_, torch)
+        R2 = multi.DistributedRenderer(sc2, local, dist_, torch, solver=args.solver)
         r = R2.render(spp, precision=args.precision, to_host=True)
         sc2.close()
         return r
@@ -285,6 +287,7 @@ def run_native(args):
                 "dtype": args.precision, "data": "synthetic",
                 "config": {"workload": "%s gradpath %dx%d %d spp, reference offset semantics, image split into %d row band(s)" % (args.scene, w, h, spp, world),
                            "precision": args.precision + " traversal/shading, f64 accumulation + Poisson",
+                           "poisson_solver": R.solver if world > 1 else "single GPU",
                            "l2_flush": "inputs larger than L2: each step streams %.1f GB of path state" % (paths / 5 * 900 / 1e9)},
                 "clocks": clocks, "gpu_launches": int(launches.item()),
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(4 * w * h * 3 * 8),

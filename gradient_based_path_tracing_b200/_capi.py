@@ -51,10 +51,16 @@ class GdptStats(C.Structure):
                 ("bounce_iterations", C.c_int64), ("tail_paths", C.c_int64)]
 
 
+class GdptDistGeom(C.Structure):
+    _fields_ = [("w", C.c_int32), ("h", C.c_int32), ("n_ranks", C.c_int32), ("rank", C.c_int32),
+                ("y0", C.c_int32), ("y1", C.c_int32), ("band_w", C.c_int32)]
+
+
 # every symbol include/gdpt.h declares
 EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_destroy", "gdpt_scene_bounds", "gdpt_render",
            "gdpt_render_accumulate_device", "gdpt_merge_device", "gdpt_poisson", "gdpt_poisson_device", "gdpt_get_stats",
-           "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill"]
+           "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill",
+           "gdpt_merge_rows_device", "gdpt_poisson_dist_rows_forward", "gdpt_poisson_dist_columns", "gdpt_poisson_dist_rows_inverse"]
 
 _lib = None
 
@@ -76,6 +82,10 @@ def lib():
         L.gdpt_merge_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
         L.gdpt_poisson.argtypes = [C.c_int, C.c_int, C.c_int, dp, dp, dp, C.c_double, dp]
         L.gdpt_poisson_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_double, vp]
+        L.gdpt_merge_rows_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
+        L.gdpt_poisson_dist_rows_forward.argtypes = [vp, C.POINTER(GdptDistGeom), vp, vp, vp, C.c_double, vp, vp]
+        L.gdpt_poisson_dist_columns.argtypes = [vp, C.POINTER(GdptDistGeom), C.c_double, vp, vp, vp]
+        L.gdpt_poisson_dist_rows_inverse.argtypes = [vp, C.POINTER(GdptDistGeom), vp, vp]
         L.gdpt_get_stats.argtypes = [vp, C.POINTER(GdptStats)]
         L.gdpt_synchronize.argtypes = [vp]
         L.gdpt_set_stream.argtypes = [vp, vp]

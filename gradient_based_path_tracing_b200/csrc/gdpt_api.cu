@@ -10,7 +10,11 @@ template <typename R> int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp);
 extern template int run_wave<double>(gdpt_ctx *, DScene<double>, WaveParams);
 extern template int run_wave<float>(gdpt_ctx *, DScene<float>, WaveParams);
 int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
-int merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const double *d_cx1, const double *d_cy0, const double *d_cy1, double *d_cx, double *d_cy);
+int merge_device(gdpt_ctx *ctx, int w, int h, int ya, int yb, const double *d_cx0, const double *d_cx1, const double *d_cy0, const double *d_cy1, double *d_cx, double *d_cy);
+int poisson_dist_rows_forward(gdpt_ctx *c, const gdpt_dist_geom *g, const double *d_u, const double *d_gx, const double *d_gy, double alpha,
+                              double *d_send, double *d_dc_partial);
+int poisson_dist_columns(gdpt_ctx *c, const gdpt_dist_geom *g, double alpha, const double *d_dc, const double *d_recv, double *d_send_back);
+int poisson_dist_rows_inverse(gdpt_ctx *c, const gdpt_dist_geom *g, const double *d_recv_back, double *d_out);
 template <typename R> int dbg_sample_primary(gdpt_ctx *ctx, const DScene<R> &sc, int n, const double *screen_pos, double *rays);
 template <typename R> int dbg_intersect(gdpt_ctx *ctx, const DScene<R> &sc, int n, const double *rays, const double *rdiff, int32_t *ids, double *vtx);
 template <typename R> int dbg_bsdf(gdpt_ctx *ctx, const DScene<R> &sc, int mat_id, int n, const double *vtx, const double *dirs, const double *rnd, double *out);
@@ -203,7 +207,33 @@ int gdpt_merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const do
                       double *d_cx, double *d_cy) {
     if (!ctx) return fail(GDPT_ERR_ARG, "null argument");
     GD_CUDA(cudaSetDevice(ctx->device));
-    return merge_device(ctx, w, h, d_cx0, d_cx1, d_cy0, d_cy1, d_cx, d_cy);
+    return merge_device(ctx, w, h, 0, h, d_cx0, d_cx1, d_cy0, d_cy1, d_cx, d_cy);
+}
+
+int gdpt_merge_rows_device(gdpt_ctx *ctx, int w, int h, int ya, int yb, const double *d_cx0, const double *d_cx1, const double *d_cy0,
+                           const double *d_cy1, double *d_cx, double *d_cy) {
+    if (!ctx || ya < 0 || yb > h || w < 1) return fail(GDPT_ERR_ARG, "bad argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return merge_device(ctx, w, h, ya, yb, d_cx0, d_cx1, d_cy0, d_cy1, d_cx, d_cy);
+}
+
+int gdpt_poisson_dist_rows_forward(gdpt_ctx *ctx, const gdpt_dist_geom *geom, const double *d_u, const double *d_gx, const double *d_gy,
+                                   double alpha, double *d_send, double *d_dc_partial) {
+    if (!ctx || !geom || !d_u || !d_gx || !d_gy || !d_send || !d_dc_partial) return fail(GDPT_ERR_ARG, "null argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return poisson_dist_rows_forward(ctx, geom, d_u, d_gx, d_gy, alpha > 0 ? alpha : 0.04, d_send, d_dc_partial);
+}
+
+int gdpt_poisson_dist_columns(gdpt_ctx *ctx, const gdpt_dist_geom *geom, double alpha, const double *d_dc, const double *d_recv, double *d_send_back) {
+    if (!ctx || !geom || !d_dc || !d_recv || !d_send_back) return fail(GDPT_ERR_ARG, "null argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return poisson_dist_columns(ctx, geom, alpha > 0 ? alpha : 0.04, d_dc, d_recv, d_send_back);
+}
+
+int gdpt_poisson_dist_rows_inverse(gdpt_ctx *ctx, const gdpt_dist_geom *geom, const double *d_recv_back, double *d_out) {
+    if (!ctx || !geom || !d_recv_back || !d_out) return fail(GDPT_ERR_ARG, "null argument");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return poisson_dist_rows_inverse(ctx, geom, d_recv_back, d_out);
 }
 
 int gdpt_poisson_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out) {
@@ -229,7 +259,7 @@ int gdpt_render(gdpt_ctx *ctx, const gdpt_render_params *params, gdpt_images *ou
                  : accumulate<float>(ctx, r, ctx->img.as<double>(), ctx->cx0.as<double>(), ctx->cy0.as<double>(), ctx->cx1.as<double>(), ctx->cy1.as<double>());
     if (rc) return rc;
     GD_CUDA(cudaEventRecord(ctx->ev[1], st));
-    if (int rc2 = merge_device(ctx, w, h, ctx->cx0.as<double>(), ctx->cx1.as<double>(), ctx->cy0.as<double>(), ctx->cy1.as<double>(),
+    if (int rc2 = merge_device(ctx, w, h, 0, h, ctx->cx0.as<double>(), ctx->cx1.as<double>(), ctx->cy0.as<double>(), ctx->cy1.as<double>(),
                                ctx->cx.as<double>(), ctx->cy.as<double>())) return rc2;
     if (int rc2 = poisson_device(ctx, w, h, ctx->img.as<double>(), ctx->cx.as<double>(), ctx->cy.as<double>(), r.alpha, ctx->out.as<double>())) return rc2;
     GD_CUDA(cudaEventRecord(ctx->ev[2], st));

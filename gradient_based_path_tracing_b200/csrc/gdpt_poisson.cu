@@ -9,11 +9,8 @@ static inline int blocks_for_p(long long n, int block) { return (int)((n + block
 #define SM_COUNT SM_COUNT_P
 #define blocks_for blocks_for_p
 
-static int ensure_poisson(gdpt_ctx *c, int w, int h) {
+static int ensure_matrices(gdpt_ctx *c, int w, int h) {
     PoissonCache &pc = c->pc;
-    size_t plane = (size_t)w * h * 3 * sizeof(double);
-    if (int r = pc.work.ensure(plane)) return r;
-    if (int r = pc.work2.ensure(plane)) return r;
     if (int r = pc.partial.ensure((size_t)SM_COUNT * 8 * 3 * sizeof(double))) return r;
     if (int r = pc.dc.ensure(64)) return r;
     if (pc.w != w || pc.h != h) {
@@ -27,6 +24,14 @@ static int ensure_poisson(gdpt_ctx *c, int w, int h) {
     return 0;
 }
 
+static int ensure_poisson(gdpt_ctx *c, int w, int h) {
+    PoissonCache &pc = c->pc;
+    size_t plane = (size_t)w * h * 3 * sizeof(double);
+    if (int r = pc.work.ensure(plane)) return r;
+    if (int r = pc.work2.ensure(plane)) return r;
+    return ensure_matrices(c, w, h);
+}
+
 int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out) {
     if (w < 2 || h < 2) return fail(GDPT_ERR_ARG, "Poisson solve needs at least a 2x2 image");
     if (int r = ensure_poisson(c, w, h)) return r;
@@ -34,7 +39,7 @@ int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d
     cudaStream_t st = c->stream;
     double *A = pc.work.as<double>(), *B = pc.work2.as<double>();
     const int nb = SM_COUNT * 8;
-    k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, h, d_u, d_gx, d_gy, alpha, A, pc.partial.as<double>());
+    k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, h, 0, h, d_u, d_gx, d_gy, alpha, A, pc.partial.as<double>());
     k_dc_reduce<<<1, 32, 0, st>>>(nb, pc.partial.as<double>(), pc.dc.as<double>());
     Epilogue ep; memset(&ep, 0, sizeof(ep));
     ep.img_w = w; ep.img_h = h; ep.alpha = alpha; ep.dc = pc.dc.as<double>(); ep.out = d_out;
@@ -57,8 +62,84 @@ int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d
 }
 
 
-int merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const double *d_cx1, const double *d_cy0, const double *d_cy1, double *d_cx, double *d_cy) {
-    k_merge<<<SM_COUNT * 8, 256, 0, ctx->stream>>>(w, h, d_cx0, d_cx1, d_cy0, d_cy1, d_cx, d_cy);
+// ---------------------------------------------------------------- distributed solve (row bands <-> column bands)
+// The separable transform F = D_H * X * D_W is split at the point where the data has to change owners:
+//   rows_forward   (row band, local)    rhs, DC partial sums, X*D_W with the result PACKED per destination rank
+//   -- all-to-all transpose (NCCL, run by the caller) --
+//   columns        (column band, local) D_H*(.), spectral divide + DC, D_H*(.) again (inverse along columns)
+//   -- all-to-all transpose back --
+//   rows_inverse   (row band, local)    (.)*D_W read straight from the received chunks, scale, RGB interleave
+// Only two transposes are needed because the DCT is applied as a dense matrix product: nothing is ever
+// physically transposed, the messages are just the [rows_r x cols_s] blocks.
+static int dist_check(const gdpt_dist_geom *g) {
+    if (!g || g->w < 2 || g->h < 2 || g->n_ranks < 1 || g->rank < 0 || g->rank >= g->n_ranks || g->y0 < 0 || g->y1 > g->h || g->y1 < g->y0 ||
+        g->band_w < 1 || (long long)g->band_w * (g->n_ranks - 1) >= g->w)
+        return fail(GDPT_ERR_ARG, "bad distributed-solve geometry");
+    return 0;
+}
+static Banded dist_band(const gdpt_dist_geom *g) { Banded b; b.n_bands = g->n_ranks; b.band_w = g->band_w; b.rows = g->y1 - g->y0; b.W = g->w; return b; }
+
+int poisson_dist_rows_forward(gdpt_ctx *c, const gdpt_dist_geom *g, const double *d_u, const double *d_gx, const double *d_gy, double alpha,
+                              double *d_send, double *d_dc_partial) {
+    if (int r = dist_check(g)) return r;
+    if (int r = ensure_matrices(c, g->w, g->h)) return r;
+    PoissonCache &pc = c->pc;
+    cudaStream_t st = c->stream;
+    const int w = g->w, rows = g->y1 - g->y0, nb = SM_COUNT * 8;
+    if (int r = pc.work.ensure(std::max<size_t>((size_t)w * rows * 3 * sizeof(double), 16))) return r;
+    k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, g->h, g->y0, g->y1, d_u, d_gx, d_gy, alpha, pc.work.as<double>(), pc.partial.as<double>());
+    k_dc_reduce<<<1, 32, 0, st>>>(nb, pc.partial.as<double>(), d_dc_partial);
+    c->stats.kernel_launches += 2;
+    if (rows > 0) {
+        Epilogue ep; memset(&ep, 0, sizeof(ep));
+        ep.mode = EPI_PACK; ep.band = dist_band(g);
+        dim3 grid(blocks_for(w, GT), blocks_for(3 * rows, GT), 1);
+        k_dgemm<<<grid, 256, 0, st>>>(3 * rows, w, w, pc.work.as<double>(), w, 0, pc.Dw.as<double>(), w, 0, d_send, w, 0, ep);
+        c->stats.kernel_launches++;
+    }
+    GD_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int poisson_dist_columns(gdpt_ctx *c, const gdpt_dist_geom *g, double alpha, const double *d_dc, const double *d_recv, double *d_send_back) {
+    if (int r = dist_check(g)) return r;
+    if (int r = ensure_matrices(c, g->w, g->h)) return r;
+    PoissonCache &pc = c->pc;
+    cudaStream_t st = c->stream;
+    const int h = g->h, x0 = g->rank * g->band_w, ws = (g->rank == g->n_ranks - 1) ? g->w - x0 : g->band_w, n = 3 * ws;
+    if (int r = pc.work2.ensure((size_t)h * n * sizeof(double))) return r;
+    Epilogue ep; memset(&ep, 0, sizeof(ep));
+    ep.img_w = g->w; ep.img_h = h; ep.alpha = alpha; ep.dc = d_dc; ep.ch_w = ws; ep.x0 = x0;
+    dim3 grid(blocks_for(n, GT), blocks_for(h, GT), 1);
+    ep.mode = EPI_DIVIDE;
+    k_dgemm<<<grid, 256, 0, st>>>(h, n, h, pc.DhT.as<double>(), h, 0, d_recv, n, 0, pc.work2.as<double>(), n, 0, ep);
+    ep.mode = EPI_STORE;
+    k_dgemm<<<grid, 256, 0, st>>>(h, n, h, pc.DhT.as<double>(), h, 0, pc.work2.as<double>(), n, 0, d_send_back, n, 0, ep);
+    c->stats.kernel_launches += 2;
+    GD_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int poisson_dist_rows_inverse(gdpt_ctx *c, const gdpt_dist_geom *g, const double *d_recv_back, double *d_out) {
+    if (int r = dist_check(g)) return r;
+    if (int r = ensure_matrices(c, g->w, g->h)) return r;
+    PoissonCache &pc = c->pc;
+    const int w = g->w, rows = g->y1 - g->y0;
+    if (rows == 0) return 0;
+    Epilogue ep; memset(&ep, 0, sizeof(ep));
+    ep.mode = EPI_SCALE_INTERLEAVE; ep.img_w = w; ep.img_h = rows; ep.band = dist_band(g);
+    ep.scale = 4.0 * (w - 1) * (g->h - 1);
+    ep.out = d_out + (size_t)g->y0 * w * 3;
+    dim3 grid(blocks_for(w, GT), blocks_for(3 * rows, GT), 1);
+    k_dgemm<true><<<grid, 256, 0, c->stream>>>(3 * rows, w, w, d_recv_back, w, 0, pc.Dw.as<double>(), w, 0, nullptr, w, 0, ep);
+    c->stats.kernel_launches++;
+    GD_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int merge_device(gdpt_ctx *ctx, int w, int h, int ya, int yb, const double *d_cx0, const double *d_cx1, const double *d_cy0, const double *d_cy1, double *d_cx, double *d_cy) {
+    if (yb <= ya) return 0;
+    k_merge<<<SM_COUNT * 8, 256, 0, ctx->stream>>>(w, h, ya, yb, d_cx0, d_cx1, d_cy0, d_cy1, d_cx, d_cy);
     ctx->stats.kernel_launches++;
     GD_CUDA(cudaGetLastError());
     return 0;

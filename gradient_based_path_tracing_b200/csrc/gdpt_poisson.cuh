@@ -19,9 +19,11 @@
 
 namespace gdpt {
 
-static __global__ void k_merge(int w, int h, const double *cx0, const double *cx1, const double *cy0, const double *cy1, double *cx, double *cy) {
-    size_t n = (size_t)w * h * 3;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+// rows [ya, yb) of the full-size images (the single-GPU solve passes 0, h)
+static __global__ void k_merge(int w, int h, int ya, int yb, const double *cx0, const double *cx1, const double *cy0, const double *cy1, double *cx, double *cy) {
+    (void)h;
+    size_t n = (size_t)w * yb * 3;
+    for (size_t i = (size_t)w * ya * 3 + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         size_t pix = i / 3;
         int x = (int)(pix % w), y = (int)(pix / w);
         cx[i] = x == 0 ? cx0[i] : cx0[i] + cx1[i - 3];
@@ -30,12 +32,16 @@ static __global__ void k_merge(int w, int h, const double *cx0, const double *cx
 }
 
 constexpr int RHS_BLOCK = 256;
-static __global__ void __launch_bounds__(RHS_BLOCK) k_poisson_rhs(int w, int h, const double *u, const double *gx, const double *gy, double alpha,
+// u, gx, gy are full-size interleaved images; rows [y0, y1) are turned into the planar band buffer
+// buf[3][y1-y0][w] (the single-GPU solve passes 0, h; a rank of the distributed solve its own band, whose
+// gy must be valid up to row y1 when y1 < h)
+static __global__ void __launch_bounds__(RHS_BLOCK) k_poisson_rhs(int w, int h, int y0, int y1, const double *u, const double *gx, const double *gy, double alpha,
                                                            double *buf, double *partial /* [gridDim.x][3] */) {
     __shared__ double red[3][RHS_BLOCK];
     double dc[3] = {0, 0, 0};
-    size_t npix = (size_t)w * h;
-    for (size_t p = blockIdx.x * (size_t)RHS_BLOCK + threadIdx.x; p < npix; p += (size_t)gridDim.x * RHS_BLOCK) {
+    size_t npix = (size_t)w * (y1 - y0);
+    for (size_t q = blockIdx.x * (size_t)RHS_BLOCK + threadIdx.x; q < npix; q += (size_t)gridDim.x * RHS_BLOCK) {
+        size_t p = q + (size_t)w * y0;
         int x = (int)(p % w), y = (int)(p / w);
         bool ix = x > 0 && x < w - 1, iy = y > 0 && y < h - 1;
         double m = 1.0;
@@ -49,7 +55,7 @@ static __global__ void __launch_bounds__(RHS_BLOCK) k_poisson_rhs(int w, int h, 
             double v = alpha * uv;
             if (ix) v -= (gx[a + 3] - gx[a]); else v -= (-2.0 * gx[a]);
             if (iy) v -= (gy[a + (size_t)w * 3] - gy[a]); else v -= (-2.0 * gy[a]);
-            buf[(size_t)c * npix + p] = v;
+            buf[(size_t)c * npix + q] = v;
         }
     }
     for (int c = 0; c < 3; c++) red[c][threadIdx.x] = dc[c];
@@ -82,17 +88,32 @@ static __global__ void k_dct_matrix(int N, int transpose, double *D) {
     }
 }
 
-enum { EPI_STORE = 0, EPI_DIVIDE = 1, EPI_SCALE_INTERLEAVE = 2 };
+enum { EPI_STORE = 0, EPI_DIVIDE = 1, EPI_SCALE_INTERLEAVE = 2, EPI_PACK = 3 };
+// Distributed solve: a rank's rows x W band of the three channels laid out chunk-major by COLUMN band, the
+// chunk of column band s holding [rows][3][w_s] — i.e. exactly the message rank s receives in the all-to-all
+// transpose, and (stacked over the sending ranks) a row-major [H][3*w_s] matrix on the receiving side.
+// Column bands are band_w wide except the last.
+struct Banded {
+    int n_bands, band_w, rows, W;
+    __host__ __device__ size_t addr(int ch, int y, int col) const {
+        int s = col / band_w; if (s > n_bands - 1) s = n_bands - 1;
+        int x0 = s * band_w, ws = (s == n_bands - 1) ? W - x0 : band_w;
+        return (size_t)rows * 3 * x0 + (size_t)y * 3 * ws + (size_t)ch * ws + (col - x0);
+    }
+};
 struct Epilogue {
     int mode;
-    int img_w, img_h;
+    int img_w, img_h;   // full image size (spectral divide); img_h = rows of the band for the interleaving / packing epilogues
     double alpha, scale;
     const double *dc;   // [3]
     double *out;        // interleaved RGB for EPI_SCALE_INTERLEAVE
+    int ch_w, x0;       // EPI_DIVIDE on a column band: columns are [3][ch_w] side by side starting at image column x0 (ch_w = 0: channel = blockIdx.z)
+    Banded band;        // EPI_PACK store / BANDED_A load
 };
 
 constexpr int GT = 64, GK = 16;
 // C[z] (MxN, ldc) = A (MxK, lda; shared by the batch when strideA == 0) * B[z] (KxN, ldb)
+template <bool BANDED_A = false>
 static __global__ void __launch_bounds__(256) k_dgemm(int M, int N, int K, const double *A, int lda, long long strideA,
                                                const double *B, int ldb, long long strideB, double *C, int ldc, long long strideC, Epilogue ep) {
     __shared__ double As[2][GK][GT + 1];
@@ -113,7 +134,8 @@ static __global__ void __launch_bounds__(256) k_dgemm(int M, int N, int K, const
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             int r = row0 + a_r, k = k0 + a_k + q;
-            As[buf][a_k + q][a_r] = (r < M && k < K) ? A[(size_t)r * lda + k] : 0.0;
+            if (BANDED_A) As[buf][a_k + q][a_r] = (r < M && k < K) ? A[ep.band.addr(r / ep.band.rows, r % ep.band.rows, k)] : 0.0;
+            else As[buf][a_k + q][a_r] = (r < M && k < K) ? A[(size_t)r * lda + k] : 0.0;
         }
 #pragma unroll
         for (int q = 0; q < 4; q++) {
@@ -153,13 +175,16 @@ static __global__ void __launch_bounds__(256) k_dgemm(int M, int N, int K, const
             if (ep.mode == EPI_STORE) {
                 C[(size_t)r * ldc + c] = v;
             } else if (ep.mode == EPI_DIVIDE) {
-                // r = y, c = x of channel z
-                double lapx = 2.0 * cos(3.14159265358979323846 * c / (ep.img_w - 1));
+                // r = y, c = x of channel z (whole image) or column ch*ch_w + (x - x0) of a column band
+                int x = ep.ch_w ? ep.x0 + c % ep.ch_w : c, ch = ep.ch_w ? c / ep.ch_w : z;
+                double lapx = 2.0 * cos(3.14159265358979323846 * x / (ep.img_w - 1));
                 double lapy = -4.0 + (2.0 * cos(3.14159265358979323846 * r / (ep.img_h - 1)));
                 float resp = (float)(lapy + lapx);
                 v = v / (ep.alpha - resp);
-                if (r == 0 && c == 0) v = ep.dc[z];
+                if (r == 0 && x == 0) v = ep.dc[ch];
                 C[(size_t)r * ldc + c] = v;
+            } else if (ep.mode == EPI_PACK) {
+                C[ep.band.addr(r / ep.band.rows, r % ep.band.rows, c)] = v;
             } else {
                 // rows of the planar [3][H] stack: r = ch*H + y
                 int ch = r / ep.img_h, y = r % ep.img_h;

@@ -116,6 +116,37 @@ int gdpt_merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const do
 /* fourierSolve (render.cpp:172-254): host buffers / device buffers.  `device` selects the GPU for the host form. */
 int gdpt_poisson(int device, int w, int h, const double *u, const double *gx, const double *gy, double alpha, double *out);
 int gdpt_poisson_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
+
+/* ---- distributed screened-Poisson solve (BASELINE configs[4]: 3840x2160 on 8 GPUs) ----
+ * fourierSolve (render.cpp:172-254) over the ranks of one box.  Rank r owns the row band [y0,y1) of the
+ * image and the column band [r*band_w, (r+1)*band_w) (the last band runs to w).  The three stages below
+ * are the local work; between them the caller runs the two all-to-all transposes (NCCL) and, before the
+ * first stage, the 3-double all-reduce of the DC sums (render.cpp:199-211):
+ *
+ *   halo:     cy1 row y0-1 from rank-1, cy0 row y1 from rank+1 (into the full-size images), then
+ *             gdpt_merge_rows_device(rows [y0, min(y1+1,h)))                                  render.cpp:340-350
+ *   stage 1:  gdpt_poisson_dist_rows_forward  -> d_send [3*(y1-y0)*w]: for every rank s, contiguous,
+ *             the chunk [y1-y0][3][w_s] it must receive; d_dc_partial[3] = this band's DC sums
+ *   exchange: all-to-all (send split (y1-y0)*3*w_s to rank s; the chunks received from ranks 0..n-1,
+ *             stacked, ARE the row-major [h][3*w_me] matrix of this rank's column band); all-reduce(dc)
+ *   stage 2:  gdpt_poisson_dist_columns       -> d_send_back [h][3*w_me] (rows [y0_r,y1_r) go back to rank r)
+ *   exchange: all-to-all back (contiguous row slices; received chunk s = [y1-y0][3][w_s])
+ *   stage 3:  gdpt_poisson_dist_rows_inverse  -> rows [y0,y1) of the full-size interleaved d_out
+ * With n_ranks = 1 the three stages alone equal gdpt_poisson_device. */
+typedef struct {
+    int32_t w, h;             /* full image */
+    int32_t n_ranks, rank;
+    int32_t y0, y1;           /* this rank's row band */
+    int32_t band_w;           /* column-band width; band_w*(n_ranks-1) < w */
+} gdpt_dist_geom;
+int gdpt_merge_rows_device(gdpt_ctx *ctx, int w, int h, int ya, int yb, const double *d_cx0, const double *d_cx1,
+                           const double *d_cy0, const double *d_cy1, double *d_cx, double *d_cy);
+int gdpt_poisson_dist_rows_forward(gdpt_ctx *ctx, const gdpt_dist_geom *geom, const double *d_u, const double *d_gx,
+                                   const double *d_gy, double alpha, double *d_send, double *d_dc_partial);
+int gdpt_poisson_dist_columns(gdpt_ctx *ctx, const gdpt_dist_geom *geom, double alpha, const double *d_dc,
+                              const double *d_recv, double *d_send_back);
+int gdpt_poisson_dist_rows_inverse(gdpt_ctx *ctx, const gdpt_dist_geom *geom, const double *d_recv_back, double *d_out);
+
 int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out);
 /* Run all of the context's work on the caller's CUDA stream (a cudaStream_t; NULL restores the context's own). */
 int gdpt_set_stream(gdpt_ctx *ctx, void *cuda_stream);

@@ -83,6 +83,57 @@ def test_poisson_full_size_properties(g):
     assert rel_l2(lhs, rhs) < 1e-9
 
 
+@pytest.mark.parametrize("h,w,n", [(37, 22, 1), (37, 22, 2), (24, 31, 3), (270, 480, 4), (1080, 1920, 8), (2160, 3840, 8)])
+def test_distributed_poisson_stages_equal_the_single_gpu_solve(g, scenes, h, w, n):
+    """The three local stages of the distributed solve (include/gdpt.h, gdpt_poisson_dist_*) for n virtual ranks on
+    one GPU, with the two all-to-all transposes emulated by slicing: must equal gdpt_poisson on the whole image
+    (and through it the oracle's fourierSolve).  The collectives themselves: tests/test_multi_cpu.py (gloo),
+    tests/test_multi_gpu.py (NCCL)."""
+    import torch
+    from gradient_based_path_tracing_b200 import multi
+    rng = np.random.default_rng(h + w + n)
+    full = [rng.standard_normal((h, w, 3)) for _ in range(5)]          # img, cx0, cy0, cx1, cy1
+    dev = torch.device("cuda", 0)
+    t = [torch.from_numpy(f.reshape(-1)).to(dev) for f in full]
+    cx, cy, out = (torch.zeros(h * w * 3, dtype=torch.float64, device=dev) for _ in range(3))
+    st = multi.CudaStages(scenes("cbox_gdpt_64").context(0), g._capi)
+    bands, cols, bw = multi.partition_rows(h, n), multi.column_bands(w, n), multi.column_band_width(w, n)
+    assert all(b1 > b0 for b0, b1 in bands)
+    sends, dcs = [], []
+    for r, (y0, y1) in enumerate(bands):
+        geom = dict(w=w, h=h, n_ranks=n, rank=r, y0=y0, y1=y1, band_w=bw)
+        st.merge_rows(geom, y0, min(y1 + 1, h), t[1], t[3], t[2], t[4], cx, cy)
+        send = torch.zeros(3 * (y1 - y0) * w, dtype=torch.float64, device=dev)
+        dc = torch.zeros(3, dtype=torch.float64, device=dev)
+        st.rows_forward(geom, t[0], cx, cy, 0.04, send, dc)
+        st.sync()
+        sends.append(send); dcs.append(dc)
+    dc = torch.stack(dcs).sum(0)
+    backs = []
+    for s, (x0, x1) in enumerate(cols):
+        parts = []
+        for r, (y0, y1) in enumerate(bands):
+            off = (y1 - y0) * 3 * x0
+            parts.append(sends[r][off:off + (y1 - y0) * 3 * (x1 - x0)])
+        recv = torch.cat(parts)
+        back = torch.zeros_like(recv)
+        geom = dict(w=w, h=h, n_ranks=n, rank=s, y0=bands[s][0], y1=bands[s][1], band_w=bw)
+        st.columns(geom, 0.04, dc, recv, back)
+        st.sync()
+        backs.append(back)
+    for r, (y0, y1) in enumerate(bands):
+        recv_back = torch.cat([backs[s][y0 * 3 * (x1 - x0):y1 * 3 * (x1 - x0)] for s, (x0, x1) in enumerate(cols)])
+        geom = dict(w=w, h=h, n_ranks=n, rank=r, y0=y0, y1=y1, band_w=bw)
+        st.rows_inverse(geom, recv_back, out)
+        st.sync()
+    wx, wy = cport.merge(full[1], full[3], full[2], full[4])
+    assert np.array_equal(cx.cpu().numpy().reshape(h, w, 3), wx) and np.array_equal(cy.cpu().numpy().reshape(h, w, 3), wy)
+    got = out.cpu().numpy().reshape(h, w, 3)
+    assert rel_l2(got, g.fourier_solve(full[0], wx, wy)) < 1e-12
+    if h * w <= 1080 * 1920:
+        assert rel_l2(got, cport.poisson(full[0], wx, wy)) < 1e-9      # gate: 1e-5
+
+
 def test_poisson_rejects_degenerate_sizes(g):
     u = np.zeros((1, 8, 3))
     with pytest.raises(g._capi.GdptError):
