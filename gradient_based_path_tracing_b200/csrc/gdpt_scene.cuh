@@ -78,6 +78,21 @@ template <typename R> struct Vertex {
 };
 
 struct Hit { float t, u, v; int shape_id, prim_id; };   // shape_id < 0: miss
+// The hit as it travels through HBM between the trace and the shade kernels: one aligned 32-byte sector, moved as
+// two 16-byte vectors (the sorted trace launch writes hits in scattered order; five 4-byte stores per ray into an
+// unaligned 20-byte slot cost five L2 write requests and straddle sectors)
+struct alignas(32) HitRec { float t, u, v; int shape_id; int prim_id, pad0, pad1, pad2; };
+GD_D void store_hit(HitRec *dst, const Hit &h) {
+    int4 *d = reinterpret_cast<int4 *>(dst);
+    d[0] = make_int4(__float_as_int(h.t), __float_as_int(h.u), __float_as_int(h.v), h.shape_id);
+    d[1] = make_int4(h.prim_id, 0, 0, 0);
+}
+GD_D Hit load_hit(const HitRec *src) {
+    const int4 *s = reinterpret_cast<const int4 *>(src);
+    int4 a = s[0]; int b = reinterpret_cast<const int *>(src)[4];
+    Hit h; h.t = __int_as_float(a.x); h.u = __int_as_float(a.y); h.v = __int_as_float(a.z); h.shape_id = a.w; h.prim_id = b;
+    return h;
+}
 
 // ---------------------------------------------------------------- camera
 template <typename R> GD_D V3<R> xform_point(const R *m, const V3<R> &p) {

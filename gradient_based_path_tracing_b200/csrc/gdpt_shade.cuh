@@ -75,14 +75,14 @@ GD_D bool start_iteration(const DScene<R> &sc, const Vertex<R> &vtx, const V3<R>
 
 // ---------------------------------------------------------------- primary stage
 template <typename R, int MS, int MINB = 1>
-__global__ void __launch_bounds__(128, MINB) k_primary(DScene<R> sc, WaveParams wp, const GenRec<R> *gen, const Hit *hits,
+__global__ void __launch_bounds__(128, MINB) k_primary(DScene<R> sc, WaveParams wp, const GenRec<R> *gen, const HitRec *hits,
                                                  PathRec<R> *out, OffRec<R> *off_out, RayF *rays_out, int *out_count) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     bool alive = false;
     PathRec<R> pr; OffRec<R> off; RayF ray;
     if (i < wp.n_paths) {
-        GenRec<R> g; load_rec(g, gen + i);
-        Hit h0 = hits[i];
+        GenRec<R> g; load_soa(g, gen, i, wp.n_paths);
+        Hit h0 = load_hit(hits + i);
         if (h0.shape_id >= 0) {   // inactive padding slots carry a ray that cannot hit
             const int ox[5] = {0, -1, 0, 1, 0}, oy[5] = {0, 0, 1, 0, -1};
             const R spread0 = R(0.25) / R(sc.width > sc.height ? sc.width : sc.height);   // init_ray_differential
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(128, MINB) k_primary(DScene<R> sc, WaveParams 
             off.enabled = 0; off.sampled = 0;
             for (int k = 0; k < 4; k++) {
                 off.contrib[k] = V3<R>(1, 1, 1); off.p2s[k] = R(1);
-                Hit hk = hits[(size_t)(k + 1) * wp.n_paths + i];
+                Hit hk = load_hit(hits + (size_t)(k + 1) * wp.n_paths + i);
                 if (hk.shape_id < 0) continue;
                 if (sc.shapes[hk.shape_id].material_id != vtx.material_id) continue;
                 V3<R> ok_, dk;
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(128, MINB) k_primary(DScene<R> sc, WaveParams 
         }
     }
     int slot = warp_slot(alive, out_count);
-    if (alive) { store_rec(out + slot, pr); store_rec(off_out + slot, off); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
+    if (alive) { store_soa(out, slot, wp.n_paths, pr); store_soa(off_out, slot, wp.n_paths, off); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
 }
 
 // ---------------------------------------------------------------- bounce stage
@@ -177,21 +177,21 @@ GD_D bool bounce_step(const DScene<R> &sc, const WaveParams &wp, PathRec<R> &pr,
 
 template <typename R, int MS, int MINB = 1>
 __global__ void __launch_bounds__(128, MINB) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
-                                                const Hit *hits, const int *in_count, int in_max,
+                                                const HitRec *hits, const int *in_count, int in_max,
                                                 PathRec<R> *out, RayF *rays_out, int *out_count) {
     int n = min(*in_count, in_max);
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     bool alive = false;
     PathRec<R> pr; RayF ray;
     if (i < n) {
-        load_rec(pr, in + i);
+        load_soa(pr, in, i, wp.n_paths);
         const bool first = off_in != nullptr;          // iteration with num_vertices == 3
-        OffRec<R> off; if (first) load_rec(off, off_in + i);
-        Hit h = hits[i];
+        OffRec<R> off; if (first) load_soa(off, off_in, i, wp.n_paths);
+        Hit h = load_hit(hits + i);
         alive = bounce_step<R, MS>(sc, wp, pr, first ? &off : nullptr, h, ray);
     }
     int slot = warp_slot(alive, out_count);
-    if (alive) { store_rec(out + slot, pr); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
+    if (alive) { store_soa(out, slot, wp.n_paths, pr); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
 }
 
 // ---------------------------------------------------------------- tail
@@ -205,9 +205,9 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_tail(DScene<R> sc, WaveParams w
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     PathRec<R> pr; RayF ray;
-    load_rec(pr, in + i); load_rec(ray, rays + i);
+    load_soa(pr, in, i, wp.n_paths); load_rec(ray, rays + i);
     bool first = off_in != nullptr;
-    OffRec<R> off; if (first) load_rec(off, off_in + i);
+    OffRec<R> off; if (first) load_soa(off, off_in, i, wp.n_paths);
     while (true) {
         Hit h; h.t = ray.tfar; h.u = h.v = 0.f; h.shape_id = -1; h.prim_id = -1;
         if (!(ray.tfar < ray.tnear)) {

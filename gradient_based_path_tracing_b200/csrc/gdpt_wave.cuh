@@ -18,13 +18,13 @@ constexpr int TRACE_DEFAULT_VARIANT = 0;
 constexpr int SORT_MIN_RAYS = 1 << 17;   // below this a launch is too small for the sort to pay
 
 template <bool EXACT, bool COUNT, int V>
-inline void launch_trace_v(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const int *order) {
+inline void launch_trace_v(gdpt_ctx *c, const RayF *rays, HitRec *hits, int n, const int *order) {
     int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
     k_trace<EXACT, COUNT, V><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, order, n, COUNT ? c->trav_counters.as<unsigned long long>() : nullptr);
 }
 
 template <bool EXACT>
-inline void launch_trace(gdpt_ctx *c, const RayF *rays, Hit *hits, int n, const int *order = nullptr) {
+inline void launch_trace(gdpt_ctx *c, const RayF *rays, HitRec *hits, int n, const int *order = nullptr) {
     if (n <= 0) return;
     if (c->count_traversal) launch_trace_v<EXACT, true, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
     else if constexpr (EXACT) launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, rays, hits, n, order);
@@ -44,7 +44,7 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     if (N <= 0) return 0;
     if (int r = c->gen.ensure((size_t)N * sizeof(GenRec<R>))) return r;
     if (int r = c->rays.ensure((size_t)N * 5 * sizeof(RayF))) return r;
-    if (int r = c->hits.ensure((size_t)N * 5 * sizeof(Hit))) return r;
+    if (int r = c->hits.ensure((size_t)N * 5 * sizeof(HitRec))) return r;
     if (int r = c->rec_a.ensure((size_t)N * sizeof(PathRec<R>))) return r;
     if (int r = c->rec_b.ensure((size_t)N * sizeof(PathRec<R>))) return r;
     if (int r = c->off.ensure((size_t)N * sizeof(OffRec<R>))) return r;
@@ -65,7 +65,7 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     int *cnt = c->counters.as<int>();
     const int n_bins = sorting ? sort_bins(c->sort_cell_bits, c->sort_dir_bits) : 0, n_chunks = std::max(1, n_bins / SORT_CHUNK);
     GenRec<R> *gen = c->gen.as<GenRec<R>>();
-    RayF *rays = c->rays.as<RayF>(); Hit *hits = c->hits.as<Hit>();
+    RayF *rays = c->rays.as<RayF>(); HitRec *hits = c->hits.as<HitRec>();
     PathRec<R> *cur = c->rec_a.as<PathRec<R>>(), *nxt = c->rec_b.as<PathRec<R>>();
     OffRec<R> *off = c->off.as<OffRec<R>>();
     cudaStream_t st = c->stream;

@@ -161,6 +161,24 @@ template <typename T> GD_D void store_rec(T *dst, const T &src) {
     for (int i = 0; i < (int)(sizeof(T) / 16); i++) d[i] = s[i];
 }
 
+// Queue records (PathRec, OffRec, GenRec) live in HBM as planes of 16-byte vectors: vector k of record i sits at
+// base[k*n + i] (n = slots in the wave), so a warp moving its 32 records issues fully coalesced 512-byte accesses
+// instead of 32 strided ones.  Rays stay AoS (32 B): the sorted trace launch gathers them one by one.
+template <typename T> GD_D void load_soa(T &dst, const T *base, int i, int n) {
+    static_assert(sizeof(T) % 16 == 0 && alignof(T) >= 16, "record must be a multiple of 16 bytes");
+    const int4 *s = reinterpret_cast<const int4 *>(base) + i;
+    int4 *d = reinterpret_cast<int4 *>(&dst);
+#pragma unroll
+    for (int k = 0; k < (int)(sizeof(T) / 16); k++) d[k] = s[(size_t)k * n];
+}
+template <typename T> GD_D void store_soa(T *base, int i, int n, const T &src) {
+    static_assert(sizeof(T) % 16 == 0 && alignof(T) >= 16, "record must be a multiple of 16 bytes");
+    int4 *d = reinterpret_cast<int4 *>(base) + i;
+    const int4 *s = reinterpret_cast<const int4 *>(&src);
+#pragma unroll
+    for (int k = 0; k < (int)(sizeof(T) / 16); k++) d[(size_t)k * n] = s[k];
+}
+
 GD_D int warp_slot(bool alive, int *counter) {
     unsigned mask = __ballot_sync(0xffffffffu, alive);
     int lane = threadIdx.x & 31;
@@ -193,13 +211,13 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
     }
     RayF r; r.ox = r.oy = r.oz = 0.f; r.dx = r.dy = r.dz = 0.f; r.tnear = 0.f; r.tfar = -1.f;   // tfar < tnear: never hits
     if (!active) {
-        store_rec(gen + i, g);
+        store_soa(gen, i, wp.n_paths, g);
         for (int k = 0; k < 5; k++) store_rec(rays + (size_t)k * wp.n_paths + i, r);
         return;
     }
     g.rng = pcg_init(stream, wp.seed);
     g.rng_x = pcg_real<R>(g.rng); g.rng_y = pcg_real<R>(g.rng);
-    store_rec(gen + i, g);
+    store_soa(gen, i, wp.n_paths, g);
     const int ox[5] = {0, -1, 0, 1, 0}, oy[5] = {0, 0, 1, 0, -1};   // base, X0=(x-1,y), Y0=(x,y+1), X1=(x+1,y), Y1=(x,y-1)
 #pragma unroll
     for (int k = 0; k < 5; k++) {
@@ -229,7 +247,7 @@ constexpr int trace_variant_depth(int v) { return ((v / 100) % 10) == 0 ? 20 : (
 constexpr int trace_variant_blocks(int v) { return ((v / 1000) % 10) == 0 ? 8 : ((v / 1000) % 10) == 1 ? 7 : ((v / 1000) % 10) == 2 ? 9 : 10; }
 
 template <bool EXACT, bool COUNT, int V>
-__global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(DBvh bvh, const RayF *rays, Hit *hits, const int *order, int count_max,
+__global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(DBvh bvh, const RayF *rays, HitRec *hits, const int *order, int count_max,
                                                                                unsigned long long *counters) {
     constexpr int SORT = V % 10, FMA = (V / 10) % 10, DEPTH = trace_variant_depth(V), LOOP = V / 10000;
     __shared__ int2 stack[DEPTH * TRACE_BLOCK];
@@ -249,7 +267,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(
                 if (cur < 0 && cur != TRACE_DONE) cur = trace_leaf<EXACT, (LOOP & 2) != 0>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
             }
         }
-        hits[i] = r.hit;
+        store_hit(hits + i, r.hit);
         if (COUNT) { tn += cn; tp += cp; }
     }
     if (COUNT) {
