@@ -9,6 +9,13 @@ namespace gdpt {
 template <typename R> int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp);
 extern template int run_wave<double>(gdpt_ctx *, DScene<double>, WaveParams);
 extern template int run_wave<float>(gdpt_ctx *, DScene<float>, WaveParams);
+template <typename R> int run_path_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp);
+extern template int run_path_wave<double>(gdpt_ctx *, DScene<double>, WaveParams);
+extern template int run_path_wave<float>(gdpt_ctx *, DScene<float>, WaveParams);
+template <typename R> int dbg_sample_light(gdpt_ctx *ctx, const DScene<R> &sc, int n, const double *ref_points, const double *rnd, double *out);
+extern template int dbg_sample_light<double>(gdpt_ctx *, const DScene<double> &, int, const double *, const double *, double *);
+extern template int dbg_sample_light<float>(gdpt_ctx *, const DScene<float> &, int, const double *, const double *, double *);
+int dbg_occluded(gdpt_ctx *ctx, bool exact, int n, const double *rays, int32_t *out);
 int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
 int merge_device(gdpt_ctx *ctx, int w, int h, int ya, int yb, const double *d_cx0, const double *d_cx1, const double *d_cy0, const double *d_cy1, double *d_cx, double *d_cy);
 int poisson_dist_rows_forward(gdpt_ctx *c, const gdpt_dist_geom *g, const double *d_u, const double *d_gx, const double *d_gy, double alpha,
@@ -54,7 +61,8 @@ template <typename R> DScene<R> &scene_of(gdpt_ctx *c);
 template <> DScene<double> &scene_of<double>(gdpt_ctx *c) { return c->sc_d; }
 template <> DScene<float> &scene_of<float>(gdpt_ctx *c) { return c->sc_f; }
 
-template <typename R>
+// PATH: the plain `path` integrator (one image) instead of gradpath (five)
+template <typename R, bool PATH = false>
 int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, double *d_cy0, double *d_cx1, double *d_cy1) {
     DScene<R> sc = scene_of<R>(c);
     sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth;
@@ -73,8 +81,13 @@ int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, dou
         long long n = wp.npix_pad * kk;
         if (n > 0x7fffffffLL / 8) return fail(GDPT_ERR_ARG, "wave too large");
         wp.n_paths = (int)n;
-        if (int rc = run_wave<R>(c, sc, wp)) return rc;
+        if (int rc = PATH ? run_path_wave<R>(c, sc, wp) : run_wave<R>(c, sc, wp)) return rc;
     }
+    return 0;
+}
+
+int path_supported(gdpt_ctx *c) {
+    if (c->has_envmap) return fail(GDPT_ERR_UNSUPPORTED, "the path integrator does not handle environment-map lights yet");
     return 0;
 }
 
@@ -276,6 +289,89 @@ int gdpt_render(gdpt_ctx *ctx, const gdpt_render_params *params, gdpt_images *ou
     cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]); ctx->stats.ms_poisson = ms;
     cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]); ctx->stats.ms_copy = ms;
     return 0;
+}
+
+/* path_render (render.cpp:74-117): host output */
+int gdpt_render_path(gdpt_ctx *ctx, const gdpt_render_params *params, double *out_image) {
+    Resolved r;
+    if (int rc = resolve(ctx, params, r)) return rc;
+    if (int rc = path_supported(ctx)) return rc;
+    GD_CUDA(cudaSetDevice(ctx->device));
+    if (int rc = ensure_images(ctx)) return rc;
+    const size_t bytes = (size_t)ctx->width * ctx->height * 3 * sizeof(double);
+    cudaStream_t st = ctx->stream;
+    ctx->stats.ms_trace = ctx->stats.ms_shade = 0;
+    GD_CUDA(cudaEventRecord(ctx->ev[0], st));
+    GD_CUDA(cudaMemsetAsync(ctx->img.p, 0, bytes, st));
+    int rc = r.precision == GDPT_PRECISION_F64 ? accumulate<double, true>(ctx, r, ctx->img.as<double>(), nullptr, nullptr, nullptr, nullptr)
+                                               : accumulate<float, true>(ctx, r, ctx->img.as<double>(), nullptr, nullptr, nullptr, nullptr);
+    if (rc) return rc;
+    GD_CUDA(cudaEventRecord(ctx->ev[1], st));
+    if (out_image) GD_CUDA(cudaMemcpyAsync(out_image, ctx->img.p, bytes, cudaMemcpyDeviceToHost, st));
+    GD_CUDA(cudaEventRecord(ctx->ev[3], st));
+    GD_CUDA(cudaStreamSynchronize(st));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]); ctx->stats.ms_total = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[3]); ctx->stats.ms_copy = ms;
+    ctx->stats.ms_poisson = 0;
+    return 0;
+}
+
+int gdpt_render_path_accumulate_device(gdpt_ctx *ctx, const gdpt_render_params *params, double *d_img) {
+    Resolved r;
+    if (int rc = resolve(ctx, params, r)) return rc;
+    if (int rc = path_supported(ctx)) return rc;
+    if (!d_img) return fail(GDPT_ERR_ARG, "null device image");
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return r.precision == GDPT_PRECISION_F64 ? accumulate<double, true>(ctx, r, d_img, nullptr, nullptr, nullptr, nullptr)
+                                             : accumulate<float, true>(ctx, r, d_img, nullptr, nullptr, nullptr, nullptr);
+}
+
+/* path_tracing (path_tracing.h:13-348) for n explicit (x, y, rng stream) triples; rad[n][3] */
+int gdpt_path_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, const int32_t *xs, const int32_t *ys,
+                      const uint64_t *streams, double *rad) {
+    Resolved r;
+    if (int rc = resolve(ctx, params, r)) return rc;
+    if (int rc = path_supported(ctx)) return rc;
+    if (!xs || !ys || !streams || !rad || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
+    if (n == 0) return 0;
+    for (int i = 0; i < n; i++) if (xs[i] < 0 || xs[i] >= ctx->width || ys[i] < 0 || ys[i] >= ctx->height) return fail(GDPT_ERR_ARG, "pixel %d out of range", i);
+    GD_CUDA(cudaSetDevice(ctx->device));
+    if (int rc = ctx->xs.ensure((size_t)n * 4)) return rc;
+    if (int rc = ctx->ys.ensure((size_t)n * 4)) return rc;
+    if (int rc = ctx->streams.ensure((size_t)n * 8)) return rc;
+    if (int rc = ctx->recout.ensure((size_t)n * 3 * 8)) return rc;
+    GD_CUDA(cudaMemcpy(ctx->xs.p, xs, (size_t)n * 4, cudaMemcpyHostToDevice));
+    GD_CUDA(cudaMemcpy(ctx->ys.p, ys, (size_t)n * 4, cudaMemcpyHostToDevice));
+    GD_CUDA(cudaMemcpy(ctx->streams.p, streams, (size_t)n * 8, cudaMemcpyHostToDevice));
+    GD_CUDA(cudaMemsetAsync(ctx->recout.p, 0, (size_t)n * 3 * 8, ctx->stream));
+    WaveParams wp; memset(&wp, 0, sizeof(wp));
+    wp.width = ctx->width; wp.height = ctx->height; wp.y0 = 0; wp.y1 = ctx->height; wp.tiles_x = (ctx->width + 7) / 8;
+    wp.n_paths = n; wp.npix_pad = n; wp.spp_total = 1; wp.seed = r.seed;
+    wp.xs = ctx->xs.as<int>(); wp.ys = ctx->ys.as<int>(); wp.streams = ctx->streams.as<unsigned long long>();
+    wp.rec_out = ctx->recout.as<double>();
+    int rc;
+    if (r.precision == GDPT_PRECISION_F64) { DScene<double> sc = ctx->sc_d; sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth; rc = run_path_wave<double>(ctx, sc, wp); }
+    else { DScene<float> sc = ctx->sc_f; sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth; rc = run_path_wave<float>(ctx, sc, wp); }
+    if (rc) return rc;
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    GD_CUDA(cudaMemcpy(rad, ctx->recout.p, (size_t)n * 3 * 8, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int gdpt_sample_light(gdpt_ctx *ctx, int precision, int n, const double *ref_points, const double *rnd, double *out) {
+    if (!ctx || !ref_points || !rnd || !out || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
+    if (int rc = path_supported(ctx)) return rc;
+    if (n == 0) return 0;
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return precision == GDPT_PRECISION_F64 ? dbg_sample_light<double>(ctx, ctx->sc_d, n, ref_points, rnd, out) : dbg_sample_light<float>(ctx, ctx->sc_f, n, ref_points, rnd, out);
+}
+
+int gdpt_occluded(gdpt_ctx *ctx, int precision, int n, const double *rays, int32_t *out) {
+    if (!ctx || !rays || !out || n < 0) return fail(GDPT_ERR_ARG, "bad argument");
+    if (n == 0) return 0;
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return dbg_occluded(ctx, precision == GDPT_PRECISION_F64, n, rays, out);
 }
 
 int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, const int32_t *xs, const int32_t *ys,

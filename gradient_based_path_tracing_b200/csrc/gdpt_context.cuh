@@ -64,6 +64,9 @@ struct gdpt_ctx {
     gdpt::DevBuf shapes, spheres, indices, materials, img3, img1;
     gdpt::DevBuf pos_d, nrm_d, uv_d, tex_d, texels3_d, texels1_d, light_d;   // exact mode
     gdpt::DevBuf pos_f, nrm_f, uv_f, tex_f, texels3_f, texels1_f, light_f;   // fast mode
+    gdpt::DevBuf lcdf_d, lcdf_f, lpmf_d, lpmf_f, tcdf_d, tcdf_f, area_d, area_f, lshape;   // light sampling tables (path integrator)
+    bool has_envmap = false;
+    gdpt::DevBuf shadow_rays, shadow_hits, prec_a, prec_b;                                  // path-integrator queues
     gdpt::DevBuf bvh_nodes, bvh_prims;
     gdpt::DScene<double> sc_d;
     gdpt::DScene<float> sc_f;
@@ -166,6 +169,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         DShape &ds = shapes[i];
         ds.kind = s[0]; ds.material_id = s[1]; ds.area_light_id = s[2]; ds.flags = s[5];
         ds.vtx_off = (int)o[0]; ds.tri_off = (int)o[1]; ds.nrm_off = (int)o[2]; ds.uv_off = (int)o[3];
+        ds.n_tris = s[4]; ds.cdf_off = -1;
         if (ds.material_id < 0 || ds.material_id >= d->n_materials) return fail(GDPT_ERR_ARG, "shape %d: material id %d out of range", i, ds.material_id);
         if (ds.area_light_id >= d->n_lights) return fail(GDPT_ERR_ARG, "shape %d: light id out of range", i);
         HostShape &h = hs[i];
@@ -260,6 +264,50 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     std::vector<double> li(3 * (size_t)std::max(d->n_lights, 1), 0.0);
     for (int i = 0; i < d->n_lights; i++) for (int k = 0; k < 3; k++) li[3 * i + k] = d->lights[5 * i + 2 + k];
     if (int r = upload(c->light_d, li)) return r; if (int r = upload(c->light_f, to_f(li))) return r;
+    {   // light sampling tables: init_sampling_dist of the emissive meshes (triangle_mesh.inl:60-75), light_power
+        // (diffuse_area_light.inl:1-3) and the light distribution (scene.cpp:46-52), all as make_table_dist_1d builds them
+        auto table = [](const std::vector<double> &f, std::vector<double> &pmf, std::vector<double> &cdf) {
+            pmf = f; cdf.assign(f.size() + 1, 0.0);
+            for (size_t i = 0; i < f.size(); i++) cdf[i + 1] = cdf[i] + pmf[i];
+            double total = cdf.back();
+            if (total > 0) { for (size_t i = 0; i < pmf.size(); i++) { pmf[i] /= total; cdf[i] /= total; } }   // the last cdf entry keeps the total
+            else { for (size_t i = 0; i < pmf.size(); i++) { pmf[i] = 1.0 / (double)pmf.size(); cdf[i] = (double)i / (double)pmf.size(); } if (!cdf.empty()) cdf.back() = 1; }
+        };
+        std::vector<double> tri_cdf, area(std::max(d->n_shapes, 1), 0.0);
+        for (int i = 0; i < d->n_shapes; i++) {
+            const HostShape &h = hs[i];
+            if (h.kind == 0) { area[i] = 4 * 3.14159265358979323846 * h.sphere[3] * h.sphere[3]; continue; }
+            if (shapes[i].area_light_id < 0) continue;
+            std::vector<double> ta(h.ntris), pm, cd; double total = 0;
+            for (int t = 0; t < h.ntris; t++) {
+                const double *v0 = h.positions + 3 * h.indices[3 * t], *v1 = h.positions + 3 * h.indices[3 * t + 1], *v2 = h.positions + 3 * h.indices[3 * t + 2];
+                double e1[3] = {v1[0] - v0[0], v1[1] - v0[1], v1[2] - v0[2]}, e2[3] = {v2[0] - v0[0], v2[1] - v0[1], v2[2] - v0[2]};
+                double cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+                ta[t] = sqrt(cx * cx + cy * cy + cz * cz) / 2; total += ta[t];
+            }
+            table(ta, pm, cd);
+            shapes[i].cdf_off = (int)tri_cdf.size(); area[i] = total;
+            tri_cdf.insert(tri_cdf.end(), cd.begin(), cd.end());
+        }
+        std::vector<double> power(d->n_lights), lpmf, lcdf; std::vector<int> lshape(std::max(d->n_lights, 1), -1);
+        c->has_envmap = false;
+        for (int i = 0; i < d->n_lights; i++) {
+            const double *l = d->lights + 5 * i;
+            if ((int)l[0] != 0) { c->has_envmap = true; power[i] = 0; continue; }
+            int sid = (int)l[1];
+            if (sid < 0 || sid >= d->n_shapes) return fail(GDPT_ERR_ARG, "light %d: shape id out of range", i);
+            lshape[i] = sid;
+            power[i] = (l[2] * 0.212671 + l[3] * 0.715160 + l[4] * 0.072169) * area[sid] * 3.14159265358979323846;
+        }
+        table(power, lpmf, lcdf);
+        if (lpmf.empty()) lpmf.push_back(0.0);
+        if (tri_cdf.empty()) tri_cdf.push_back(0.0);
+        if (int r = upload(c->lcdf_d, lcdf)) return r; if (int r = upload(c->lcdf_f, to_f(lcdf))) return r;
+        if (int r = upload(c->lpmf_d, lpmf)) return r; if (int r = upload(c->lpmf_f, to_f(lpmf))) return r;
+        if (int r = upload(c->tcdf_d, tri_cdf)) return r; if (int r = upload(c->tcdf_f, to_f(tri_cdf))) return r;
+        if (int r = upload(c->area_d, area)) return r; if (int r = upload(c->area_f, to_f(area))) return r;
+        if (int r = upload(c->lshape, lshape)) return r;
+    }
 
     lap("texel upload");
     bvh_thread.join();
@@ -296,6 +344,11 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     c->sc_d.texels3 = c->texels3_d.as<double>(); c->sc_d.texels1 = c->texels1_d.as<double>();
     c->sc_f.texels3 = c->texels3_f.as<float4>(); c->sc_f.texels1 = c->texels1_f.as<float>();
     c->sc_d.light_intensity = c->light_d.as<double>(); c->sc_f.light_intensity = c->light_f.as<float>();
+    c->sc_d.light_cdf = c->lcdf_d.as<double>(); c->sc_f.light_cdf = c->lcdf_f.as<float>();
+    c->sc_d.light_pmf = c->lpmf_d.as<double>(); c->sc_f.light_pmf = c->lpmf_f.as<float>();
+    c->sc_d.tri_cdf = c->tcdf_d.as<double>(); c->sc_f.tri_cdf = c->tcdf_f.as<float>();
+    c->sc_d.shape_area = c->area_d.as<double>(); c->sc_f.shape_area = c->area_f.as<float>();
+    c->sc_d.light_shape = c->sc_f.light_shape = c->lshape.as<int>();
     return 0;
 }
 
@@ -304,7 +357,7 @@ inline void destroy_context(gdpt_ctx *c) {
     cudaSetDevice(c->device);
     gdpt::DevBuf *all[] = {&c->shapes, &c->spheres, &c->indices, &c->materials, &c->img3, &c->img1, &c->pos_d, &c->nrm_d, &c->uv_d, &c->tex_d,
                            &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tex_f, &c->texels3_f, &c->texels1_f,
-                           &c->light_f, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
+                           &c->light_f, &c->lcdf_d, &c->lcdf_f, &c->lpmf_d, &c->lpmf_f, &c->tcdf_d, &c->tcdf_f, &c->area_d, &c->area_f, &c->lshape, &c->shadow_rays, &c->shadow_hits, &c->prec_a, &c->prec_b, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
                            &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
     for (auto *b : all) b->release();
     c->pc.release();

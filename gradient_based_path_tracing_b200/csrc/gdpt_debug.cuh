@@ -3,6 +3,7 @@
 // compare them one call at a time with the reference (oracle/ref.py).
 #pragma once
 #include "gdpt_shade.cuh"
+#include "gdpt_light.cuh"
 
 namespace gdpt {
 
@@ -75,6 +76,21 @@ static __global__ void k_fill_default_records(int n, double *rec) {
     double *o = rec + (size_t)i * 23;
     for (int k = 0; k < 18; k++) o[k] = 0.0;
     for (int k = 18; k < 23; k++) o[k] = 1.0;
+}
+
+// sample_light + sample_point_on_light + pdf_point_on_light + light_pmf (scene.cpp:61-67, light.cpp:57-71):
+// rnd[n][4] = light_w, uv0, uv1, shape_w; out[n][9] = light id, position3, normal3, pdf of the point, pmf of the light
+template <typename R>
+static __global__ void k_dbg_sample_light(DScene<R> sc, int n, const double *ref_points, const double *rnd, double *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    V3<R> ref((R)ref_points[3 * i], (R)ref_points[3 * i + 1], (R)ref_points[3 * i + 2]);
+    const double *q = rnd + 4 * i;
+    int id = sample_light<R>(sc, (R)q[0]);
+    LightPoint<R> p = sample_point_on_light<R>(sc, id, ref, (R)q[1], (R)q[2], (R)q[3]);
+    double *o = out + 9 * i;
+    o[0] = id; o[1] = p.position.x; o[2] = p.position.y; o[3] = p.position.z; o[4] = p.normal.x; o[5] = p.normal.y; o[6] = p.normal.z;
+    o[7] = pdf_point_on_light<R>(sc, id, p, ref); o[8] = light_pmf<R>(sc, id);
 }
 
 } // namespace gdpt

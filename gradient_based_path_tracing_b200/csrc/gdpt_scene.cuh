@@ -40,6 +40,7 @@ struct DMaterial {
 struct DShape {
     int kind, material_id, area_light_id, flags;   // flags: 1 = has normals, 2 = has uvs
     int vtx_off, tri_off, nrm_off, uv_off;
+    int n_tris, cdf_off;                           // triangles of the mesh; offset of its area CDF in tri_cdf (-1: not emissive)
 };
 
 // texel storage: exact mode keeps doubles (3 per RGB texel, 1 per scalar texel),
@@ -65,6 +66,13 @@ template <typename R> struct DScene {
     const typename TexelTypes<R>::T3 *texels3;
     const typename TexelTypes<R>::T1 *texels1;
     const R *light_intensity;     // [n_lights][3]
+    // light sampling tables (the `path` integrator; gdpt_light.cuh): TableDist1D over the light powers
+    // (scene.cpp:46-52), area CDFs of the emissive meshes (triangle_mesh.inl:60-75), total areas
+    const R *light_cdf;           // [n_lights + 1]
+    const R *light_pmf;           // [n_lights]
+    const int *light_shape;       // [n_lights] shape id, -1 for an environment map
+    const R *tri_cdf;             // pooled; DShape::cdf_off
+    const R *shape_area;          // [n_shapes] surface_area(shape)
     R eps;                        // get_intersection_epsilon (scene.h:104-106)
     int max_depth, rr_depth;
 };

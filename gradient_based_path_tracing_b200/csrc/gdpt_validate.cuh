@@ -60,4 +60,17 @@ template <typename R> int dbg_bsdf(gdpt_ctx *ctx, const DScene<R> &sc, int mat_i
     return 0;
 }
 
+template <typename R> int dbg_sample_light(gdpt_ctx *ctx, const DScene<R> &sc, int n, const double *ref_points, const double *rnd, double *out) {
+    if (sc.n_lights <= 0) return fail(GDPT_ERR_ARG, "the scene has no lights");
+    Scratch s; double *dp, *drn, *dout;
+    if (int r = s.put(&dp, ref_points, (size_t)n * 3)) return r;
+    if (int r = s.put(&drn, rnd, (size_t)n * 4)) return r;
+    if (int r = s.alloc(&dout, (size_t)n * 9)) return r;
+    k_dbg_sample_light<R><<<blocks_for(n, 128), 128, 0, ctx->stream>>>(sc, n, dp, drn, dout);
+    ctx->stats.kernel_launches++;
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    GD_CUDA(cudaMemcpy(out, dout, (size_t)n * 9 * sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 } // namespace gdpt

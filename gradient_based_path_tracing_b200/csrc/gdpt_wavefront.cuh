@@ -246,7 +246,8 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 constexpr int trace_variant_depth(int v) { return ((v / 100) % 10) == 0 ? 20 : ((v / 100) % 10) == 1 ? 16 : ((v / 100) % 10) == 2 ? 12 : 8; }
 constexpr int trace_variant_blocks(int v) { return ((v / 1000) % 10) == 0 ? 8 : ((v / 1000) % 10) == 1 ? 7 : ((v / 1000) % 10) == 2 ? 9 : 10; }
 
-template <bool EXACT, bool COUNT, int V>
+// ANY: occlusion query (rtcOccluded1, intersection.cpp:66-85): the walk stops at the first accepted hit.
+template <bool EXACT, bool COUNT, int V, bool ANY = false>
 __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(DBvh bvh, const RayF *rays, HitRec *hits, const int *order, int count_max,
                                                                                unsigned long long *counters) {
     constexpr int SORT = V % 10, FMA = (V / 10) % 10, DEPTH = trace_variant_depth(V), LOOP = V / 10000;
@@ -265,6 +266,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(
             while (cur != TRACE_DONE) {
                 if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA>(bvh, cur, r, st, sp); if ((LOOP & 1) == 0) continue; }
                 if (cur < 0 && cur != TRACE_DONE) cur = trace_leaf<EXACT, (LOOP & 2) != 0>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
+                if (ANY && r.hit.shape_id >= 0) break;
             }
         }
         store_hit(hits + i, r.hit);

@@ -58,8 +58,21 @@ def gradient_path_render(scene, device=0, outputs=("primal", "dx", "dy", "poisso
     return res
 
 
+def path_render(scene, device=0, **kw):
+    """path_render (render.cpp:74-117): the plain NEE + MIS path tracer, the metric's equal-time comparator.
+    Returns the (H, W, 3) image; scenes with an environment-map light raise GdptError (not built)."""
+    ctx = scene.context(device)
+    p = _params(scene, **kw)
+    img = np.zeros((scene.height, scene.width, 3), dtype=np.float64)
+    _capi.check(_capi.lib().gdpt_render_path(ctx, C.byref(p), _capi.as_dp(img)))
+    return img
+
+
 def render(scene, device=0, **kw):
-    """Image3 render(const Scene&): dispatch on scene.options.integrator; only GradPath lives here."""
+    """Image3 render(const Scene&) (render.cpp:373-395): dispatch on scene.options.integrator; GradPath and Path
+    live here, any other integrator ends like the reference's `assert(false)` arm."""
+    if scene.options.integrator == Integrator.Path:
+        return path_render(scene, device, **kw)
     if scene.options.integrator != Integrator.GradPath:
         raise AssertionError("render(): integrator %s is outside the gradpath hot path (render.cpp:390-393)" % scene.options.integrator.name)
     return gradient_path_render(scene, device, outputs=("poisson",), **kw)["poisson"]
@@ -117,6 +130,36 @@ def grad_samples(scene, xs, ys, streams, device=0, **kw):
     _capi.check(_capi.lib().gdpt_grad_samples(scene.context(device), C.byref(p), xs.size, xs.ctypes.data_as(_capi.ip),
                                               ys.ctypes.data_as(_capi.ip), st.ctypes.data_as(C.POINTER(C.c_uint64)), _capi.as_dp(rec)))
     return rec
+
+
+def path_samples(scene, xs, ys, streams, device=0, **kw):
+    """path_tracing (path_tracing.h:13-348) for explicit (x, y, rng stream) triples -> (n, 3) radiance."""
+    xs = np.ascontiguousarray(xs, dtype=np.int32)
+    ys = np.ascontiguousarray(ys, dtype=np.int32)
+    st = np.ascontiguousarray(streams, dtype=np.uint64)
+    rad = np.zeros((xs.size, 3))
+    p = _params(scene, **kw)
+    _capi.check(_capi.lib().gdpt_path_samples(scene.context(device), C.byref(p), xs.size, xs.ctypes.data_as(_capi.ip),
+                                              ys.ctypes.data_as(_capi.ip), st.ctypes.data_as(C.POINTER(C.c_uint64)), _capi.as_dp(rad)))
+    return rad
+
+
+def sample_light(scene, ref_points, rnd, precision="f64", device=0):
+    """sample_light + sample_point_on_light + pdf_point_on_light + light_pmf: rnd[n][4] = light_w, uv0, uv1, shape_w
+    -> (n, 9) = light id, position3, normal3, pdf of the point, pmf of the light."""
+    ref_points, rnd = _capi.f64(ref_points).reshape(-1, 3), _capi.f64(rnd).reshape(-1, 4)
+    out = np.zeros((ref_points.shape[0], 9))
+    _capi.check(_capi.lib().gdpt_sample_light(scene.context(device), _prec(precision), ref_points.shape[0], _capi.as_dp(ref_points),
+                                              _capi.as_dp(rnd), _capi.as_dp(out)))
+    return out
+
+
+def occluded(scene, rays, precision="f64", device=0):
+    """occluded (intersection.cpp:66-85): rays[n][8] = org, dir, tnear, tfar -> bool[n]."""
+    rays = _capi.f64(rays).reshape(-1, 8)
+    out = np.zeros(rays.shape[0], dtype=np.int32)
+    _capi.check(_capi.lib().gdpt_occluded(scene.context(device), _prec(precision), rays.shape[0], _capi.as_dp(rays), out.ctypes.data_as(_capi.ip)))
+    return out.astype(bool)
 
 
 def pcg_fill(stream, n, seed=_capi.DEFAULT_SEED, device=0):

@@ -172,6 +172,20 @@ int gdpt_bsdf(gdpt_ctx *ctx, int precision, int mat_id, int n, const double *vtx
  * rec[n][23] = radiance3, contrib3, contribX0 3, contribX1 3, contribY0 3, contribY1 3, prob, wX0, wY0, wX1, wY1 */
 int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, const int32_t *xs, const int32_t *ys,
                       const uint64_t *streams, double *rec);
+/* ---- the plain `path` integrator (render.cpp:74-117, path_tracing.h:13-348): NEE + MIS on the same kernels.
+ * Area lights (spheres, meshes); scenes with an environment-map light return GDPT_ERR_UNSUPPORTED. ---- */
+/* path_render end to end: out_image = W*H*3 doubles (host), the Image3 render() returns for Integrator::Path */
+int gdpt_render_path(gdpt_ctx *ctx, const gdpt_render_params *params, double *out_image);
+/* same accumulation into a caller-provided DEVICE image (already zeroed or holding earlier passes / other bands) */
+int gdpt_render_path_accumulate_device(gdpt_ctx *ctx, const gdpt_render_params *params, double *d_img);
+/* path_tracing for n explicit (x, y, rng stream) triples; rad[n][3] */
+int gdpt_path_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, const int32_t *xs, const int32_t *ys,
+                      const uint64_t *streams, double *rad);
+/* sample_light + sample_point_on_light + pdf_point_on_light + light_pmf (scene.cpp:61-67, light.cpp:57-71):
+ * ref_points[n][3]; rnd[n][4] = light_w, uv0, uv1, shape_w; out[n][9] = light id, position3, normal3, pdf, pmf */
+int gdpt_sample_light(gdpt_ctx *ctx, int precision, int n, const double *ref_points, const double *rnd, double *out);
+/* occluded (intersection.cpp:66-85): rays[n][8] = org, dir, tnear, tfar; out[n] = 1 if anything is hit in (tnear, tfar] */
+int gdpt_occluded(gdpt_ctx *ctx, int precision, int n, const double *rays, int32_t *out);
 /* PCG32 (pcg.h): first n doubles (and raw 32-bit outputs, may be NULL) of a stream, generated on the device */
 int gdpt_pcg_fill(int device, uint64_t stream, uint64_t seed, int n, double *out, uint32_t *raw);
 

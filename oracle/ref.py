@@ -47,6 +47,10 @@ def lib():
         L.gdpt_ref_intersect.argtypes = [C.c_void_p, C.c_int, dp, dp, ip, dp]
         L.gdpt_ref_bsdf.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp, dp, dp]
         L.gdpt_ref_export.argtypes = [C.c_void_p, C.c_char_p]
+        L.gdpt_ref_path_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, dp]
+        L.gdpt_ref_sample_light.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
+        L.gdpt_ref_occluded.argtypes = [C.c_void_p, C.c_int, dp, ip]
+        L.gdpt_ref_render_path_pixelseed.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, dp]
         _lib = L
     return _lib
 
@@ -198,6 +202,30 @@ class RefScene:
         out = np.zeros((vtx.shape[0], 10))
         lib().gdpt_ref_bsdf(self.h, mat_id, vtx.shape[0], _dp(vtx), _dp(dirs), _dp(rnd), _dp(out))
         return out
+
+    def path_sample(self, x, y, stream, seed=DEFAULT_SEED):
+        """One path_tracing evaluation (src/path_tracing.h:13-348) with rng = init_pcg32(stream, seed)."""
+        rad = np.zeros(3)
+        lib().gdpt_ref_path_sample(self.h, x, y, stream, seed, _dp(rad))
+        return rad
+
+    def render_path_pixelseed(self, spp, seed=DEFAULT_SEED, sample0=0):
+        img = self._img()
+        lib().gdpt_ref_render_path_pixelseed(self.h, seed, spp, sample0, _dp(img))
+        return img
+
+    def sample_light(self, ref_points, rnd):
+        ref_points = np.ascontiguousarray(ref_points, dtype=np.float64).reshape(-1, 3)
+        rnd = np.ascontiguousarray(rnd, dtype=np.float64).reshape(-1, 4)
+        out = np.zeros((ref_points.shape[0], 9))
+        lib().gdpt_ref_sample_light(self.h, ref_points.shape[0], _dp(ref_points), _dp(rnd), _dp(out))
+        return out
+
+    def occluded(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=np.float64).reshape(-1, 8)
+        out = np.zeros(rays.shape[0], dtype=np.int32)
+        lib().gdpt_ref_occluded(self.h, rays.shape[0], _dp(rays), out.ctypes.data_as(C.POINTER(C.c_int)))
+        return out.astype(bool)
 
     def export(self, path):
         if lib().gdpt_ref_export(self.h, os.path.abspath(path).encode()) != 0:

@@ -9,6 +9,7 @@
 //   render           src/render.cpp:374-394  (GradPath arm -> gradient_path_render :257-370)
 //   fourierSolve     src/render.cpp:172-254
 //   grad_path_tracing src/path_tracing.h:354-1050
+//   path_tracing     src/path_tracing.h:13-348; sample_light / sample_point_on_light / occluded (scene.cpp:61-67, light.cpp:57-71, intersection.cpp:66-85)
 //   sample_primary   src/camera.cpp:23-47
 //   intersect        src/intersection.cpp:7-65
 //   eval / pdf_sample_bsdf / sample_bsdf   src/material.cpp:90-119
@@ -33,6 +34,7 @@
 // cannot be included by a second translation unit)
 struct pcg32_state { uint64_t state; uint64_t inc; };
 GraidentPTRadiance grad_path_tracing(const Scene &scene, int x, int y, pcg32_state &rng);
+Spectrum path_tracing(const Scene &scene, int x, int y, pcg32_state &rng);   // src/path_tracing.h:13 (non-inline, defined in the render.cpp TU)
 void fourierSolve(int width, int height, const double *imgData, const double *imgGradX,
                   const double *imgGradY, double dataCost, double *imgOut);
 
@@ -203,6 +205,63 @@ void gdpt_ref_grad_sample(void *hs, int x, int y, uint64_t stream, uint64_t seed
     const Vector3 *v[6] = {&g.radiance, &g.contrib, &g.contribX0, &g.contribX1, &g.contribY0, &g.contribY1};
     for (int i = 0; i < 6; i++) { rec[3 * i] = v[i]->x; rec[3 * i + 1] = v[i]->y; rec[3 * i + 2] = v[i]->z; }
     rec[18] = g.prob; rec[19] = g.wX0; rec[20] = g.wY0; rec[21] = g.wX1; rec[22] = g.wY1;
+}
+
+// One path_tracing evaluation (src/path_tracing.h:13-348) with rng = init_pcg32(stream, seed). rad[3]
+void gdpt_ref_path_sample(void *hs, int x, int y, uint64_t stream, uint64_t seed, double *rad) {
+    Scene *s = (Scene *)hs;
+    gdpt_pcg32 r0; gdpt_oracle_pcg_init(&r0, stream, seed);
+    pcg32_state rng{r0.state, r0.inc};
+    Spectrum v = path_tracing(*s, x, y, rng);
+    rad[0] = v.x; rad[1] = v.y; rad[2] = v.z;
+}
+
+// sample_light + sample_point_on_light + pdf_point_on_light + light_pmf (src/scene.cpp:61-67, src/light.cpp:57-71)
+// rnd[n][4] = light_w, uv0, uv1, shape_w; out[n][9] = light id, position3, normal3, pdf of the point, pmf of the light
+void gdpt_ref_sample_light(void *hs, int n, const double *ref_points, const double *rnd, double *out) {
+    Scene *s = (Scene *)hs;
+    for (int i = 0; i < n; i++) {
+        Vector3 ref{ref_points[3 * i], ref_points[3 * i + 1], ref_points[3 * i + 2]};
+        const double *q = rnd + 4 * i;
+        int id = sample_light(*s, q[0]);
+        const Light &light = s->lights[id];
+        PointAndNormal p = sample_point_on_light(light, ref, Vector2{q[1], q[2]}, q[3], *s);
+        double *o = out + 9 * i;
+        o[0] = id; o[1] = p.position.x; o[2] = p.position.y; o[3] = p.position.z; o[4] = p.normal.x; o[5] = p.normal.y; o[6] = p.normal.z;
+        o[7] = pdf_point_on_light(light, p, ref, *s); o[8] = light_pmf(*s, id);
+    }
+}
+
+// occluded (src/intersection.cpp:66-85). rays[n][8] = org, dir, tnear, tfar; out[n]
+void gdpt_ref_occluded(void *hs, int n, const double *rays, int *out) {
+    Scene *s = (Scene *)hs;
+    for (int i = 0; i < n; i++) {
+        const double *q = rays + 8 * i;
+        Ray r{Vector3{q[0], q[1], q[2]}, Vector3{q[3], q[4], q[5]}, q[6], q[7]};
+        out[i] = occluded(*s, r) ? 1 : 0;
+    }
+}
+
+// Pixel-seeded path accumulation (stream = sample * W*H + y*W + x, like the GPU product): img = sum radiance / spp
+int gdpt_ref_render_path_pixelseed(void *hs, uint64_t seed, int spp, int sample0, double *img) {
+    Scene *s = (Scene *)hs;
+    const int w = s->camera.width, h = s->camera.height;
+    parallel_for([&](Vector2i rc) {
+        int y = rc[0];
+        for (int x = 0; x < w; x++) {
+            Vector3 r{0, 0, 0};
+            for (int k = 0; k < spp; k++) {
+                uint64_t stream = (uint64_t)(sample0 + k) * (uint64_t)w * h + (uint64_t)y * w + x;
+                gdpt_pcg32 r0; gdpt_oracle_pcg_init(&r0, stream, seed);
+                pcg32_state rng{r0.state, r0.inc};
+                r += path_tracing(*s, x, y, rng);
+            }
+            r = r / Real(spp);
+            size_t i = ((size_t)y * w + x) * 3;
+            img[i] = r.x; img[i + 1] = r.y; img[i + 2] = r.z;
+        }
+    }, Vector2i(h, 1));
+    return 0;
 }
 
 // Pixel-seeded gradpath accumulation: every (pixel, sample) gets its own stream

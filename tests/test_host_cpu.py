@@ -82,7 +82,7 @@ def test_shipped_scene_containers_match_baseline_configs(g, name, size, spp):
 
 def test_render_rejects_other_integrators(g):
     sc = g.Scene.named("cbox_gdpt_64")
-    sc.options.integrator = g.Integrator.Path
+    sc.options.integrator = g.Integrator.VolPath       # Path and GradPath are built; the rest ends like render.cpp:390-393
     with pytest.raises(AssertionError):
         g.render(sc)
 
