@@ -193,4 +193,34 @@ __global__ void __launch_bounds__(128) k_path_shade(DScene<R> sc, WaveParams wp,
     if (alive) { store_soa(out, slot, wp.n_paths, ps); store_rec(rays_out + slot, ray); store_rec(shadow_out + slot, shadow); sort_emit(wp, slot, ray); }
 }
 
+// Last paths of a wave: walked to their end in one launch (both ray casts and the shading in the same thread), like
+// k_tail does for gradpath — the per-bounce launches and count read-backs cost more than the work left in them.
+template <typename R, int MS, bool EXACT>
+__global__ void __launch_bounds__(TRACE_BLOCK) k_path_tail(DScene<R> sc, WaveParams wp, DBvh bvh, const PathState<R> *in, const RayF *rays, const RayF *shadows, int n) {
+    __shared__ int2 stack[STACK_SMEM * TRACE_BLOCK];
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    PathState<R> ps; RayF ray, shadow;
+    load_soa(ps, in, i, wp.n_paths); load_rec(ray, rays + i); load_rec(shadow, shadows + i);
+    while (true) {
+        Hit h; h.t = ray.tfar; h.u = h.v = 0.f; h.shape_id = -1; h.prim_id = -1;
+        if (!(ray.tfar < ray.tnear)) {
+            const float o[3] = {ray.ox, ray.oy, ray.oz}, d[3] = {ray.dx, ray.dy, ray.dz};
+            h = trace_closest<EXACT, false>(bvh, o, d, ray.tnear, ray.tfar, stack);
+        }
+        const bool shadow_traced = !(shadow.tfar < shadow.tnear);
+        bool occluded = false;
+        if (shadow_traced) {
+            const float o[3] = {shadow.ox, shadow.oy, shadow.oz}, d[3] = {shadow.dx, shadow.dy, shadow.dz};
+            occluded = trace_occluded<EXACT>(bvh, o, d, shadow.tnear, shadow.tfar, stack);
+        }
+        Vertex<R> nv;
+        V3<R> dir_in = ps.dir;
+        bool alive = path_finish_iteration<R, MS>(sc, ps, shadow_traced, occluded, h, nv);
+        if (alive) alive = path_begin_iteration<R, MS>(sc, nv, dir_in, ps, ray, shadow);
+        if (!alive) break;
+    }
+    path_finish<R>(wp, ps);
+}
+
 } // namespace gdpt

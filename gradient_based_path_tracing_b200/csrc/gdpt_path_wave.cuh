@@ -7,10 +7,10 @@
 namespace gdpt {
 
 template <bool EXACT>
-inline void launch_trace_any(gdpt_ctx *c, const RayF *rays, HitRec *hits, int n) {
+inline void launch_trace_any(gdpt_ctx *c, const RayF *rays, HitRec *hits, int n, const int *order) {
     if (n <= 0) return;
     int grid = std::min(blocks_for(n, TRACE_BLOCK), SM_COUNT * 16);
-    k_trace<EXACT, false, TRACE_DEFAULT_VARIANT, true><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, nullptr, n, nullptr);
+    k_trace<EXACT, false, TRACE_DEFAULT_VARIANT, true><<<grid, TRACE_BLOCK, 0, c->stream>>>(c->bvh, rays, hits, order, n, nullptr);
     c->stats.kernel_launches++; c->stats.rays_traced += n;
 }
 
@@ -70,6 +70,15 @@ int run_path_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     std::swap(cur, nxt);
     int which = 0;
     while (count > 0) {
+        if (count <= c->tail_paths) {   // few paths left: finish them in one launch
+            GD_CUDA(cudaEventRecord(e0, st));
+            k_path_tail<R, MS, ModeSel<R>::exact><<<blocks_for(count, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(sc, wp, c->bvh, cur, rays, shadow, count);
+            GD_CUDA(cudaEventRecord(e1, st));
+            c->stats.kernel_launches++; c->stats.tail_paths += count;
+            GD_CUDA(cudaEventSynchronize(e1));
+            cudaEventElapsedTime(&ms, e0, e1); c->stats.ms_shade += ms;
+            break;
+        }
         GD_CUDA(cudaEventRecord(e0, st));
         const int *order = nullptr;
         if (sorting && count >= SORT_MIN_RAYS) {
@@ -80,7 +89,8 @@ int run_path_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
             order = c->sort_order.as<int>();
         }
         launch_trace<ModeSel<R>::exact>(c, rays, hits, count, order);
-        launch_trace_any<ModeSel<R>::exact>(c, shadow, shadow_hits, count);
+        // shadow rays leave from the same vertices as the BSDF rays: the permutation sorted by origin cell serves both
+        launch_trace_any<ModeSel<R>::exact>(c, shadow, shadow_hits, count, order);
         GD_CUDA(cudaEventRecord(e1, st));
         if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)n_bins * sizeof(int), st));
         int *cin = cnt + which, *cout = cnt + (which ^ 1);

@@ -219,4 +219,19 @@ GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], floa
     return r.hit;
 }
 
+// Occlusion query for one ray (rtcOccluded1): stops at the first accepted hit.
+template <bool EXACT>
+GD_D bool trace_occluded(const DBvh &bvh, const float o[3], const float d[3], float tnear, float tfar, int2 *smem_stack) {
+    RayState r; r.init(make_float4(o[0], o[1], o[2], tnear), make_float4(d[0], d[1], d[2], tfar));
+    if (bvh.n_nodes == 0) return false;
+    TraceStack st; st.smem = smem_stack;
+    int sp = 0, cur = 0;
+    while (cur != TRACE_DONE) {
+        while (cur >= 0) cur = trace_node<0, 0>(bvh, cur, r, st, sp);
+        if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, nullptr);
+        if (r.hit.shape_id >= 0) return true;
+    }
+    return false;
+}
+
 } // namespace gdpt

@@ -5,7 +5,7 @@
 // C ABI of include/gdpt.h.  Writes the Poisson reconstruction to the -o file like the reference,
 // plus <stem>_primal / <stem>_dx / <stem>_dy (SURVEY.md 8b "Outputs on disk").
 //
-//   lajolla_b200 [-o out.pfm] [-overlay camera.gdpt] [-spp N] [-precision f32|f64] [-device D] [-seed S] scene.gdpt[.z] ...
+//   lajolla_b200 [-o out.pfm] [-overlay camera.gdpt] [-spp N] [-precision f32|f64] [-integrator path|gradpath] [-device D] [-seed S] scene.gdpt[.z] ...
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -63,6 +63,7 @@ int main(int argc, char *argv[]) {
     std::string outputfile, overlay, precision = "f32";
     int spp = 0, device = 0; unsigned long long seed = 0;
     bool describe = false;
+    int integrator_override = -1;   // Integrator enum value (src/scene.h:14-23): 5 Path, 7 GradPath
     std::vector<std::string> filenames;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
@@ -74,6 +75,7 @@ int main(int argc, char *argv[]) {
         else if (a == "-precision") precision = value();
         else if (a == "-device") device = std::stoi(value());
         else if (a == "-seed") seed = std::stoull(value());
+        else if (a == "-integrator") { std::string v = value(); if (v == "path") integrator_override = 5; else if (v == "gradpath") integrator_override = 7; else { std::cerr << "-integrator must be path or gradpath" << std::endl; return 2; } }
         else if (a == "-describe") describe = true;             // print a digest of the flattened scene and exit (no device needed)
         else filenames.push_back(a);
     }
@@ -89,7 +91,8 @@ int main(int argc, char *argv[]) {
         FlatScene scene;
         if (err.empty()) err = scene.build(c);
         if (!err.empty()) { std::cerr << err << std::endl; return 1; }
-        if (scene.integrator != 7) {   // render() asserts on integrators it does not know (render.cpp:390-393); only GradPath lives here
+        if (integrator_override >= 0) scene.integrator = integrator_override;
+        if (scene.integrator != 7 && scene.integrator != 5) {   // render() asserts on integrators it does not know (render.cpp:390-393); GradPath and Path live here
             std::cerr << "integrator " << scene.integrator << " is outside the gradpath hot path" << std::endl;
             return 1;
         }
@@ -106,14 +109,17 @@ int main(int argc, char *argv[]) {
         p.max_depth = -2; p.rr_depth = -2; p.seed = seed; p.data_cost = 0.04;
         p.precision = precision == "f64" ? GDPT_PRECISION_F64 : GDPT_PRECISION_F32;
         gdpt_images img{primal.data(), dx.data(), dy.data(), out.data()};
-        int rc = gdpt_render(ctx, &p, &img);
+        const bool path = scene.integrator == 5;          // Integrator::Path -> path_render (render.cpp:385-386): one image
+        int rc = path ? gdpt_render_path(ctx, &p, out.data()) : gdpt_render(ctx, &p, &img);
         gdpt_stats st{};
         gdpt_get_stats(ctx, &st);
         gdpt_destroy(ctx);
         if (rc != GDPT_OK) { std::cerr << gdpt_last_error() << std::endl; return 1; }
         double took = seconds_since(timer);
         std::cout << "Done. Took " << took << " seconds." << std::endl;
-        std::printf("%.1f Mpaths/s (base + 4 shifts; %d spp, %lld kernel launches, trace %.1f ms, shade %.1f ms, Poisson %.1f ms, copies %.1f ms)\n",
+        if (path) std::printf("%.1f Mpaths/s (path, NEE + MIS; %d spp, %lld kernel launches, trace %.1f ms, shade %.1f ms, copies %.1f ms)\n",
+                              1.0 * w * h * p.spp / took / 1e6, p.spp, (long long)st.kernel_launches, st.ms_trace, st.ms_shade, st.ms_copy);
+        else std::printf("%.1f Mpaths/s (base + 4 shifts; %d spp, %lld kernel launches, trace %.1f ms, shade %.1f ms, Poisson %.1f ms, copies %.1f ms)\n",
                     5.0 * w * h * p.spp / took / 1e6, p.spp, (long long)st.kernel_launches, st.ms_trace, st.ms_shade, st.ms_poisson, st.ms_copy);
 
         std::string of = outputfile.empty() ? "image.pfm" : outputfile;   // the reference's default film name is image.exr; EXR needs tinyexr, so PFM here
@@ -121,6 +127,7 @@ int main(int argc, char *argv[]) {
         std::string stem = of.substr(0, of.size() - 4);
         const std::pair<std::string, const double *> files[] = {{of, out.data()}, {stem + "_primal.pfm", primal.data()}, {stem + "_dx.pfm", dx.data()}, {stem + "_dy.pfm", dy.data()}};
         for (const auto &f : files) {
+            if (path && f.second != out.data()) continue;
             err = write_pfm(f.first, w, h, f.second);
             if (!err.empty()) { std::cerr << err << std::endl; return 1; }
         }

@@ -371,3 +371,19 @@ def test_cpp_host_cli_writes_the_same_images(g, scenes, tmp_path):
     for suffix, img in (("", want.poisson), ("_primal", want.primal), ("_dx", want.dx), ("_dy", want.dy)):
         got = _read_pfm(str(out)[:-4] + suffix + ".pfm")
         assert np.allclose(got, img.astype(np.float32), rtol=1e-6, atol=1e-9), suffix
+
+
+def test_cpp_host_cli_path_integrator(g, scenes, tmp_path):
+    """`-integrator path` (Integrator::Path, render.cpp:385-386): one image, equal to path_render of the Python host."""
+    import os
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "lajolla_b200")
+    out = tmp_path / "cbp.pfm"
+    r = subprocess.run([exe, "-o", str(out), "-spp", "2", "-precision", "f64", "-integrator", "path",
+                        os.path.join(ROOT, "scenes", "cbox_gdpt_64.gdpt.z")], capture_output=True, timeout=600)
+    assert r.returncode == 0, r.stderr.decode()
+    assert "Image written to " + str(out) in r.stdout.decode()
+    want = g.path_render(scenes("cbox_gdpt_64"), spp=2, precision="f64")
+    assert np.allclose(_read_pfm(str(out)), want.astype(np.float32), rtol=1e-6, atol=1e-9)
+    assert not os.path.exists(str(out)[:-4] + "_dx.pfm")

@@ -103,3 +103,30 @@ def test_path_refuses_environment_maps(g, scenes):
     sc = scenes("disney_small")
     with pytest.raises(g._capi.GdptError):
         g.path_render(sc, spp=1)
+
+
+@pytest.mark.parametrize("name", ["cbox_gdpt_64", "veach_mi_small"])
+def test_path_queues_and_tail_kernel_agree(g, name, monkeypatch):
+    """Per-bounce queue kernels (k_trace closest + any-hit, k_path_shade; with and without ray sorting) and the
+    single-launch k_path_tail are the same arithmetic: FP64 records agree bit for bit with each other and the reference."""
+    z = golden("path_%s.npz" % name)
+    out = {}
+    for tag, env in (("tail", {"GDPT_TAIL_PATHS": str(1 << 30)}), ("queues", {"GDPT_TAIL_PATHS": "0"})):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        sc = g.Scene.named(name)
+        out[tag] = g.path_samples(sc, z["xs"], z["ys"], z["streams"], precision="f64")
+        sc.close()
+    assert np.array_equal(out["tail"], out["queues"])
+    bad = (np.abs(out["queues"] - z["rad"]) > 1e-9 * (1 + np.abs(z["rad"]))).any(axis=1)
+    assert bad.sum() <= 6
+    imgs = {}
+    for tag, env in (("sorted", {"GDPT_TAIL_PATHS": "0", "GDPT_SORT_RAYS": "1"}), ("plain", {"GDPT_TAIL_PATHS": "0", "GDPT_SORT_RAYS": "0"}),
+                     ("tail", {"GDPT_TAIL_PATHS": str(1 << 30), "GDPT_SORT_RAYS": "0"})):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        sc = g.Scene.named("cbox_gdpt")
+        imgs[tag] = g.path_render(sc, spp=1, precision="f64")
+        sc.close()
+    for tag in ("plain", "tail"):
+        assert np.allclose(imgs["sorted"], imgs[tag], rtol=1e-9, atol=1e-12), tag
