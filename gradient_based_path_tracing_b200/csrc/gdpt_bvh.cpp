@@ -5,6 +5,8 @@
 #include "gdpt_bvh.h"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <atomic>
 #include <cmath>
 #include <cstdlib>
@@ -31,13 +33,16 @@ struct BNode { Box b; int left = -1, right = -1, first = 0, count = 0; };
 
 struct Builder {
     std::vector<Ref> refs;
-    std::vector<BNode> nodes;          // preallocated (2n); slots handed out by `next` so subtrees can be built concurrently
-    std::atomic<int> next{0};
+    std::vector<BNode> nodes;          // preallocated (2n)
     double ci = 1.0;      // SAH cost of one primitive test relative to one (binary) node step
     int max_leaf = 4;     // <= 7 (3-bit count in the leaf encoding)
-    int fork_levels = 0;  // subtrees down to this depth are built on their own threads
+    std::atomic<int> workers{0};   // extra build threads alive
+    int max_workers = 0;
 
-    int build(int first, int count, int depth = 0) {
+    // Node slots are handed out by position, not by a shared counter: the subtree over `count` references owns the
+    // slots [slot, slot + 2*count - 1), its root sits at `slot`, the left child's range follows, then the right
+    // child's.  Concurrent subtrees therefore never touch the same cache lines, and the layout is deterministic.
+    int build(int first, int count, int slot, int depth = 0) {
         BNode n; n.b.reset();
         Box cb; cb.reset();
         for (int i = first; i < first + count; i++) {
@@ -45,25 +50,30 @@ struct Builder {
             for (int k = 0; k < 3; k++) { cb.lo[k] = std::min(cb.lo[k], refs[i].c[k]); cb.hi[k] = std::max(cb.hi[k], refs[i].c[k]); }
         }
         n.first = first; n.count = count;
-        int id = next.fetch_add(1);
+        const int id = slot;
         nodes[id] = n;
         if (count <= 1) return id;
-        const int NB = 16;
+        // 16 bins per axis; small nodes (most of the tree) use fewer, their cost is the bin bookkeeping, not the references
+        constexpr int NBMAX = 16;
+        const int NB = count > 32 ? 16 : (count > 8 ? 8 : 4);
+        // one pass over the references fills the bins of all three axes
+        float scale[3]; bool live[3];
+        for (int ax = 0; ax < 3; ax++) { float ext = cb.hi[ax] - cb.lo[ax]; live[ax] = ext > 0.f; scale[ax] = live[ax] ? (float)NB / ext : 0.f; }
+        auto bin_of = [&](const Ref &r, int ax) { int b = (int)((r.c[ax] - cb.lo[ax]) * scale[ax]); return b < 0 ? 0 : (b > NB - 1 ? NB - 1 : b); };
+        int cnt[3][NBMAX]; Box bb[3][NBMAX];
+        for (int ax = 0; ax < 3; ax++) for (int b = 0; b < NB; b++) { cnt[ax][b] = 0; bb[ax][b].reset(); }
+        for (int i = first; i < first + count; i++) {
+            const Ref &r = refs[i];
+            for (int ax = 0; ax < 3; ax++) { int b = bin_of(r, ax); cnt[ax][b]++; bb[ax][b].grow(r.b); }
+        }
         double best = std::numeric_limits<double>::infinity(); int bax = -1, bbin = -1;
         for (int ax = 0; ax < 3; ax++) {
-            double ext = (double)cb.hi[ax] - cb.lo[ax];
-            if (!(ext > 0)) continue;
-            int cnt[NB] = {0}; Box bb[NB];
-            for (int b = 0; b < NB; b++) bb[b].reset();
-            for (int i = first; i < first + count; i++) {
-                int b = std::min(NB - 1, (int)(NB * ((double)refs[i].c[ax] - cb.lo[ax]) / ext));
-                cnt[b]++; bb[b].grow(refs[i].b);
-            }
-            double ra[NB]; int rc[NB]; Box acc; acc.reset(); int c = 0;
-            for (int b = NB - 1; b > 0; b--) { c += cnt[b]; acc.grow(bb[b]); ra[b] = acc.area(); rc[b] = c; }
+            if (!live[ax]) continue;
+            double ra[NBMAX]; int rc[NBMAX]; Box acc; acc.reset(); int c = 0;
+            for (int b = NB - 1; b > 0; b--) { c += cnt[ax][b]; acc.grow(bb[ax][b]); ra[b] = acc.area(); rc[b] = c; }
             acc.reset(); c = 0;
             for (int b = 0; b < NB - 1; b++) {
-                c += cnt[b]; acc.grow(bb[b]);
+                c += cnt[ax][b]; acc.grow(bb[ax][b]);
                 if (c == 0 || rc[b + 1] == 0) continue;
                 double cost = acc.area() * c + ra[b + 1] * rc[b + 1];
                 if (cost < best) { best = cost; bax = ax; bbin = b; }
@@ -77,22 +87,23 @@ struct Builder {
             // leaf cost vs split cost (traversal cost 1, intersection cost 1 per primitive)
             double leaf = n.b.area() * count * ci, split = n.b.area() * 1.0 + best * ci;
             if (count <= max_leaf && leaf <= split) return id;
-            double ext = (double)cb.hi[bax] - cb.lo[bax];
-            auto it = std::partition(refs.begin() + first, refs.begin() + first + count, [&](const Ref &r) {
-                int b = std::min(NB - 1, (int)(NB * ((double)r.c[bax] - cb.lo[bax]) / ext));
-                return b <= bbin;
-            });
+            auto it = std::partition(refs.begin() + first, refs.begin() + first + count, [&](const Ref &r) { return bin_of(r, bax) <= bbin; });
             mid = (int)(it - refs.begin());
             if (mid == first || mid == first + count) mid = first + count / 2;
         }
+        const int lc = mid - first, lslot = slot + 1, rslot = slot + 2 * lc;
         int l, r;
-        if (depth < fork_levels && count > 8192) {   // disjoint reference ranges, disjoint node slots: no sharing between the two halves
-            std::thread th([&] { l = build(first, mid - first, depth + 1); });
-            r = build(mid, first + count - mid, depth + 1);
+        // SAH splits of real scenes are lopsided (Sponza's first cuts peel off walls with a few percent of the
+        // triangles), so forking by depth leaves one thread with nearly everything: fork wherever BOTH halves are
+        // still large, as long as a worker slot is free.  Disjoint reference ranges, disjoint node slots.
+        if (std::min(lc, count - lc) > 4096 && workers.fetch_add(1) < max_workers) {
+            std::thread th([&] { l = build(first, lc, lslot, depth + 1); workers.fetch_sub(1); });
+            r = build(mid, count - lc, rslot, depth + 1);
             th.join();
         } else {
-            l = build(first, mid - first, depth + 1);
-            r = build(mid, first + count - mid, depth + 1);
+            if (std::min(lc, count - lc) > 4096) workers.fetch_sub(1);
+            l = build(first, lc, lslot, depth + 1);
+            r = build(mid, count - lc, rslot, depth + 1);
         }
         nodes[id].left = l; nodes[id].right = r; nodes[id].count = 0;
         return id;
@@ -120,14 +131,9 @@ inline void clip_poly(const Poly &in, int axis, double plane, bool keep_below, P
     }
 }
 
-// tight float box of (triangle ∩ box), rounded outwards; false if empty
-inline bool clipped_box(const float tri[3][3], const Box &box, Box &out) {
-    Poly p, q; p.n = 3;
-    for (int c = 0; c < 3; c++) for (int k = 0; k < 3; k++) p.v[c][k] = tri[c][k];
-    for (int ax = 0; ax < 3; ax++) {
-        clip_poly(p, ax, (double)box.lo[ax], false, q); if (q.n == 0) return false;
-        clip_poly(q, ax, (double)box.hi[ax], true, p); if (p.n == 0) return false;
-    }
+// tight float box of a clipped polygon, rounded outwards and kept inside `box`; false if empty
+inline bool poly_box(const Poly &p, const Box &box, Box &out) {
+    if (p.n == 0) return false;
     const float inf = std::numeric_limits<float>::infinity();
     for (int k = 0; k < 3; k++) {
         double lo = p.v[0][k], hi = p.v[0][k];
@@ -142,42 +148,70 @@ inline bool clipped_box(const float tri[3][3], const Box &box, Box &out) {
     return true;
 }
 
-// Split the largest boxes first until the reference count reaches `budget`.
+// Split the largest boxes first until the reference count reaches `budget`.  Every reference that has been cut
+// carries the polygon (triangle ∩ its box) it covers, so a cut is one clip per side instead of re-clipping the
+// triangle against all six planes of each half.
 inline void presplit(std::vector<Ref> &refs, const std::vector<BvhPrim> &src, size_t budget) {
-    auto cmp = [&](int a, int b) { return refs[a].b.area() < refs[b].b.area(); };
-    std::vector<int> heap;
-    for (int i = 0; i < (int)refs.size(); i++) if (src[refs[i].idx].kind == 0) heap.push_back(i);
-    std::make_heap(heap.begin(), heap.end(), cmp);
+    // heap entries carry their key (area, then index for a deterministic order): comparing through refs[] would be
+    // two cache misses per comparison
+    typedef std::pair<double, int> Entry;
+    std::vector<Entry> heap;
+    for (int i = 0; i < (int)refs.size(); i++) if (src[refs[i].idx].kind == 0) heap.push_back(Entry(refs[i].b.area(), i));
+    std::make_heap(heap.begin(), heap.end());
+    auto push = [&](int i) { heap.push_back(Entry(refs[i].b.area(), i)); std::push_heap(heap.begin(), heap.end()); };
+    std::vector<Poly> polys;                       // polygon of reference i at poly_of[i] (or -1: still the whole triangle)
+    std::vector<int> poly_of(refs.size(), -1);
+    polys.reserve(budget > refs.size() ? 2 * (budget - refs.size()) + 16 : 16);
+    refs.reserve(budget + 1); poly_of.reserve(budget + 1);
     while (!heap.empty() && refs.size() < budget) {
-        std::pop_heap(heap.begin(), heap.end(), cmp);
-        int i = heap.back(); heap.pop_back();
+        std::pop_heap(heap.begin(), heap.end());
+        int i = heap.back().second; heap.pop_back();
         Ref r = refs[i];
         int ax = 0; float ext = r.b.hi[0] - r.b.lo[0];
         for (int k = 1; k < 3; k++) if (r.b.hi[k] - r.b.lo[k] > ext) { ext = r.b.hi[k] - r.b.lo[k]; ax = k; }
         if (!(ext > 0.f)) break;      // the largest box is a point: nothing left to split
         float mid = 0.5f * (r.b.lo[ax] + r.b.hi[ax]);
         if (!(mid > r.b.lo[ax] && mid < r.b.hi[ax])) continue;
-        const BvhPrim &p = src[r.idx];
-        const float tri[3][3] = {{p.v0[0], p.v0[1], p.v0[2]}, {p.v1[0], p.v1[1], p.v1[2]}, {p.v2[0], p.v2[1], p.v2[2]}};
+        Poly whole;
+        if (poly_of[i] < 0) {
+            const BvhPrim &p = src[r.idx];
+            whole.n = 3;
+            for (int k = 0; k < 3; k++) { whole.v[0][k] = p.v0[k]; whole.v[1][k] = p.v1[k]; whole.v[2][k] = p.v2[k]; }
+        } else whole = polys[poly_of[i]];
+        Poly pl, pr;
+        clip_poly(whole, ax, (double)mid, true, pl);
+        clip_poly(whole, ax, (double)mid, false, pr);
         Box lb = r.b, rb = r.b; lb.hi[ax] = mid; rb.lo[ax] = mid;
         Box lt, rt;
-        bool hl = clipped_box(tri, lb, lt), hr = clipped_box(tri, rb, rt);
+        bool hl = poly_box(pl, lb, lt), hr = poly_box(pr, rb, rt);
         if (!hl || !hr) {             // the triangle only touches one half: just tighten
-            if (hl || hr) { refs[i].b = hl ? lt : rt; for (int k = 0; k < 3; k++) refs[i].c[k] = 0.5f * (refs[i].b.lo[k] + refs[i].b.hi[k]); }
+            if (hl || hr) {
+                refs[i].b = hl ? lt : rt; for (int k = 0; k < 3; k++) refs[i].c[k] = 0.5f * (refs[i].b.lo[k] + refs[i].b.hi[k]);
+                if (poly_of[i] < 0) { poly_of[i] = (int)polys.size(); polys.push_back(hl ? pl : pr); } else polys[poly_of[i]] = hl ? pl : pr;
+                if (refs[i].b.area() < r.b.area()) push(i);
+            }
             continue;
         }
         Ref a = r, b = r;
         a.b = lt; b.b = rt;
         for (int k = 0; k < 3; k++) { a.c[k] = 0.5f * (lt.lo[k] + lt.hi[k]); b.c[k] = 0.5f * (rt.lo[k] + rt.hi[k]); }
         refs[i] = a; refs.push_back(b);
-        heap.push_back(i); std::push_heap(heap.begin(), heap.end(), cmp);
-        heap.push_back((int)refs.size() - 1); std::push_heap(heap.begin(), heap.end(), cmp);
+        if (poly_of[i] < 0) { poly_of[i] = (int)polys.size(); polys.push_back(pl); } else polys[poly_of[i]] = pl;
+        poly_of.push_back((int)polys.size()); polys.push_back(pr);
+        push(i); push((int)refs.size() - 1);
     }
 }
 
 } // namespace
 
 void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
+    const bool verbose = getenv("GDPT_VERBOSE") != nullptr;
+    auto t_last = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        auto now = std::chrono::steady_clock::now();
+        if (verbose) fprintf(stderr, "[build_bvh]   %-16s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+        t_last = now;
+    };
     std::vector<BvhPrim> src;
     Builder B;
     for (int s = 0; s < (int)shapes.size(); s++) {
@@ -241,10 +275,14 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
     if (const char *e = getenv("GDPT_BVH_MAX_LEAF")) B.max_leaf = std::min(7, std::max(1, atoi(e)));
     double split_budget = 2.0;      // extra references allowed, as a fraction of the primitive count (B200 sweep: profiles/r1_bvh_sweep.txt)
     if (const char *e = getenv("GDPT_BVH_SPLIT")) split_budget = atof(e);
+    lap("references");
     if (split_budget > 0.0) presplit(B.refs, src, (size_t)((1.0 + split_budget) * B.refs.size()));
+    lap("pre-split");
     B.nodes.resize(2 * B.refs.size());
-    { unsigned hc = std::max(1u, std::thread::hardware_concurrency()); while ((1u << (B.fork_levels + 1)) <= std::min(16u, hc)) B.fork_levels++; }
-    B.build(0, (int)B.refs.size());
+    B.max_workers = (int)std::min(15u, std::max(1u, std::thread::hardware_concurrency()) - 1);
+    if (const char *e = getenv("GDPT_BVH_THREADS")) B.max_workers = std::max(0, atoi(e) - 1);
+    B.build(0, (int)B.refs.size(), 0);
+    lap("binned SAH");
     out.prims.resize(B.refs.size());
     for (size_t i = 0; i < B.refs.size(); i++) out.prims[i] = src[B.refs[i].idx];
 
@@ -288,6 +326,7 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
             }
         }
     }
+    lap("collapse to 4");
 }
 
 } // namespace gdpt

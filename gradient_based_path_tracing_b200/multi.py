@@ -144,6 +144,7 @@ class DistributedPoisson:
         self._sync()
         if self.world > 1:
             self.halo(cy0, cy1)
+            self._sync()          # the halo rows must have landed before the merge kernel (context stream) reads them
         st.merge_rows(g, y0, min(y1 + 1, self.h), cx0, cx1, cy0, cy1, cx, cy)
         st.rows_forward(g, img, cx, cy, alpha, self.send, self.dc)
         self._sync()
@@ -204,6 +205,27 @@ class DistributedRenderer:
         self.dsolve = None
         if solver == "distributed":
             self.dsolve = DistributedPoisson(scene.width, scene.height, self.bands, dist, torch, CudaStages(self.ctx, _capi), device=dev)
+
+    def render_path(self, spp, precision="f32", seed=0, to_host=False):
+        """path_render (render.cpp:74-117) over the ranks: each renders its row band, the bands are summed onto rank 0."""
+        from .render import _params
+        lib, check, torch = self._capi.lib(), self._capi.check, self.torch
+        y0, y1 = self.bands[self.rank]
+        img = self.acc[0]
+        img.zero_()
+        torch.cuda.current_stream().synchronize()
+        if y1 > y0:
+            p = _params(self.scene, spp=spp, precision=precision, seed=seed, rows=(y0, y1))
+            if y0 == 0:
+                p.y0 = 0
+            check(lib.gdpt_render_path_accumulate_device(self.ctx, C.byref(p), C.c_void_p(img.data_ptr())))
+            check(lib.gdpt_synchronize(self.ctx))
+        if self.world > 1:
+            reduce_bands([img], self.dist, dst=0)
+            torch.cuda.current_stream().synchronize()
+        if self.rank == 0 and to_host:
+            return img.cpu().numpy().reshape(self.scene.height, self.scene.width, 3)
+        return None
 
     def render(self, spp, precision="f32", seed=0, data_cost=0.04, to_host=False):
         from .render import _params

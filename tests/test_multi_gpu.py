@@ -38,6 +38,13 @@ if rank == 0:
     rel = np.linalg.norm(single.poisson - b["poisson"]) / np.linalg.norm(single.poisson)
     assert rel < 1e-10, rel
     print("OK")
+# the plain path integrator over the same bands
+r = DistributedRenderer(sc, rank, dist, torch, solver="gather")
+img = r.render_path(spp=2, precision="f64", to_host=True)
+if rank == 0:
+    want = g.path_render(sc, spp=2, precision="f64")
+    assert np.abs(img - want).max() < 1e-12
+    print("PATH OK")
 dist.barrier()
 dist.destroy_process_group()
 '''
@@ -61,4 +68,4 @@ def test_distributed_solve_equals_gather_solve_nccl(tmp_path, world):
         procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
     outs = [p.communicate(timeout=600)[0].decode() for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
-    assert "OK" in outs[0]
+    assert "OK" in outs[0] and "PATH OK" in outs[0]
