@@ -1,6 +1,7 @@
 #include "gdpt_container.h"
 
 #include <zlib.h>
+#include <algorithm>
 
 #include <cstdio>
 #include <cstring>
@@ -148,6 +149,89 @@ std::string write_pfm(const std::string &path, int w, int h, const double *rgb) 
         f.write((const char *)row.data(), (std::streamsize)(row.size() * sizeof(float)));
     }
     return f ? "" : "short write to " + path;
+}
+
+// ---- OpenEXR output, the reference's default film format (image.exr; imwrite -> tinyexr SaveEXR(data, w, h, 3,
+// save_as_fp16 = 1), /root/reference/src/image.cpp:150-171): single-part scan-line file, channels B, G, R of type HALF,
+// ZIP compression in blocks of 16 scan lines (NONE below 16x16 like SaveEXR), increasing-Y line order.
+static unsigned short float_to_half(float f) {      // IEEE round to nearest even, with denormals, inf and NaN
+    unsigned int x; std::memcpy(&x, &f, 4);
+    unsigned int sign = (x >> 16) & 0x8000u, mant = x & 0x007fffffu;
+    int exp = (int)((x >> 23) & 0xff);
+    if (exp == 0xff) return (unsigned short)(sign | 0x7c00u | (mant ? 0x0200u | (mant >> 13) : 0));
+    int e = exp - 127 + 15;
+    if (e >= 0x1f) return (unsigned short)(sign | 0x7c00u);
+    if (e <= 0) {
+        if (e < -10) return (unsigned short)sign;
+        mant |= 0x00800000u;
+        unsigned int shift = (unsigned int)(14 - e), h = mant >> shift, rem = mant & ((1u << shift) - 1), half = 1u << (shift - 1);
+        if (rem > half || (rem == half && (h & 1))) h++;
+        return (unsigned short)(sign | h);
+    }
+    unsigned int h = ((unsigned int)e << 10) | (mant >> 13), rem = mant & 0x1fffu;
+    if (rem > 0x1000u || (rem == 0x1000u && (h & 1))) h++;      // a carry into the exponent is the correct rounding
+    return (unsigned short)(sign | h);
+}
+
+std::string write_exr(const std::string &path, int w, int h, const double *rgb) {
+    std::vector<unsigned char> out;
+    auto put = [&](const void *p, size_t n) { const unsigned char *b = (const unsigned char *)p; out.insert(out.end(), b, b + n); };
+    auto put_i32 = [&](int v) { put(&v, 4); };
+    auto put_f32 = [&](float v) { put(&v, 4); };
+    auto put_str = [&](const char *s) { put(s, std::strlen(s) + 1); };
+    auto attr = [&](const char *name, const char *type, int size) { put_str(name); put_str(type); put_i32(size); };
+    const unsigned char magic[8] = {0x76, 0x2f, 0x31, 0x01, 2, 0, 0, 0};
+    put(magic, 8);
+    attr("channels", "chlist", 3 * 18 + 1);
+    for (const char *c : {"B", "G", "R"}) { put_str(c); put_i32(1 /* HALF */); unsigned char lin[4] = {0, 0, 0, 0}; put(lin, 4); put_i32(1); put_i32(1); }
+    out.push_back(0);
+    const bool zip = !(w < 16 && h < 16);
+    attr("compression", "compression", 1); out.push_back(zip ? 3 : 0);
+    attr("dataWindow", "box2i", 16); put_i32(0); put_i32(0); put_i32(w - 1); put_i32(h - 1);
+    attr("displayWindow", "box2i", 16); put_i32(0); put_i32(0); put_i32(w - 1); put_i32(h - 1);
+    attr("lineOrder", "lineOrder", 1); out.push_back(0);
+    attr("pixelAspectRatio", "float", 4); put_f32(1.0f);
+    attr("screenWindowCenter", "v2f", 8); put_f32(0.0f); put_f32(0.0f);
+    attr("screenWindowWidth", "float", 4); put_f32(1.0f);
+    out.push_back(0);
+    const int lines = zip ? 16 : 1, nblocks = (h + lines - 1) / lines;
+    const size_t table = out.size();
+    out.resize(out.size() + 8 * (size_t)nblocks);
+    std::vector<unsigned char> raw, tmp, comp;
+    for (int b = 0; b < nblocks; b++) {
+        const int y0 = b * lines, y1 = std::min(h, y0 + lines);
+        raw.clear();
+        for (int y = y0; y < y1; y++)
+            for (int c = 2; c >= 0; c--)             // B, G, R
+                for (int x = 0; x < w; x++) { unsigned short hv = float_to_half((float)rgb[((size_t)y * w + x) * 3 + c]); raw.push_back((unsigned char)(hv & 0xff)); raw.push_back((unsigned char)(hv >> 8)); }
+        const unsigned char *payload = raw.data(); size_t psize = raw.size();
+        if (zip) {
+            const size_t n = raw.size();
+            tmp.resize(n);
+            size_t t1 = 0, t2 = (n + 1) / 2;         // even bytes first, then odd bytes
+            for (size_t i = 0; i < n; i++) { if (i & 1) tmp[t2++] = raw[i]; else tmp[t1++] = raw[i]; }
+            unsigned char prev = tmp[0];
+            for (size_t i = 1; i < n; i++) { unsigned char cur = tmp[i]; tmp[i] = (unsigned char)((int)cur - (int)prev + 128 + 256); prev = cur; }
+            uLongf clen = compressBound((uLong)n);
+            comp.resize(clen);
+            if (compress(comp.data(), &clen, tmp.data(), (uLong)n) != Z_OK) return "zlib compress failed for " + path;
+            if (clen < n) { payload = comp.data(); psize = clen; }   // a block that does not shrink is stored raw
+        }
+        unsigned long long off = out.size();
+        std::memcpy(out.data() + table + 8 * (size_t)b, &off, 8);
+        put_i32(y0); put_i32((int)psize); put(payload, psize);
+    }
+    std::ofstream f(path, std::ios::binary);
+    if (!f) return "cannot write " + path;
+    f.write((const char *)out.data(), (std::streamsize)out.size());
+    return f ? "" : "short write to " + path;
+}
+
+std::string write_image(const std::string &path, int w, int h, const double *rgb) {
+    auto ends = [&](const char *suf) { size_t n = std::strlen(suf); return path.size() >= n && path.compare(path.size() - n, n, suf) == 0; };
+    if (ends(".pfm")) return write_pfm(path, w, h, rgb);
+    if (ends(".exr")) return write_exr(path, w, h, rgb);
+    return "Unsupported image format: " + path;       // imwrite writes nothing for other names (image.cpp:134-173)
 }
 
 } // namespace gdpt_host

@@ -45,5 +45,9 @@ struct FlatScene {
 
 // PFM as lajolla's imwrite writes it (src/image.cpp:135-150): "PF", "w h", "-1", float RGB rows top-down.
 std::string write_pfm(const std::string &path, int w, int h, const double *rgb);
+// OpenEXR as imwrite -> tinyexr SaveEXR(..., 3, fp16) writes it (src/image.cpp:150-171): B, G, R HALF channels, ZIP.
+std::string write_exr(const std::string &path, int w, int h, const double *rgb);
+// imwrite's dispatch on the file name (.pfm / .exr)
+std::string write_image(const std::string &path, int w, int h, const double *rgb);
 
 } // namespace gdpt_host

@@ -122,13 +122,15 @@ int main(int argc, char *argv[]) {
         else std::printf("%.1f Mpaths/s (base + 4 shifts; %d spp, %lld kernel launches, trace %.1f ms, shade %.1f ms, Poisson %.1f ms, copies %.1f ms)\n",
                     5.0 * w * h * p.spp / took / 1e6, p.spp, (long long)st.kernel_launches, st.ms_trace, st.ms_shade, st.ms_poisson, st.ms_copy);
 
-        std::string of = outputfile.empty() ? "image.pfm" : outputfile;   // the reference's default film name is image.exr; EXR needs tinyexr, so PFM here
-        if (of.size() < 4 || of.compare(of.size() - 4, 4, ".pfm") != 0) { std::cerr << "only .pfm output is supported: " << of << std::endl; return 1; }
-        std::string stem = of.substr(0, of.size() - 4);
-        const std::pair<std::string, const double *> files[] = {{of, out.data()}, {stem + "_primal.pfm", primal.data()}, {stem + "_dx.pfm", dx.data()}, {stem + "_dy.pfm", dy.data()}};
+        // the film name: -o, else the reference's default image.exr (parse_scene.cpp:15); .exr (fp16) or .pfm like imwrite
+        std::string of = outputfile.empty() ? "image.exr" : outputfile;
+        auto ends = [&](const char *suf) { size_t n = std::char_traits<char>::length(suf); return of.size() >= n && of.compare(of.size() - n, n, suf) == 0; };
+        if (!ends(".pfm") && !ends(".exr")) { std::cerr << "Unsupported image format: " << of << std::endl; return 1; }
+        const std::string stem = of.substr(0, of.size() - 4), ext = of.substr(of.size() - 4);
+        const std::pair<std::string, const double *> files[] = {{of, out.data()}, {stem + "_primal" + ext, primal.data()}, {stem + "_dx" + ext, dx.data()}, {stem + "_dy" + ext, dy.data()}};
         for (const auto &f : files) {
             if (path && f.second != out.data()) continue;
-            err = write_pfm(f.first, w, h, f.second);
+            err = write_image(f.first, w, h, f.second);
             if (!err.empty()) { std::cerr << err << std::endl; return 1; }
         }
         std::cout << "Image written to " << of << std::endl;

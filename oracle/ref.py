@@ -47,6 +47,7 @@ def lib():
         L.gdpt_ref_intersect.argtypes = [C.c_void_p, C.c_int, dp, dp, ip, dp]
         L.gdpt_ref_bsdf.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp, dp, dp]
         L.gdpt_ref_export.argtypes = [C.c_void_p, C.c_char_p]
+        L.gdpt_ref_imread3.argtypes = [C.c_char_p, ip, ip, dp]
         L.gdpt_ref_path_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, dp]
         L.gdpt_ref_sample_light.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
         L.gdpt_ref_occluded.argtypes = [C.c_void_p, C.c_int, dp, ip]
@@ -231,6 +232,16 @@ class RefScene:
         if lib().gdpt_ref_export(self.h, os.path.abspath(path).encode()) != 0:
             raise RuntimeError("export failed: " + path)
         return path
+
+
+def imread3(path):
+    """The reference's own image loader (src/image.cpp:80-133) on a file."""
+    w, h = C.c_int(0), C.c_int(0)
+    p = os.path.abspath(path).encode()
+    lib().gdpt_ref_imread3(p, C.byref(w), C.byref(h), None)
+    img = np.zeros((h.value, w.value, 3))
+    lib().gdpt_ref_imread3(p, C.byref(w), C.byref(h), _dp(img))
+    return img
 
 
 def fourier_solve(u, gx, gy, alpha=0.04):

@@ -22,6 +22,7 @@
 #include "intersection.h"
 #include "material.h"
 #include "camera.h"
+#include "image.h"
 #include "parsers/parse_scene.h"
 
 #include <cstdio>
@@ -205,6 +206,15 @@ void gdpt_ref_grad_sample(void *hs, int x, int y, uint64_t stream, uint64_t seed
     const Vector3 *v[6] = {&g.radiance, &g.contrib, &g.contribX0, &g.contribX1, &g.contribY0, &g.contribY1};
     for (int i = 0; i < 6; i++) { rec[3 * i] = v[i]->x; rec[3 * i + 1] = v[i]->y; rec[3 * i + 2] = v[i]->z; }
     rec[18] = g.prob; rec[19] = g.wX0; rec[20] = g.wY0; rec[21] = g.wX1; rec[22] = g.wY1;
+}
+
+// imread3 (src/image.cpp:80-133; tinyexr / PFM): lets the tests read the product's output files with the reference's
+// own loader.  Two calls: data == NULL returns the size.
+int gdpt_ref_imread3(const char *path, int *w, int *h, double *data) {
+    Image3 img = imread3(fs::path(path));
+    *w = img.width; *h = img.height;
+    if (data) memcpy(data, img.data.data(), sizeof(double) * 3 * img.data.size());
+    return 0;
 }
 
 // One path_tracing evaluation (src/path_tracing.h:13-348) with rng = init_pcg32(stream, seed). rad[3]

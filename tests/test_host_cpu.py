@@ -208,3 +208,85 @@ def test_cpp_host_rejects_bad_input(tmp_path):
     assert r.returncode == 1 and b"not a GDPT1 container" in r.stderr
     r = subprocess.run([exe, "-describe", str(tmp_path / "missing.gdpt")], capture_output=True, timeout=60)
     assert r.returncode == 1 and b"cannot open" in r.stderr
+
+
+# ------------------------------------------------------------------ image writers of the C++ host (imwrite, image.cpp:134-173)
+def _read_exr(path):
+    """Independent minimal OpenEXR reader (scan lines, NONE / ZIP, HALF channels) for the writer's round trip."""
+    import struct
+    import zlib
+    b = open(path, "rb").read()
+    assert b[:4] == bytes([0x76, 0x2f, 0x31, 0x01]) and b[4] == 2
+    p, attrs = 8, {}
+    while b[p] != 0:
+        e = b.index(0, p); name = b[p:e].decode(); p = e + 1
+        e = b.index(0, p); typ = b[p:e].decode(); p = e + 1
+        size = struct.unpack_from("<i", b, p)[0]; p += 4
+        attrs[name] = (typ, b[p:p + size]); p += size
+    p += 1
+    chans, q, cl = [], 0, attrs["channels"][1]
+    while cl[q] != 0:
+        e = cl.index(0, q); chans.append((cl[q:e].decode(), struct.unpack_from("<i", cl, e + 1)[0])); q = e + 1 + 16
+    assert [c[0] for c in chans] == ["B", "G", "R"] and all(c[1] == 1 for c in chans)
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1])
+    w, h = x1 - x0 + 1, y1 - y0 + 1
+    comp = attrs["compression"][1][0]
+    lines = {0: 1, 3: 16}[comp]
+    nblocks = (h + lines - 1) // lines
+    offs = struct.unpack_from("<%dQ" % nblocks, b, p)
+    img = np.zeros((h, w, 3), dtype=np.float32)
+    for o in offs:
+        y, size = struct.unpack_from("<2i", b, o)
+        data = b[o + 8:o + 8 + size]
+        n = min(lines, h - y) * w * 3 * 2
+        if comp == 3 and size < n:
+            t = np.frombuffer(zlib.decompress(data), dtype=np.uint8).astype(np.int32)
+            t = (np.cumsum(t - np.concatenate([[0], np.full(n - 1, 128)])) % 256).astype(np.uint8)   # undo the predictor
+            raw = np.empty(n, dtype=np.uint8)
+            raw[0::2], raw[1::2] = t[:(n + 1) // 2], t[(n + 1) // 2:]
+        else:
+            raw = np.frombuffer(data, dtype=np.uint8)
+        px = raw.view(np.float16).reshape(-1, 3, w).astype(np.float32)      # [line][B,G,R][x]
+        img[y:y + px.shape[0]] = px[:, ::-1, :].transpose(0, 2, 1)
+    return img
+
+
+@pytest.mark.parametrize("w,h", [(8, 5), (37, 41), (160, 90)])
+def test_cpp_host_exr_and_pfm_writers(tmp_path, w, h):
+    """write_image (csrc/host): the EXR the reference would write by default (fp16 B/G/R, ZIP; NONE below 16x16) read back by an
+    independent reader, by OpenCV and by the reference's own imread3 (tinyexr) where the oracle is built; PFM as imwrite."""
+    import subprocess
+    csrc = os.path.join(ROOT, "gradient_based_path_tracing_b200", "csrc")
+    exe = tmp_path / "exr_check"
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", os.path.join(csrc, "host"), "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "host", "exr_check.cpp"), os.path.join(csrc, "host", "gdpt_container.cpp"), "-o", str(exe), "-lz"])
+    rng = np.random.default_rng(w * h)
+    img = rng.random((h, w, 3)) * np.array([1.0, 40.0, 1e-3]) - 0.1
+    img[0, 0] = [0.0, 65504.0, 1e-8]            # zero, the largest half, a half denormal
+    img[1, 1] = [1e6, -1e6, 6.1e-5]             # overflow to +-inf, smallest normal
+    raw = tmp_path / "img.f64"
+    img.tofile(raw)
+    with np.errstate(over="ignore"):
+        want = img.astype(np.float32).astype(np.float16).astype(np.float32)
+    subprocess.check_call([str(exe), str(w), str(h), str(raw), str(tmp_path / "o.exr")])
+    got = _read_exr(str(tmp_path / "o.exr"))
+    assert np.array_equal(got, want)
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    try:
+        import cv2
+        cvimg = cv2.imread(str(tmp_path / "o.exr"), cv2.IMREAD_UNCHANGED)
+    except Exception:
+        cvimg = None
+    if cvimg is not None:
+        fin = np.isfinite(want)
+        assert np.array_equal(cvimg[..., ::-1][fin], want[fin])
+    from oracle import ref
+    if ref.available():
+        back = ref.imread3(str(tmp_path / "o.exr"))
+        fin = np.isfinite(want)
+        assert np.array_equal(back.astype(np.float32)[fin], want[fin])
+    subprocess.check_call([str(exe), str(w), str(h), str(raw), str(tmp_path / "o.pfm")])
+    b = open(tmp_path / "o.pfm", "rb").read()
+    head = ("PF\n%d %d\n-1\n" % (w, h)).encode()
+    assert b.startswith(head)
+    assert np.array_equal(np.frombuffer(b[len(head):], dtype=np.float32).reshape(h, w, 3), img.astype(np.float32))

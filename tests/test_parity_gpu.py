@@ -387,3 +387,21 @@ def test_cpp_host_cli_path_integrator(g, scenes, tmp_path):
     want = g.path_render(scenes("cbox_gdpt_64"), spp=2, precision="f64")
     assert np.allclose(_read_pfm(str(out)), want.astype(np.float32), rtol=1e-6, atol=1e-9)
     assert not os.path.exists(str(out)[:-4] + "_dx.pfm")
+
+
+def test_cpp_host_cli_default_film_is_exr(g, scenes, tmp_path):
+    """Without -o the reference writes image.exr (parse_scene.cpp:15; fp16 RGB through tinyexr): same here, plus the three
+    companion buffers, all readable back as the half-rounded images."""
+    import os
+    import subprocess
+    from conftest import ROOT
+    from test_host_cpu import _read_exr
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "lajolla_b200")
+    r = subprocess.run([exe, "-spp", "2", "-precision", "f64", os.path.join(ROOT, "scenes", "cbox_gdpt_64.gdpt.z")],
+                       capture_output=True, timeout=600, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stderr.decode()
+    assert "Image written to image.exr" in r.stdout.decode()
+    want = g.gradient_path_render(scenes("cbox_gdpt_64"), spp=2, precision="f64")
+    for suffix, img in (("", want.poisson), ("_primal", want.primal), ("_dx", want.dx), ("_dy", want.dy)):
+        got = _read_exr(str(tmp_path / ("image" + suffix + ".exr")))
+        assert np.allclose(got, img.astype(np.float32).astype(np.float16).astype(np.float32), rtol=2e-3, atol=1e-7), suffix
