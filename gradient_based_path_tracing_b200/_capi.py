@@ -32,6 +32,7 @@ class GdptSceneDesc(C.Structure):
         ("n_images3", C.c_int32), ("n_images1", C.c_int32), ("images3", C.POINTER(GdptImage)), ("images1", C.POINTER(GdptImage)),
         ("n_lights", C.c_int32), ("lights", dp),
         ("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("samples_per_pixel", C.c_int32),
+        ("envmap_to_world", dp), ("envmap_to_local", dp),
     ]
 
 

@@ -87,7 +87,7 @@ int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, dou
 }
 
 int path_supported(gdpt_ctx *c) {
-    if (c->has_envmap) return fail(GDPT_ERR_UNSUPPORTED, "the path integrator does not handle environment-map lights yet");
+    if (c->has_envmap && !c->envmap_ready) return fail(GDPT_ERR_UNSUPPORTED, "the scene has an environment map whose image / transforms were not provided (gdpt_scene_desc.envmap_*)");
     return 0;
 }
 

@@ -65,7 +65,8 @@ struct gdpt_ctx {
     gdpt::DevBuf pos_d, nrm_d, uv_d, tex_d, texels3_d, texels1_d, light_d;   // exact mode
     gdpt::DevBuf pos_f, nrm_f, uv_f, tex_f, texels3_f, texels1_f, light_f;   // fast mode
     gdpt::DevBuf lcdf_d, lcdf_f, lpmf_d, lpmf_f, tcdf_d, tcdf_f, area_d, area_f, lshape;   // light sampling tables (path integrator)
-    bool has_envmap = false;
+    bool has_envmap = false, envmap_ready = false;   // the scene has an environment map / its image and transforms were provided
+    gdpt::DevBuf ecr_d, ecr_f, epr_d, epr_f, ecm_d, ecm_f, epm_d, epm_f;   // the environment map's TableDist2D
     gdpt::DevBuf shadow_rays, shadow_hits, prec_a, prec_b;                                  // path-integrator queues
     gdpt::DevBuf bvh_nodes, bvh_prims;
     gdpt::DScene<double> sc_d;
@@ -264,15 +265,16 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     std::vector<double> li(3 * (size_t)std::max(d->n_lights, 1), 0.0);
     for (int i = 0; i < d->n_lights; i++) for (int k = 0; k < 3; k++) li[3 * i + k] = d->lights[5 * i + 2 + k];
     if (int r = upload(c->light_d, li)) return r; if (int r = upload(c->light_f, to_f(li))) return r;
-    {   // light sampling tables: init_sampling_dist of the emissive meshes (triangle_mesh.inl:60-75), light_power
-        // (diffuse_area_light.inl:1-3) and the light distribution (scene.cpp:46-52), all as make_table_dist_1d builds them
-        auto table = [](const std::vector<double> &f, std::vector<double> &pmf, std::vector<double> &cdf) {
-            pmf = f; cdf.assign(f.size() + 1, 0.0);
-            for (size_t i = 0; i < f.size(); i++) cdf[i + 1] = cdf[i] + pmf[i];
-            double total = cdf.back();
-            if (total > 0) { for (size_t i = 0; i < pmf.size(); i++) { pmf[i] /= total; cdf[i] /= total; } }   // the last cdf entry keeps the total
-            else { for (size_t i = 0; i < pmf.size(); i++) { pmf[i] = 1.0 / (double)pmf.size(); cdf[i] = (double)i / (double)pmf.size(); } if (!cdf.empty()) cdf.back() = 1; }
-        };
+    // light sampling tables, all as make_table_dist_1d builds them (table_dist.cpp:3-26)
+    auto table = [](const std::vector<double> &f, std::vector<double> &pmf, std::vector<double> &cdf) {
+        pmf = f; cdf.assign(f.size() + 1, 0.0);
+        for (size_t i = 0; i < f.size(); i++) cdf[i + 1] = cdf[i] + pmf[i];
+        double total = cdf.back();
+        if (total > 0) { for (size_t i = 0; i < pmf.size(); i++) { pmf[i] /= total; cdf[i] /= total; } }   // the last cdf entry keeps the total
+        else { for (size_t i = 0; i < pmf.size(); i++) { pmf[i] = 1.0 / (double)pmf.size(); cdf[i] = (double)i / (double)pmf.size(); } if (!cdf.empty()) cdf.back() = 1; }
+    };
+    std::vector<double> shape_area;
+    {   // init_sampling_dist of the emissive meshes (triangle_mesh.inl:60-75) and the surface areas
         std::vector<double> tri_cdf, area(std::max(d->n_shapes, 1), 0.0);
         for (int i = 0; i < d->n_shapes; i++) {
             const HostShape &h = hs[i];
@@ -289,24 +291,10 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
             shapes[i].cdf_off = (int)tri_cdf.size(); area[i] = total;
             tri_cdf.insert(tri_cdf.end(), cd.begin(), cd.end());
         }
-        std::vector<double> power(d->n_lights), lpmf, lcdf; std::vector<int> lshape(std::max(d->n_lights, 1), -1);
-        c->has_envmap = false;
-        for (int i = 0; i < d->n_lights; i++) {
-            const double *l = d->lights + 5 * i;
-            if ((int)l[0] != 0) { c->has_envmap = true; power[i] = 0; continue; }
-            int sid = (int)l[1];
-            if (sid < 0 || sid >= d->n_shapes) return fail(GDPT_ERR_ARG, "light %d: shape id out of range", i);
-            lshape[i] = sid;
-            power[i] = (l[2] * 0.212671 + l[3] * 0.715160 + l[4] * 0.072169) * area[sid] * 3.14159265358979323846;
-        }
-        table(power, lpmf, lcdf);
-        if (lpmf.empty()) lpmf.push_back(0.0);
         if (tri_cdf.empty()) tri_cdf.push_back(0.0);
-        if (int r = upload(c->lcdf_d, lcdf)) return r; if (int r = upload(c->lcdf_f, to_f(lcdf))) return r;
-        if (int r = upload(c->lpmf_d, lpmf)) return r; if (int r = upload(c->lpmf_f, to_f(lpmf))) return r;
         if (int r = upload(c->tcdf_d, tri_cdf)) return r; if (int r = upload(c->tcdf_f, to_f(tri_cdf))) return r;
         if (int r = upload(c->area_d, area)) return r; if (int r = upload(c->area_f, to_f(area))) return r;
-        if (int r = upload(c->lshape, lshape)) return r;
+        shape_area = area;
     }
 
     lap("texel upload");
@@ -329,9 +317,98 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         for (int k = 0; k < 3; k++) c->bounds[1 + k] = (lb[k] + ub[k]) / 2.0;
     }
     double eps = std::min(c->bounds[0] * 1e-5, 0.01);   // scene.h:104-106
+    fill_scene_common(c->sc_d, d); fill_scene_common(c->sc_f, d);
+    {   // light_power (diffuse_area_light.inl:1-3, envmap.inl:1-5) and the light distribution (scene.cpp:46-52); the
+        // environment map's TableDist2D over luminance * sin(elevation) of its level-0 texels (envmap.inl:76-98)
+        std::vector<double> power(d->n_lights), lpmf, lcdf; std::vector<int> lshape(std::max(d->n_lights, 1), -1);
+        std::vector<double> cdf_rows(1, 0.0), pdf_rows(1, 0.0), cdf_marg(1, 0.0), pdf_marg(1, 0.0);
+        c->has_envmap = false; c->envmap_ready = false;
+        c->sc_d.env_light = c->sc_f.env_light = -1; c->sc_d.env_tex = c->sc_f.env_tex = -1;
+        c->sc_d.env_w = c->sc_f.env_w = 0; c->sc_d.env_h = c->sc_f.env_h = 0;
+        for (int i = 0; i < d->n_lights; i++) {
+            const double *l = d->lights + 5 * i;
+            if ((int)l[0] != 0) {
+                c->has_envmap = true; power[i] = 0;
+                const int tid = (int)l[1];
+                if (tid < 0 || !d->envmap_to_world || !d->envmap_to_local) continue;          // not provided: path refuses the scene
+                if (tid >= d->n_textures || td[tid].kind != TEX_IMAGE || d->textures[14 * tid + 1] == 0) return fail(GDPT_ERR_UNSUPPORTED, "environment map %d is not an RGB image texture", i);
+                const DImage &im = im3[td[tid].image_id];
+                const int w = im.w[0], h = im.h[0];
+                const double *tex = pool3.data() + 3 * (size_t)im.off[0];
+                auto imod = [](int a, int b) { int r = a % b; return r < 0 ? r + b : r; };
+                std::vector<double> f((size_t)w * h);
+                for (int y = 0; y < h; y++) {
+                    double v = (y + 0.5) / (double)h, sin_el = sin(3.14159265358979323846 * v);
+                    for (int x = 0; x < w; x++) {
+                        double u = (x + 0.5) / (double)w;
+                        // lookup(mipmap, u, v, 0): bilinear at level 0 (mipmap.h:46-69)
+                        double uu = u * w - 0.5, vv = v * h - 0.5;
+                        int ufi = imod((int)uu, w), vfi = imod((int)vv, h), uci = imod(ufi + 1, w), vci = imod(vfi + 1, h);
+                        double uo = uu - ufi, vo = vv - vfi, lum[4];
+                        const int xs[4] = {ufi, ufi, uci, uci}, ys[4] = {vfi, vci, vfi, vci};
+                        double rgb[3];
+                        for (int ch = 0; ch < 3; ch++) {
+                            double ff = tex[3 * ((size_t)ys[0] * w + xs[0]) + ch], fc = tex[3 * ((size_t)ys[1] * w + xs[1]) + ch];
+                            double cf = tex[3 * ((size_t)ys[2] * w + xs[2]) + ch], cc = tex[3 * ((size_t)ys[3] * w + xs[3]) + ch];
+                            rgb[ch] = ff * (1 - uo) * (1 - vo) + fc * (1 - uo) * vo + cf * uo * (1 - vo) + cc * uo * vo;
+                        }
+                        (void)lum;
+                        f[(size_t)y * w + x] = (rgb[0] * 0.212671 + rgb[1] * 0.715160 + rgb[2] * 0.072169) * sin_el;
+                    }
+                }
+                // make_table_dist_2d (table_dist.cpp:45-123)
+                cdf_rows.assign((size_t)h * (w + 1), 0.0); pdf_rows.assign((size_t)h * w, 0.0);
+                for (int y = 0; y < h; y++) {
+                    double *cr = cdf_rows.data() + (size_t)y * (w + 1), *pr = pdf_rows.data() + (size_t)y * w;
+                    for (int x = 0; x < w; x++) cr[x + 1] = cr[x] + f[(size_t)y * w + x];
+                    double integral = cr[w];
+                    if (integral > 0) { for (int x = 0; x < w; x++) cr[x] /= integral; for (int x = 0; x < w; x++) pr[x] = f[(size_t)y * w + x] / integral; }
+                    else { for (int x = 0; x < w; x++) { pr[x] = 1.0 / (double)w; cr[x] = (double)x / (double)w; } cr[w] = 1; }
+                }
+                cdf_marg.assign((size_t)h + 1, 0.0); pdf_marg.assign((size_t)h, 0.0);
+                for (int y = 0; y < h; y++) cdf_marg[y + 1] = cdf_marg[y] + cdf_rows[(size_t)y * (w + 1) + w];
+                const double total = cdf_marg.back();
+                if (total > 0) {
+                    for (int y = 0; y < h; y++) cdf_marg[y] /= total;
+                    cdf_marg[h] = 1;
+                    for (int y = 0; y < h; y++) pdf_marg[y] = cdf_rows[(size_t)y * (w + 1) + w] / total;
+                } else {
+                    for (int y = 0; y < h; y++) { pdf_marg[y] = 1.0 / (double)h; cdf_marg[y] = (double)y / (double)h; }
+                    cdf_marg[h] = 1;
+                }
+                for (int y = 0; y < h; y++) cdf_rows[(size_t)y * (w + 1) + w] = 1;
+                power[i] = 3.14159265358979323846 * c->bounds[0] * c->bounds[0] * total / (double)(w * h);
+                c->envmap_ready = true;
+                c->sc_d.env_light = c->sc_f.env_light = i; c->sc_d.env_tex = c->sc_f.env_tex = tid;
+                c->sc_d.env_w = c->sc_f.env_w = w; c->sc_d.env_h = c->sc_f.env_h = h;
+                c->sc_d.env_scale = l[2]; c->sc_f.env_scale = (float)l[2];
+                for (int k = 0; k < 16; k++) {
+                    c->sc_d.env_to_world[k] = d->envmap_to_world[k]; c->sc_f.env_to_world[k] = (float)d->envmap_to_world[k];
+                    c->sc_d.env_to_local[k] = d->envmap_to_local[k]; c->sc_f.env_to_local[k] = (float)d->envmap_to_local[k];
+                }
+                continue;
+            }
+            int sid = (int)l[1];
+            if (sid < 0 || sid >= d->n_shapes) return fail(GDPT_ERR_ARG, "light %d: shape id out of range", i);
+            lshape[i] = sid;
+            power[i] = (l[2] * 0.212671 + l[3] * 0.715160 + l[4] * 0.072169) * shape_area[sid] * 3.14159265358979323846;
+        }
+        table(power, lpmf, lcdf);
+        if (lpmf.empty()) lpmf.push_back(0.0);
+        if (int r = upload(c->lcdf_d, lcdf)) return r; if (int r = upload(c->lcdf_f, to_f(lcdf))) return r;
+        if (int r = upload(c->lpmf_d, lpmf)) return r; if (int r = upload(c->lpmf_f, to_f(lpmf))) return r;
+        if (int r = upload(c->lshape, lshape)) return r;
+        if (int r = upload(c->ecr_d, cdf_rows)) return r; if (int r = upload(c->ecr_f, to_f(cdf_rows))) return r;
+        if (int r = upload(c->epr_d, pdf_rows)) return r; if (int r = upload(c->epr_f, to_f(pdf_rows))) return r;
+        if (int r = upload(c->ecm_d, cdf_marg)) return r; if (int r = upload(c->ecm_f, to_f(cdf_marg))) return r;
+        if (int r = upload(c->epm_d, pdf_marg)) return r; if (int r = upload(c->epm_f, to_f(pdf_marg))) return r;
+        c->sc_d.env_cdf_rows = c->ecr_d.as<double>(); c->sc_f.env_cdf_rows = c->ecr_f.as<float>();
+        c->sc_d.env_pdf_rows = c->epr_d.as<double>(); c->sc_f.env_pdf_rows = c->epr_f.as<float>();
+        c->sc_d.env_cdf_marg = c->ecm_d.as<double>(); c->sc_f.env_cdf_marg = c->ecm_f.as<float>();
+        c->sc_d.env_pdf_marg = c->epm_d.as<double>(); c->sc_f.env_pdf_marg = c->epm_f.as<float>();
+    }
 
     lap("bvh upload");
-    fill_scene_common(c->sc_d, d); fill_scene_common(c->sc_f, d);
     c->sc_d.eps = eps; c->sc_f.eps = (float)eps;
     c->sc_d.shapes = c->sc_f.shapes = c->shapes.as<DShape>();
     c->sc_d.spheres = c->sc_f.spheres = c->spheres.as<double>();
@@ -357,7 +434,7 @@ inline void destroy_context(gdpt_ctx *c) {
     cudaSetDevice(c->device);
     gdpt::DevBuf *all[] = {&c->shapes, &c->spheres, &c->indices, &c->materials, &c->img3, &c->img1, &c->pos_d, &c->nrm_d, &c->uv_d, &c->tex_d,
                            &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tex_f, &c->texels3_f, &c->texels1_f,
-                           &c->light_f, &c->lcdf_d, &c->lcdf_f, &c->lpmf_d, &c->lpmf_f, &c->tcdf_d, &c->tcdf_f, &c->area_d, &c->area_f, &c->lshape, &c->shadow_rays, &c->shadow_hits, &c->prec_a, &c->prec_b, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
+                           &c->light_f, &c->lcdf_d, &c->lcdf_f, &c->lpmf_d, &c->lpmf_f, &c->tcdf_d, &c->tcdf_f, &c->area_d, &c->area_f, &c->lshape, &c->ecr_d, &c->ecr_f, &c->epr_d, &c->epr_f, &c->ecm_d, &c->ecm_f, &c->epm_d, &c->epm_f, &c->shadow_rays, &c->shadow_hits, &c->prec_a, &c->prec_b, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
                            &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
     for (auto *b : all) b->release();
     c->pc.release();

@@ -8,7 +8,8 @@
 //   emission of a sampled point       /root/reference/src/lights/diffuse_area_light.inl:15-20
 // The tables themselves (triangle-area CDFs of emissive meshes, the light-power CDF of scene.cpp:46-52) are built
 // on the host by gdpt_create exactly like make_table_dist_1d, including its quirk that the LAST cdf entry keeps the
-// un-normalised total.  Environment maps are not on this path yet (gdpt_render_path refuses scenes that have one).
+// un-normalised total.
+//   environment map                   /root/reference/src/lights/envmap.inl:1-98, TableDist2D table_dist.cpp:45-151
 #pragma once
 #include "gdpt_scene.cuh"
 
@@ -95,11 +96,70 @@ template <typename R> GD_D LightPoint<R> sample_point_on_mesh(const DScene<R> &s
     return out;
 }
 
+// ---------------------------------------------------------------- environment map
+// sample(TableDist2D, rnd)                                                  table_dist.cpp:125-148
+template <typename R> GD_D V2<R> env_table_sample(const DScene<R> &sc, R r0, R r1) {
+    const int w = sc.env_w, h = sc.env_h;
+    int y = table_sample<R>(sc.env_cdf_marg, h, r1);
+    R dy = r1 - sc.env_cdf_marg[y];
+    R wy = sc.env_cdf_marg[y + 1] - sc.env_cdf_marg[y];
+    if (wy > R(0)) dy /= wy;
+    const R *cdf = sc.env_cdf_rows + (size_t)y * (w + 1);
+    int x = table_sample<R>(cdf, w, r0);
+    R dx = r0 - cdf[x];
+    R wx = cdf[x + 1] - cdf[x];
+    if (wx > R(0)) dx /= wx;
+    return V2<R>((R(x) + dx) / R(w), (R(y) + dy) / R(h));
+}
+// pdf(TableDist2D, xy)                                                      table_dist.cpp:150-161
+template <typename R> GD_D R env_table_pdf(const DScene<R> &sc, const V2<R> &xy) {
+    const int w = sc.env_w, h = sc.env_h;
+    int x = (int)clampr(xy.x * R(w), R(0), R(w - 1)), y = (int)clampr(xy.y * R(h), R(0), R(h - 1));
+    return sc.env_pdf_marg[y] * sc.env_pdf_rows[(size_t)y * w + x] * R(w) * R(h);
+}
+// direction -> (u, v) of the lat-long map (envmap.inl:27-37, 57-65); local_dir in the map's frame
+template <typename R> GD_D V2<R> env_dir_to_uv(const V3<R> &local_dir) {
+    const R inv_two_pi = R(1) / (R(2) * Consts<R>::PI), inv_pi = R(1) / Consts<R>::PI;
+    V2<R> uv(atan2(local_dir.x, -local_dir.z) * inv_two_pi, acos(clampr(local_dir.y, R(-1), R(1))) * inv_pi);
+    if (uv.x < R(0)) uv.x += R(1);
+    return uv;
+}
+template <typename R> GD_D LightPoint<R> env_sample_point(const DScene<R> &sc, R u0, R u1) {
+    V2<R> uv = env_table_sample<R>(sc, u0, u1);
+    R azimuth = uv.x * (R(2) * Consts<R>::PI), elevation = uv.y * Consts<R>::PI;
+    V3<R> local_dir(sin(azimuth) * sin(elevation), cos(elevation), -cos(azimuth) * sin(elevation));
+    V3<R> world_dir = xform_vector<R>(sc.env_to_world, local_dir);
+    LightPoint<R> out; out.position = V3<R>(R(0), R(0), R(0)); out.normal = -world_dir;
+    return out;
+}
+template <typename R> GD_D R env_pdf_point(const DScene<R> &sc, const LightPoint<R> &p) {
+    V3<R> local_dir = xform_vector<R>(sc.env_to_local, -p.normal);
+    V2<R> uv = env_dir_to_uv<R>(local_dir);
+    R cos_el = local_dir.y;
+    R sin_el = sqrt(clampr(R(1) - cos_el * cos_el, R(0), R(1)));
+    if (sin_el <= R(0)) return R(0);
+    return env_table_pdf<R>(sc, uv) / (R(2) * Consts<R>::PI * Consts<R>::PI * sin_el);
+}
+// emission(Envmap, view_dir, view_footprint, ...) (envmap.inl:48-74).  As shipped the footprint is
+// min(|du/dw|, dv/dw_y) with dv/dw_y NEGATIVE, so the texture is always read at mip level 0; kept literally.
+template <typename R> GD_D V3<R> env_emission(const DScene<R> &sc, const V3<R> &view_dir, R view_footprint) {
+    (void)view_footprint;
+    V3<R> w = xform_vector<R>(sc.env_to_local, -view_dir);
+    V2<R> uv = env_dir_to_uv<R>(w);
+    R dudwx = -w.z / (w.x * w.x + w.z * w.z), dudwz = w.x / (w.x * w.x + w.z * w.z);
+    R dvdwy = R(-1) / sqrt(rmax(R(1) - w.y * w.y, R(0)));
+    R footprint = rmin(sqrt(dudwx * dudwx + dudwz * dudwz), dvdwy);
+    return eval_tex3<R>(sc, sc.env_tex, uv, footprint) * sc.env_scale;
+}
+
+// ---------------------------------------------------------------- lights
 template <typename R> GD_D int sample_light(const DScene<R> &sc, R u) { return table_sample<R>(sc.light_cdf, sc.n_lights, u); }
 template <typename R> GD_D R light_pmf(const DScene<R> &sc, int light_id) { return sc.light_pmf[light_id]; }
+template <typename R> GD_D bool is_envmap(const DScene<R> &sc, int light_id) { return sc.light_shape[light_id] < 0; }
 
 template <typename R> GD_D LightPoint<R> sample_point_on_light(const DScene<R> &sc, int light_id, const V3<R> &ref, R u0, R u1, R w) {
     const int shape_id = sc.light_shape[light_id];
+    if (shape_id < 0) return env_sample_point<R>(sc, u0, u1);
     const DShape sh = sc.shapes[shape_id];
     if (sh.kind == SHAPE_SPHERE) return sample_point_on_sphere<R>(sc.spheres + 4 * (size_t)shape_id, ref, u0, u1);
     return sample_point_on_mesh<R>(sc, sh, u0, u1, w);
@@ -107,13 +167,15 @@ template <typename R> GD_D LightPoint<R> sample_point_on_light(const DScene<R> &
 
 template <typename R> GD_D R pdf_point_on_light(const DScene<R> &sc, int light_id, const LightPoint<R> &p, const V3<R> &ref) {
     const int shape_id = sc.light_shape[light_id];
+    if (shape_id < 0) return env_pdf_point<R>(sc, p);
     const DShape sh = sc.shapes[shape_id];
     if (sh.kind == SHAPE_SPHERE) return pdf_point_on_sphere<R>(sc.spheres + 4 * (size_t)shape_id, p, ref);
     return R(1) / sc.shape_area[shape_id];
 }
 
-// emission(light, view_dir, footprint, point_on_light, scene) for a DiffuseAreaLight
+// emission(light, view_dir, footprint, point_on_light, scene): DiffuseAreaLight (diffuse_area_light.inl:15-20) or Envmap
 template <typename R> GD_D V3<R> light_emission(const DScene<R> &sc, int light_id, const V3<R> &view_dir, const LightPoint<R> &p) {
+    if (is_envmap(sc, light_id)) return env_emission<R>(sc, view_dir, R(0));
     if (dot(p.normal, view_dir) <= R(0)) return V3<R>(R(0), R(0), R(0));
     const R *li = sc.light_intensity + 3 * (size_t)light_id;
     return V3<R>(li[0], li[1], li[2]);

@@ -12,7 +12,9 @@
 //                          hit area light (:217-232; as shipped the BSDF-sampled light hit is NOT weighted by w2),
 //                          Russian roulette, throughput update (:252-265)
 // As shipped: a failed sample_bsdf or p2 <= 0 ends the path but keeps its radiance; bounce vertices get the
-// default ray differential.  Environment maps are not built (gdpt_render_path refuses such scenes).
+// default ray differential.  With an environment map (envmap.inl): a primary or BSDF ray that leaves the scene reads
+// it (the BSDF-sampled read IS weighted by w2, :233-246), light samples on it cast their shadow ray to infinity, and the
+// spread of the ray differential is carried along the path for its footprint (ray.h:50-66).
 #pragma once
 #include "gdpt_light.cuh"
 #include "gdpt_shade.cuh"
@@ -26,6 +28,8 @@ template <typename R> struct alignas(16) PathState {
     V3<R> thr, rad;          // current_path_throughput, radiance
     V3<R> nee;               // thr * C1 * w1 of this iteration's light sample; added iff the shadow ray is unoccluded
     R eta_scale;
+    R spread;                // ray_diff.spread (its radius stays 0: path_tracing only ever assigns the spread, :196-200)
+    R pad0, pad1, pad2;
     Pcg rng;
     int px, py, id, nv;
 };
@@ -54,8 +58,10 @@ GD_D bool path_begin_iteration(const DScene<R> &sc, const Vertex<R> &vtx, const 
     if (sc.n_lights > 0) {
         int light_id = sample_light<R>(sc, light_w);
         LightPoint<R> pl = sample_point_on_light<R>(sc, light_id, vtx.position, lu0, lu1, shape_w);
-        V3<R> dir_light = normalize(pl.position - vtx.position);
-        R G = rmax(-dot(dir_light, pl.normal), R(0)) / distance_squared(pl.position, vtx.position);
+        const bool env = is_envmap(sc, light_id);
+        V3<R> dir_light = env ? -pl.normal : normalize(pl.position - vtx.position);
+        // G of the light sample as if unoccluded (:128-149); the occlusion test itself is the shadow ray
+        R G = env ? R(1) : rmax(-dot(dir_light, pl.normal), R(0)) / distance_squared(pl.position, vtx.position);
         R p1 = light_pmf<R>(sc, light_id) * pdf_point_on_light<R>(sc, light_id, pl, vtx.position);
         if (G > R(0) && p1 > R(0)) {
             V3<R> fl = bsdf_eval_ms<R, MS>(sc, vtx, dir_view, dir_light);
@@ -68,7 +74,8 @@ GD_D bool path_begin_iteration(const DScene<R> &sc, const Vertex<R> &vtx, const 
             if (ps.nee.x != R(0) || ps.nee.y != R(0) || ps.nee.z != R(0)) {
                 shadow.ox = (float)vtx.position.x; shadow.oy = (float)vtx.position.y; shadow.oz = (float)vtx.position.z;
                 shadow.dx = (float)dir_light.x; shadow.dy = (float)dir_light.y; shadow.dz = (float)dir_light.z;
-                shadow.tnear = (float)sc.eps; shadow.tfar = (float)((R(1) - sc.eps) * distance(pl.position, vtx.position));
+                shadow.tnear = (float)sc.eps;
+                shadow.tfar = env ? __int_as_float(0x7f800000) : (float)((R(1) - sc.eps) * distance(pl.position, vtx.position));
             }
         }
     }
@@ -78,7 +85,8 @@ GD_D bool path_begin_iteration(const DScene<R> &sc, const Vertex<R> &vtx, const 
     disable_ray(ray);
     ps.org = vtx.position; ps.p2 = R(-1); ps.f = V3<R>(R(0), R(0), R(0)); ps.dir = V3<R>(R(0), R(0), R(1));
     if (bsdf_sample_ms<R, MS>(sc, vtx, dir_view, u0, u1, w, s)) {
-        if (s.eta != R(0)) ps.eta_scale /= (s.eta * s.eta);
+        if (s.eta == R(0)) ps.spread = rd_reflect<R>(R(0), ps.spread, vtx.mean_curvature, s.roughness);
+        else { ps.spread = rd_refract<R>(R(0), ps.spread, vtx.mean_curvature, s.eta, s.roughness); ps.eta_scale /= (s.eta * s.eta); }
         ps.dir = s.dir_out;
         ps.f = bsdf_eval_ms<R, MS>(sc, vtx, dir_view, s.dir_out);
         ps.p2 = bsdf_pdf_ms<R, MS>(sc, vtx, dir_view, s.dir_out);
@@ -109,6 +117,15 @@ GD_D bool path_finish_iteration(const DScene<R> &sc, PathState<R> &ps, bool shad
         V3<R> C2 = (G * ps.f) * L;
         C2 = C2 / p2;
         ps.rad = ps.rad + ps.thr * C2;
+    }
+    if (!hit && sc.env_light >= 0) {             // :233-246: the environment map seen along the BSDF ray, weighted by w2
+        V3<R> L = env_emission<R>(sc, -ps.dir, ps.spread);
+        V3<R> C2 = (G * ps.f) * L;
+        LightPoint<R> lp; lp.position = V3<R>(R(0), R(0), R(0)); lp.normal = -ps.dir;
+        R p1 = light_pmf<R>(sc, sc.env_light) * env_pdf_point<R>(sc, lp);
+        R w2 = (p2 * p2) / (p1 * p1 + p2 * p2);
+        C2 = C2 / p2;
+        ps.rad = ps.rad + (ps.thr * C2) * w2;
     }
     if (!hit) return false;
     R rr = R(1);
@@ -148,6 +165,7 @@ __global__ void __launch_bounds__(128) k_path_generate(DScene<R> sc, WaveParams 
         R ry = pcg_real<R>(ps.rng), rx = pcg_real<R>(ps.rng);
         sample_primary<R>(sc, (R(ps.px) + rx) / R(sc.width), (R(ps.py) + ry) / R(sc.height), ps.org, ps.dir);
         ps.thr = V3<R>(R(1), R(1), R(1)); ps.eta_scale = R(1); ps.nv = 3;
+        ps.spread = R(0.25) / R(sc.width > sc.height ? sc.width : sc.height);   // init_ray_differential (ray.h:35-37)
         r.ox = (float)ps.org.x; r.oy = (float)ps.org.y; r.oz = (float)ps.org.z; r.dx = (float)ps.dir.x; r.dy = (float)ps.dir.y; r.dz = (float)ps.dir.z;
         r.tnear = 0.f; r.tfar = __int_as_float(0x7f800000);
     }
@@ -170,11 +188,12 @@ __global__ void __launch_bounds__(128) k_path_shade(DScene<R> sc, WaveParams wp,
         if (FIRST) {
             if (ps.px >= 0) {
                 if (h.shape_id >= 0) {
-                    const R spread0 = R(0.25) / R(sc.width > sc.height ? sc.width : sc.height);   // init_ray_differential
                     Vertex<R> vtx;
-                    make_vertex_ms<R, MS>(sc, ps.org, ps.dir, 0.f, __int_as_float(0x7f800000), h, R(0), spread0, vtx);
+                    make_vertex_ms<R, MS>(sc, ps.org, ps.dir, 0.f, __int_as_float(0x7f800000), h, R(0), ps.spread, vtx);
                     if (is_light(sc, vtx.shape_id)) ps.rad = ps.rad + ps.thr * emission<R>(sc, vtx, -ps.dir);
                     alive = path_begin_iteration<R, MS>(sc, vtx, ps.dir, ps, ray, shadow);
+                } else if (sc.env_light >= 0) {
+                    ps.rad = env_emission<R>(sc, -ps.dir, ps.spread);                             // :28-38: the background
                 }
                 if (!alive) path_finish<R>(wp, ps);
             }

@@ -73,6 +73,15 @@ template <typename R> struct DScene {
     const int *light_shape;       // [n_lights] shape id, -1 for an environment map
     const R *tri_cdf;             // pooled; DShape::cdf_off
     const R *shape_area;          // [n_shapes] surface_area(shape)
+    // environment map (src/light.h:23-30, lights/envmap.inl): image texture, scale, transforms and the TableDist2D
+    // (table_dist.cpp:45-151) over luminance * sin(elevation) of its level-0 texels; env_light < 0: none
+    int env_light, env_tex, env_w, env_h;
+    R env_scale;
+    R env_to_world[16], env_to_local[16];
+    const R *env_cdf_rows;        // [h][w + 1]
+    const R *env_pdf_rows;        // [h][w]
+    const R *env_cdf_marg;        // [h + 1]
+    const R *env_pdf_marg;        // [h]
     R eps;                        // get_intersection_epsilon (scene.h:104-106)
     int max_depth, rr_depth;
 };

@@ -107,6 +107,13 @@ std::string FlatScene::build(const Container &c) {
     desc.shapes = shapes.data(); desc.shape_offsets = offsets.data(); desc.spheres = spheres.data();
     desc.positions = positions.data(); desc.indices = indices.data(); desc.normals = normals.data(); desc.uvs = uvs.data();
     desc.materials = materials.data(); desc.textures = textures.data(); desc.lights = lights.data();
+    // Envmap::to_world / to_local (src/light.h:23-30), present when the scene has an environment map
+    desc.envmap_to_world = desc.envmap_to_local = nullptr;
+    if (c.count("envmap.to_world") && c.count("envmap.to_local")) {
+        if (!take(c, "envmap.to_world", "f8", envmap_to_world, err) || !take(c, "envmap.to_local", "f8", envmap_to_local, err)) return err;
+        if (envmap_to_world.size() != 16 || envmap_to_local.size() != 16) return "envmap matrices have the wrong shape";
+        desc.envmap_to_world = envmap_to_world.data(); desc.envmap_to_local = envmap_to_local.data();
+    }
 
     // images: "<prefix>.<i>.size" + either ".data" (doubles) or ".palette" + ".index" (bytes)
     for (int pass = 0; pass < 2; pass++) {

@@ -35,7 +35,7 @@ struct FlatScene {
     int integrator = 7;             // Integrator::GradPath (src/scene.h:14-23)
     std::vector<int32_t> shapes, indices;
     std::vector<int64_t> offsets;
-    std::vector<double> spheres, positions, normals, uvs, materials, textures, lights;
+    std::vector<double> spheres, positions, normals, uvs, materials, textures, lights, envmap_to_world, envmap_to_local;
     std::vector<std::vector<double>> image_data, palettes;
     std::vector<std::vector<uint8_t>> image_index;
     std::vector<gdpt_image> images3, images1;

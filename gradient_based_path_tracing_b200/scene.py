@@ -179,6 +179,9 @@ class Scene:
         d.lights = _capi.as_dp(dbl("lights", 5))
         d.max_depth, d.rr_depth = self.options.max_depth, self.options.rr_depth
         d.samples_per_pixel = self.options.samples_per_pixel
+        if "envmap.to_world" in a and "envmap.to_local" in a:      # Envmap::to_world / to_local (src/light.h:23-30)
+            d.envmap_to_world = _capi.as_dp(dbl("envmap.to_world", 4))
+            d.envmap_to_local = _capi.as_dp(dbl("envmap.to_local", 4))
         return d
 
     def context(self, device=0):

@@ -68,9 +68,13 @@ typedef struct {
     const gdpt_image *images3, *images1;
     /* Lights (src/light.h:15-34) */
     int32_t n_lights;
-    const double *lights;         /* [n][5]: kind(0 area, 1 envmap — ignored by gradpath), shape_id, intensity rgb */
+    const double *lights;         /* [n][5]: area light: 0, shape_id, intensity rgb;  environment map (src/light.h:23-30; ignored by
+                                   * gradpath, used by path): 1, texture id of `values` (an image texture; -1: not provided), scale, 0, 0 */
     /* RenderOptions (src/scene.h:25-32) */
     int32_t max_depth, rr_depth, samples_per_pixel;
+    /* Envmap::to_world / to_local, row-major 4x4 each; NULL when the scene has no environment map (or does not provide it:
+     * the path integrator then refuses the scene) */
+    const double *envmap_to_world, *envmap_to_local;
 } gdpt_scene_desc;
 
 typedef struct {
@@ -173,7 +177,8 @@ int gdpt_bsdf(gdpt_ctx *ctx, int precision, int mat_id, int n, const double *vtx
 int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, const int32_t *xs, const int32_t *ys,
                       const uint64_t *streams, double *rec);
 /* ---- the plain `path` integrator (render.cpp:74-117, path_tracing.h:13-348): NEE + MIS on the same kernels.
- * Area lights (spheres, meshes); scenes with an environment-map light return GDPT_ERR_UNSUPPORTED. ---- */
+ * Area lights (spheres, meshes) and an image environment map (envmap.inl, TableDist2D); a scene whose environment map
+ * was not provided in the description returns GDPT_ERR_UNSUPPORTED. ---- */
 /* path_render end to end: out_image = W*H*3 doubles (host), the Image3 render() returns for Integrator::Path */
 int gdpt_render_path(gdpt_ctx *ctx, const gdpt_render_params *params, double *out_image);
 /* same accumulation into a caller-provided DEVICE image (already zeroed or holding earlier passes / other bands) */

@@ -282,6 +282,7 @@ VARIANTS = {
     "veach_mi_small": ("veach_mi", "mi.xml", dict(integrator="gradpath", max_depth=-1, spp=4, width=96, height=64)),
     "disney_gradpath": ("disney_bsdf_test", "disney_bsdf.xml", dict(integrator="gradpath", spp=256, extra_xml=AREA_EMITTER_XML)),
     "disney_small": ("disney_bsdf_test", "disney_bsdf.xml", dict(integrator="gradpath", spp=4, width=96, height=72, extra_xml=AREA_EMITTER_XML)),
+    "matpreview_small": ("matpreview", "matpreview.xml", dict(width=96, height=72, spp=4)),
     "sponza_1080p": ("sponza", "sponza.xml", dict(integrator="gradpath", width=1920, height=1080, spp=512)),
     "sponza_2160p": ("sponza", "sponza.xml", dict(integrator="gradpath", width=3840, height=2160, spp=1024)),
     "sponza_native": ("sponza", "sponza.xml", dict(integrator="gradpath")),

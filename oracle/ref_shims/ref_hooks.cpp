@@ -438,15 +438,19 @@ int gdpt_ref_export(void *hs, const char *path) {
                                mf.add(p->specular), mf.add(p->roughness), mf.add(p->specular_tint), mf.add(p->anisotropic),
                                mf.add(p->sheen), mf.add(p->sheen_tint), mf.add(p->clearcoat), mf.add(p->clearcoat_gloss)});
     }
-    w.arr("materials", "f8", {(int64_t)s->materials.size(), 14}, mf.mats.data(), mf.mats.size() * 8);
-    w.arr("textures", "f8", {(int64_t)mf.ntex, 14}, mf.tex.data(), mf.tex.size() * 8);
-
-    // lights: kind (0 area, 1 envmap), shape_id, intensity3
+    // lights: kind (0 area, 1 envmap); area: shape_id, intensity3; envmap: texture id of `values` (appended to the
+    // texture table), scale — its to_world / to_local matrices go into their own arrays (src/light.h:23-30)
     std::vector<double> lights;
     for (const Light &l : s->lights) {
         if (auto *a = std::get_if<DiffuseAreaLight>(&l)) lights.insert(lights.end(), {0, (double)a->shape_id, a->intensity.x, a->intensity.y, a->intensity.z});
-        else lights.insert(lights.end(), {1, -1, 0, 0, 0});
+        else if (auto *e = std::get_if<Envmap>(&l)) {
+            lights.insert(lights.end(), {1, (double)mf.add(e->values), e->scale, 0, 0});
+            w.arr("envmap.to_world", "f8", {4, 4}, e->to_world.data, 128);
+            w.arr("envmap.to_local", "f8", {4, 4}, e->to_local.data, 128);
+        }
     }
+    w.arr("materials", "f8", {(int64_t)s->materials.size(), 14}, mf.mats.data(), mf.mats.size() * 8);
+    w.arr("textures", "f8", {(int64_t)mf.ntex, 14}, mf.tex.data(), mf.tex.size() * 8);
     w.arr("lights", "f8", {(int64_t)s->lights.size(), 5}, lights.data(), lights.size() * 8);
 
     export_images<Vector3>(w, "img3", s->texture_pool.image3s);

@@ -23,7 +23,11 @@ from oracle import ref  # noqa: E402
 def main():
     ref.stage_scenes()
     rng = np.random.default_rng(20261105)
-    for name, n in [("cbox_gdpt_64", 3000), ("cbox_gdpt_d2", 1500), ("veach_mi_small", 3000), ("sponza_small", 3000)]:
+    only = sys.argv[1:]
+    for name, n in [("cbox_gdpt_64", 3000), ("cbox_gdpt_d2", 1500), ("veach_mi_small", 3000), ("sponza_small", 3000),
+                    ("matpreview_small", 3000), ("disney_small", 3000)]:      # the last two: environment map (+ a sphere light)
+        if only and name not in only:
+            continue
         s = ref.RefScene(ref.scene_path(name))
         xs = rng.integers(0, s.width, n).astype(np.int32); ys = rng.integers(0, s.height, n).astype(np.int32)
         st = rng.integers(0, 2 ** 40, n).astype(np.uint64)
@@ -43,7 +47,11 @@ def main():
         d = out[:, 1:4] - pts
         dist = np.linalg.norm(d, axis=1, keepdims=True)
         eps = 1e-4
-        shadow = np.concatenate([pts, d / dist, np.full_like(dist, eps), (1 - eps) * dist], axis=1)
+        env = (out[:, 1:4] == 0).all(axis=1)          # environment-map samples: direction = -normal, shadow ray to infinity
+        d[env] = -out[env, 4:7]; dist[env] = 1.0
+        tfar = (1 - eps) * dist
+        tfar[env] = np.inf
+        shadow = np.concatenate([pts, d / dist, np.full_like(dist, eps), tfar], axis=1)
         # ... and segments between random pairs of surface points
         perm = rng.permutation(pts.shape[0])
         d2 = pts[perm] - pts
@@ -54,9 +62,10 @@ def main():
         np.savez_compressed(os.path.join(HERE, "lights_%s.npz" % name), ref_points=pts, rnd=rnd, out=out,
                             occ_rays=occ_rays, occluded=s.occluded(occ_rays))
         s.close()
-    s = ref.RefScene(ref.scene_path("cbox_gdpt_64"))
-    np.savez_compressed(os.path.join(HERE, "path_image_cbox64.npz"), img=s.render_path_pixelseed(4))
-    s.close()
+    if not only:
+        s = ref.RefScene(ref.scene_path("cbox_gdpt_64"))
+        np.savez_compressed(os.path.join(HERE, "path_image_cbox64.npz"), img=s.render_path_pixelseed(4))
+        s.close()
     print("path golden fixtures written to", HERE)
 
 

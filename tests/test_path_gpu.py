@@ -9,7 +9,7 @@ from conftest import golden
 
 pytestmark = pytest.mark.gpu
 
-PATH_SCENES = ["cbox_gdpt_64", "cbox_gdpt_d2", "veach_mi_small", "sponza_small"]
+PATH_SCENES = ["cbox_gdpt_64", "cbox_gdpt_d2", "veach_mi_small", "sponza_small", "matpreview_small", "disney_small"]   # the last two: environment map
 
 
 @pytest.fixture(scope="module")
@@ -99,10 +99,36 @@ def test_path_full_size_sponza(g, scenes):
     assert st["rays_traced"] > 1920 * 1080 * 3
 
 
-def test_path_refuses_environment_maps(g, scenes):
-    sc = scenes("disney_small")
-    with pytest.raises(g._capi.GdptError):
-        g.path_render(sc, spp=1)
+def test_path_refuses_an_environment_map_that_was_not_provided(g, scenes):
+    """Containers written before the envmap export carry the light row but not its image/transforms: path refuses, gradpath
+    (which ignores environment maps as shipped) still renders."""
+    a = {k: v for k, v in scenes("disney_small").a.items() if not k.startswith("envmap.")}
+    sc = g.Scene(a)
+    try:
+        with pytest.raises(g._capi.GdptError):
+            g.path_render(sc, spp=1)
+        assert np.isfinite(g.gradient_path_render(sc, spp=1, precision="f32").primal).all()
+    finally:
+        sc.close()
+
+
+def test_path_environment_map_background(g, scenes):
+    """Primary rays that leave the scene return the environment map (path_tracing.h:28-38): with max_depth = 1 (no loop
+    iteration) the image is the background where the pixel sees no geometry and black elsewhere (no emitter in view)."""
+    sc = scenes("matpreview_small")
+    a = g.path_render(sc, spp=1, precision="f64", max_depth=1)
+    b = g.path_render(sc, spp=1, precision="f64", max_depth=1)
+    assert np.array_equal(a, b) and np.isfinite(a).all()
+    ys, xs = np.mgrid[0:sc.height, 0:sc.width]
+    sp = np.stack([(xs.ravel() + 0.5) / sc.width, (ys.ravel() + 0.5) / sc.height], axis=1)
+    rays6 = g.sample_primary(sc, sp)
+    rays = np.concatenate([rays6, np.zeros((sp.shape[0], 1)), np.full((sp.shape[0], 1), np.inf)], axis=1)
+    ids, _ = g.intersect(sc, rays)
+    miss = (ids[:, 0] < 0).reshape(sc.height, sc.width)
+    lit = (a.sum(axis=2) > 0)
+    if miss.any():
+        assert lit[miss].mean() > 0.9          # the sample is jittered inside the pixel: silhouette pixels may differ
+    assert lit[~miss].mean() < 0.1
 
 
 @pytest.mark.parametrize("name", ["cbox_gdpt_64", "veach_mi_small"])

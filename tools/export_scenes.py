@@ -19,7 +19,7 @@ from oracle import ref  # noqa: E402
 from gradient_based_path_tracing_b200.scene import read_container, write_container  # noqa: E402
 
 OUT = os.path.join(ROOT, "scenes")
-FULL = ["cbox_gdpt", "cbox_gdpt_64", "cbox_gdpt_d2", "veach_mi_gradpath", "veach_mi_small", "disney_gradpath", "sponza_1080p"]
+FULL = ["cbox_gdpt", "cbox_gdpt_64", "cbox_gdpt_d2", "veach_mi_gradpath", "veach_mi_small", "disney_gradpath", "matpreview_small", "sponza_1080p"]
 from gradient_based_path_tracing_b200.scene import OVERLAY_BASE as CAMERA_ONLY  # noqa: E402
 
 
