@@ -61,7 +61,7 @@ class GdptDistGeom(C.Structure):
 EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_destroy", "gdpt_scene_bounds", "gdpt_render",
            "gdpt_render_accumulate_device", "gdpt_merge_device", "gdpt_poisson", "gdpt_poisson_device", "gdpt_get_stats",
            "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill",
-           "gdpt_render_path", "gdpt_render_path_accumulate_device", "gdpt_path_samples", "gdpt_sample_light", "gdpt_occluded",
+           "gdpt_render_path", "gdpt_render_path_accumulate_device", "gdpt_path_samples", "gdpt_sample_light", "gdpt_occluded", "gdpt_render_aux",
            "gdpt_merge_rows_device", "gdpt_poisson_dist_rows_forward", "gdpt_poisson_dist_columns", "gdpt_poisson_dist_rows_inverse"]
 
 _lib = None
@@ -102,6 +102,7 @@ def lib():
         L.gdpt_path_samples.argtypes = [vp, C.POINTER(GdptRenderParams), C.c_int, ip, ip, C.POINTER(C.c_uint64), dp]
         L.gdpt_sample_light.argtypes = [vp, C.c_int, C.c_int, dp, dp, dp]
         L.gdpt_occluded.argtypes = [vp, C.c_int, C.c_int, dp, ip]
+        L.gdpt_render_aux.argtypes = [vp, C.c_int, C.c_int, dp]
         L.gdpt_pcg_fill.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.c_int, dp, C.POINTER(C.c_uint32)]
         _lib = L
     return _lib

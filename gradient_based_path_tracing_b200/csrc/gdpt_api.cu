@@ -16,6 +16,9 @@ template <typename R> int dbg_sample_light(gdpt_ctx *ctx, const DScene<R> &sc, i
 extern template int dbg_sample_light<double>(gdpt_ctx *, const DScene<double> &, int, const double *, const double *, double *);
 extern template int dbg_sample_light<float>(gdpt_ctx *, const DScene<float> &, int, const double *, const double *, double *);
 int dbg_occluded(gdpt_ctx *ctx, bool exact, int n, const double *rays, int32_t *out);
+template <typename R> int dbg_aux(gdpt_ctx *ctx, const DScene<R> &sc, int kind, double *out);
+extern template int dbg_aux<double>(gdpt_ctx *, const DScene<double> &, int, double *);
+extern template int dbg_aux<float>(gdpt_ctx *, const DScene<float> &, int, double *);
 int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
 int merge_device(gdpt_ctx *ctx, int w, int h, int ya, int yb, const double *d_cx0, const double *d_cx1, const double *d_cy0, const double *d_cy1, double *d_cx, double *d_cy);
 int poisson_dist_rows_forward(gdpt_ctx *c, const gdpt_dist_geom *g, const double *d_u, const double *d_gx, const double *d_gy, double alpha,
@@ -372,6 +375,13 @@ int gdpt_occluded(gdpt_ctx *ctx, int precision, int n, const double *rays, int32
     if (n == 0) return 0;
     GD_CUDA(cudaSetDevice(ctx->device));
     return dbg_occluded(ctx, precision == GDPT_PRECISION_F64, n, rays, out);
+}
+
+int gdpt_render_aux(gdpt_ctx *ctx, int integrator, int precision, double *out_image) {
+    if (!ctx || !out_image) return fail(GDPT_ERR_ARG, "null argument");
+    if (integrator < 0 || integrator > 4) return fail(GDPT_ERR_ARG, "integrator %d is not an auxiliary buffer (0 depth .. 4 mipmapLevel)", integrator);
+    GD_CUDA(cudaSetDevice(ctx->device));
+    return precision == GDPT_PRECISION_F64 ? dbg_aux<double>(ctx, ctx->sc_d, integrator, out_image) : dbg_aux<float>(ctx, ctx->sc_f, integrator, out_image);
 }
 
 int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, const int32_t *xs, const int32_t *ys,

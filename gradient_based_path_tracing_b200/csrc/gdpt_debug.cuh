@@ -93,4 +93,41 @@ static __global__ void k_dbg_sample_light(DScene<R> sc, int n, const double *ref
     o[7] = pdf_point_on_light<R>(sc, id, p, ref); o[8] = light_pmf<R>(sc, id);
 }
 
+// aux_render (/root/reference/src/render.cpp:15-72): one ray through every pixel centre, a function of the primary
+// vertex per Integrator value (src/scene.h:14-23): 0 depth, 1 shading normal, 2 mean curvature, 3 ray differential
+// (radius, spread, 0), 4 mip level of the material's main texture (material.cpp:121-123).  img: W*H*3 doubles.
+template <typename R, bool EXACT>
+static __global__ void __launch_bounds__(TRACE_BLOCK) k_aux(DScene<R> sc, DBvh bvh, int kind, double *img) {
+    __shared__ int2 stack[STACK_SMEM * TRACE_BLOCK];
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= sc.width * sc.height) return;
+    int x = i % sc.width, y = i / sc.width;
+    V3<R> org, dir;
+    sample_primary<R>(sc, (R(x) + R(0.5)) / R(sc.width), (R(y) + R(0.5)) / R(sc.height), org, dir);
+    const R spread0 = R(0.25) / R(sc.width > sc.height ? sc.width : sc.height);
+    float o[3] = {(float)org.x, (float)org.y, (float)org.z}, d[3] = {(float)dir.x, (float)dir.y, (float)dir.z};
+    Hit h = trace_closest<EXACT, false>(bvh, o, d, 0.f, __int_as_float(0x7f800000), stack);
+    V3<R> color(R(0), R(0), R(0));
+    if (h.shape_id >= 0) {
+        Vertex<R> v;
+        make_vertex<R>(sc, org, dir, 0.f, __int_as_float(0x7f800000), h, R(0), spread0, v);
+        if (kind == 0) { R dist = distance(v.position, org); color = V3<R>(dist, dist, dist); }
+        else if (kind == 1) color = v.sf.n;
+        else if (kind == 2) color = V3<R>(v.mean_curvature, v.mean_curvature, v.mean_curvature);
+        else if (kind == 3) color = V3<R>(R(0), spread0, R(0));
+        else if (kind == 4) {
+            const DMaterial &m = sc.materials[v.material_id];
+            int tid = m.type == MAT_DISNEY_CLEARCOAT ? -1 : m.tex[0];
+            if (tid >= 0 && sc.textures[tid].kind == TEX_IMAGE) {
+                const DTexture<R> &t = sc.textures[tid];
+                const DImage &im = sc.img3[t.image_id];
+                R sf = (R)(im.w[0] > im.h[0] ? im.w[0] : im.h[0]) * rmax(t.uscale, t.vscale) * v.uv_screen_size;
+                R level = log2(rmax(sf, R(1e-8f)));
+                color = V3<R>(level, level, level);
+            }
+        }
+    }
+    img[3 * (size_t)i] = color.x; img[3 * (size_t)i + 1] = color.y; img[3 * (size_t)i + 2] = color.z;
+}
+
 } // namespace gdpt

@@ -73,4 +73,15 @@ template <typename R> int dbg_sample_light(gdpt_ctx *ctx, const DScene<R> &sc, i
     return 0;
 }
 
+template <typename R> int dbg_aux(gdpt_ctx *ctx, const DScene<R> &sc, int kind, double *out) {
+    Scratch s; double *dimg;
+    const size_t n = (size_t)sc.width * sc.height;
+    if (int r = s.alloc(&dimg, n * 3)) return r;
+    k_aux<R, ModeSel<R>::exact><<<blocks_for((long long)n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(sc, ctx->bvh, kind, dimg);
+    ctx->stats.kernel_launches++;
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    GD_CUDA(cudaMemcpy(out, dimg, n * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 } // namespace gdpt

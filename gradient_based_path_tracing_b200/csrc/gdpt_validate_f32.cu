@@ -5,4 +5,5 @@ template int dbg_sample_primary<float>(gdpt_ctx *, const DScene<float> &, int, c
 template int dbg_intersect<float>(gdpt_ctx *, const DScene<float> &, int, const double *, const double *, int32_t *, double *);
 template int dbg_bsdf<float>(gdpt_ctx *, const DScene<float> &, int, int, const double *, const double *, const double *, double *);
 template int dbg_sample_light<float>(gdpt_ctx *, const DScene<float> &, int, const double *, const double *, double *);
+template int dbg_aux<float>(gdpt_ctx *, const DScene<float> &, int, double *);
 }

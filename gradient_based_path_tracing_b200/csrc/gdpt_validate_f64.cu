@@ -5,6 +5,7 @@ template int dbg_sample_primary<double>(gdpt_ctx *, const DScene<double> &, int,
 template int dbg_intersect<double>(gdpt_ctx *, const DScene<double> &, int, const double *, const double *, int32_t *, double *);
 template int dbg_bsdf<double>(gdpt_ctx *, const DScene<double> &, int, int, const double *, const double *, const double *, double *);
 template int dbg_sample_light<double>(gdpt_ctx *, const DScene<double> &, int, const double *, const double *, double *);
+template int dbg_aux<double>(gdpt_ctx *, const DScene<double> &, int, double *);
 
 // occluded (intersection.cpp:66-85) through the renderer's any-hit traversal kernel: rays[n][8] -> out[n] (1 = occluded)
 static __global__ void k_dbg_pack_rays(int n, const double *rays, RayF *out) {

@@ -75,7 +75,9 @@ int main(int argc, char *argv[]) {
         else if (a == "-precision") precision = value();
         else if (a == "-device") device = std::stoi(value());
         else if (a == "-seed") seed = std::stoull(value());
-        else if (a == "-integrator") { std::string v = value(); if (v == "path") integrator_override = 5; else if (v == "gradpath") integrator_override = 7; else { std::cerr << "-integrator must be path or gradpath" << std::endl; return 2; } }
+        else if (a == "-integrator") { std::string v = value(); const char *names[] = {"depth", "shadingNormal", "meanCurvature", "rayDifferential", "mipmapLevel", "path", "volpath", "gradpath"};   // parse_scene.cpp:520-566
+            for (int k = 0; k < 8; k++) if (v == names[k]) integrator_override = k;
+            if (integrator_override < 0) { std::cerr << "unknown integrator " << v << std::endl; return 2; } }
         else if (a == "-describe") describe = true;             // print a digest of the flattened scene and exit (no device needed)
         else filenames.push_back(a);
     }
@@ -92,7 +94,8 @@ int main(int argc, char *argv[]) {
         if (err.empty()) err = scene.build(c);
         if (!err.empty()) { std::cerr << err << std::endl; return 1; }
         if (integrator_override >= 0) scene.integrator = integrator_override;
-        if (scene.integrator != 7 && scene.integrator != 5) {   // render() asserts on integrators it does not know (render.cpp:390-393); GradPath and Path live here
+        const bool aux = scene.integrator >= 0 && scene.integrator <= 4;   // depth .. mipmapLevel -> aux_render (render.cpp:374-380)
+        if (scene.integrator != 7 && scene.integrator != 5 && !aux) {   // render() asserts on integrators it does not know (render.cpp:390-393); VolPath is not built
             std::cerr << "integrator " << scene.integrator << " is outside the gradpath hot path" << std::endl;
             return 1;
         }
@@ -110,14 +113,15 @@ int main(int argc, char *argv[]) {
         p.precision = precision == "f64" ? GDPT_PRECISION_F64 : GDPT_PRECISION_F32;
         gdpt_images img{primal.data(), dx.data(), dy.data(), out.data()};
         const bool path = scene.integrator == 5;          // Integrator::Path -> path_render (render.cpp:385-386): one image
-        int rc = path ? gdpt_render_path(ctx, &p, out.data()) : gdpt_render(ctx, &p, &img);
+        int rc = aux ? gdpt_render_aux(ctx, scene.integrator, p.precision, out.data()) : path ? gdpt_render_path(ctx, &p, out.data()) : gdpt_render(ctx, &p, &img);
         gdpt_stats st{};
         gdpt_get_stats(ctx, &st);
         gdpt_destroy(ctx);
         if (rc != GDPT_OK) { std::cerr << gdpt_last_error() << std::endl; return 1; }
         double took = seconds_since(timer);
         std::cout << "Done. Took " << took << " seconds." << std::endl;
-        if (path) std::printf("%.1f Mpaths/s (path, NEE + MIS; %d spp, %lld kernel launches, trace %.1f ms, shade %.1f ms, copies %.1f ms)\n",
+        if (aux) std::printf("auxiliary buffer %d (aux_render)\n", scene.integrator);
+        else if (path) std::printf("%.1f Mpaths/s (path, NEE + MIS; %d spp, %lld kernel launches, trace %.1f ms, shade %.1f ms, copies %.1f ms)\n",
                               1.0 * w * h * p.spp / took / 1e6, p.spp, (long long)st.kernel_launches, st.ms_trace, st.ms_shade, st.ms_copy);
         else std::printf("%.1f Mpaths/s (base + 4 shifts; %d spp, %lld kernel launches, trace %.1f ms, shade %.1f ms, Poisson %.1f ms, copies %.1f ms)\n",
                     5.0 * w * h * p.spp / took / 1e6, p.spp, (long long)st.kernel_launches, st.ms_trace, st.ms_shade, st.ms_poisson, st.ms_copy);
@@ -129,7 +133,7 @@ int main(int argc, char *argv[]) {
         const std::string stem = of.substr(0, of.size() - 4), ext = of.substr(of.size() - 4);
         const std::pair<std::string, const double *> files[] = {{of, out.data()}, {stem + "_primal" + ext, primal.data()}, {stem + "_dx" + ext, dx.data()}, {stem + "_dy" + ext, dy.data()}};
         for (const auto &f : files) {
-            if (path && f.second != out.data()) continue;
+            if ((path || aux) && f.second != out.data()) continue;
             err = write_image(f.first, w, h, f.second);
             if (!err.empty()) { std::cerr << err << std::endl; return 1; }
         }

@@ -68,9 +68,26 @@ def path_render(scene, device=0, **kw):
     return img
 
 
+AUX_INTEGRATORS = (Integrator.Depth, Integrator.ShadingNormal, Integrator.MeanCurvature, Integrator.RayDifferential, Integrator.MipmapLevel)
+
+
+def aux_render(scene, integrator=None, precision="f64", device=0):
+    """aux_render (render.cpp:15-72): depth / shading normal / mean curvature / ray differential / mip level of the
+    primary vertex of every pixel centre, (H, W, 3)."""
+    kind = Integrator(scene.options.integrator if integrator is None else integrator)
+    if kind not in AUX_INTEGRATORS:
+        raise ValueError("%s is not an auxiliary integrator" % kind.name)
+    img = np.zeros((scene.height, scene.width, 3), dtype=np.float64)
+    _capi.check(_capi.lib().gdpt_render_aux(scene.context(device), int(kind), _prec(precision), _capi.as_dp(img)))
+    return img
+
+
 def render(scene, device=0, **kw):
     """Image3 render(const Scene&) (render.cpp:373-395): dispatch on scene.options.integrator; GradPath and Path
-    live here, any other integrator ends like the reference's `assert(false)` arm."""
+    and the
+    auxiliary buffers live here; VolPath ends like the reference's `assert(false)` arm."""
+    if scene.options.integrator in AUX_INTEGRATORS:
+        return aux_render(scene, precision=kw.get("precision", "f64"), device=device)
     if scene.options.integrator == Integrator.Path:
         return path_render(scene, device, **kw)
     if scene.options.integrator != Integrator.GradPath:

@@ -191,6 +191,10 @@ int gdpt_path_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, co
 int gdpt_sample_light(gdpt_ctx *ctx, int precision, int n, const double *ref_points, const double *rnd, double *out);
 /* occluded (intersection.cpp:66-85): rays[n][8] = org, dir, tnear, tfar; out[n] = 1 if anything is hit in (tnear, tfar] */
 int gdpt_occluded(gdpt_ctx *ctx, int precision, int n, const double *rays, int32_t *out);
+/* aux_render (render.cpp:15-72): the auxiliary integrators of render() — `integrator` is the Integrator enum value
+ * (src/scene.h:14-23): 0 depth, 1 shadingNormal, 2 meanCurvature, 3 rayDifferential, 4 mipmapLevel; one ray through every
+ * pixel centre; out_image = W*H*3 doubles (host).  Cheap always-available validation channels. */
+int gdpt_render_aux(gdpt_ctx *ctx, int integrator, int precision, double *out_image);
 /* PCG32 (pcg.h): first n doubles (and raw 32-bit outputs, may be NULL) of a stream, generated on the device */
 int gdpt_pcg_fill(int device, uint64_t stream, uint64_t seed, int n, double *out, uint32_t *raw);
 

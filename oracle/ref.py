@@ -47,6 +47,7 @@ def lib():
         L.gdpt_ref_intersect.argtypes = [C.c_void_p, C.c_int, dp, dp, ip, dp]
         L.gdpt_ref_bsdf.argtypes = [C.c_void_p, C.c_int, C.c_int, dp, dp, dp, dp]
         L.gdpt_ref_export.argtypes = [C.c_void_p, C.c_char_p]
+        L.gdpt_ref_render_aux.argtypes = [C.c_void_p, C.c_int, dp]
         L.gdpt_ref_imread3.argtypes = [C.c_char_p, ip, ip, dp]
         L.gdpt_ref_path_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, dp]
         L.gdpt_ref_sample_light.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
@@ -167,6 +168,13 @@ class RefScene:
         out = self._img()
         with _quiet():
             lib().gdpt_ref_render_path(self.h, _dp(out))
+        return out
+
+    def render_aux(self, integrator):
+        """aux_render (src/render.cpp:15-72) for Integrator value 0..4."""
+        out = self._img()
+        with _quiet():
+            lib().gdpt_ref_render_aux(self.h, int(integrator), _dp(out))
         return out
 
     def grad_sample(self, x, y, stream, seed=DEFAULT_SEED):

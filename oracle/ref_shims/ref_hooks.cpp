@@ -192,6 +192,18 @@ int gdpt_ref_render_path(void *hs, double *out) {
     return 0;
 }
 
+// The reference's auxiliary integrators (aux_render, src/render.cpp:15-72) through render(): `integrator` is the enum
+// value 0..4 (depth, shadingNormal, meanCurvature, rayDifferential, mipmapLevel).  out: W*H*3.
+int gdpt_ref_render_aux(void *hs, int integrator, double *out) {
+    Scene *s = (Scene *)hs;
+    Integrator saved = s->options.integrator;
+    s->options.integrator = (Integrator)integrator;
+    Image3 img = render(*s);
+    memcpy(out, img.data.data(), sizeof(double) * 3 * img.data.size());
+    s->options.integrator = saved;
+    return 0;
+}
+
 void gdpt_ref_fourier_solve(int w, int h, const double *u, const double *gx, const double *gy, double alpha, double *out) {
     fourierSolve(w, h, u, gx, gy, alpha, out);
 }

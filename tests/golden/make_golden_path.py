@@ -62,6 +62,15 @@ def main():
         np.savez_compressed(os.path.join(HERE, "lights_%s.npz" % name), ref_points=pts, rnd=rnd, out=out,
                             occ_rays=occ_rays, occluded=s.occluded(occ_rays))
         s.close()
+    # auxiliary integrators (aux_render, src/render.cpp:15-72): depth, shading normal, mean curvature, ray differential, mip level
+    if not only or "aux" in only:
+        out = {}
+        for name in ("cbox_gdpt_64", "veach_mi_small", "sponza_small"):
+            s = ref.RefScene(ref.scene_path(name))
+            for kind in range(5):
+                out["%s.%d" % (name, kind)] = s.render_aux(kind)
+            s.close()
+        np.savez_compressed(os.path.join(HERE, "aux_images.npz"), **out)
     if not only:
         s = ref.RefScene(ref.scene_path("cbox_gdpt_64"))
         np.savez_compressed(os.path.join(HERE, "path_image_cbox64.npz"), img=s.render_path_pixelseed(4))

@@ -156,3 +156,24 @@ def test_path_queues_and_tail_kernel_agree(g, name, monkeypatch):
         sc.close()
     for tag in ("plain", "tail"):
         assert np.allclose(imgs["sorted"], imgs[tag], rtol=1e-9, atol=1e-12), tag
+
+
+@pytest.mark.parametrize("name", ["cbox_gdpt_64", "veach_mi_small", "sponza_small"])
+def test_aux_integrators_match_reference(g, scenes, name):
+    """aux_render (render.cpp:15-72): depth, shading normal, mean curvature, ray differential and mip level of the primary
+    vertex at every pixel centre, against the reference's own render() for Integrator values 0..4."""
+    z = golden("aux_images.npz")
+    sc = scenes(name)
+    for kind in range(5):
+        want = z["%s.%d" % (name, kind)]
+        got = g.aux_render(sc, integrator=kind, precision="f64")
+        ok = np.isclose(got, want, rtol=1e-9, atol=1e-12, equal_nan=True).all(axis=2)
+        assert ok.mean() > 0.998, "integrator %d: %d pixels differ" % (kind, (~ok).sum())   # pixel-centre rays on a silhouette edge
+    saved = sc.options.integrator
+    sc.options.integrator = g.Integrator.Depth
+    try:
+        assert np.array_equal(g.render(sc), g.aux_render(sc, integrator=0))
+    finally:
+        sc.options.integrator = saved
+    depth32 = g.aux_render(sc, integrator=0, precision="f32")
+    assert np.allclose(depth32, z["%s.0" % name], rtol=1e-3, atol=1e-3) or (np.isclose(depth32, z["%s.0" % name], rtol=1e-3, atol=1e-3).mean() > 0.99)
