@@ -48,6 +48,17 @@ template <typename R> GD_D R GTR2(R n_dot_h, R roughness) {
     R t = R(1) + (a2 - R(1)) * n_dot_h * n_dot_h;
     return a2 / (Consts<R>::PI * t * t);
 }
+// GTR2 at the half vector h.  double: the reference's expression on n.h, literally.  float: 1 + (a2 - 1) cos^2 loses
+// everything to cancellation once a2 < 2^-24 (roughness 0.01 gives a2 = 1e-8), so the same number is formed from the
+// local components, sin^2 + a2 cos^2, which has no subtraction.
+template <typename R> GD_D R GTR2_at(const Frame<R> &f, const V3<R> &h, R roughness) {
+    if (sizeof(R) == 8) return GTR2(dot(f.n, h), roughness);
+    V3<R> hl = to_local(f, h);
+    R alpha = roughness * roughness;
+    R a2 = alpha * alpha;
+    R t = hl.x * hl.x + hl.y * hl.y + a2 * hl.z * hl.z;
+    return a2 / (Consts<R>::PI * t * t);
+}
 template <typename R> GD_D R smith_masking_gtr2(const V3<R> &v_local, R roughness) {
     R alpha = roughness * roughness;
     R a2 = alpha * alpha;
@@ -128,7 +139,7 @@ template <typename R> GD_D V3<R> eval_roughplastic(const BCtx<R> &c, const V3<R>
     R roughness = clampr(c.t1(m.tex[2]), R(0.01), R(1));
     R eta = (R)m.eta;
     R F_o = fresnel_dielectric(dot(h, dir_out), eta);
-    R D = GTR2(n_dot_h, roughness);
+    R D = GTR2_at(f, h, roughness);
     R G = smith_masking_gtr2(to_local(f, c.dir_in), roughness) * smith_masking_gtr2(to_local(f, dir_out), roughness);
     V3<R> spec = Ks * (G * F_o * D) / (R(4) * n_dot_in * n_dot_out);
     R F_i = fresnel_dielectric(dot(h, c.dir_in), eta);
@@ -148,7 +159,7 @@ template <typename R> GD_D R pdf_roughplastic(const BCtx<R> &c, const V3<R> &dir
     R spec_prob = lS / (lS + lR);
     R diff_prob = R(1) - spec_prob;
     R G = smith_masking_gtr2(to_local(f, c.dir_in), roughness);
-    R D = GTR2(n_dot_h, roughness);
+    R D = GTR2_at(f, h, roughness);
     spec_prob *= (G * D) / (R(4) * n_dot_in);
     diff_prob *= n_dot_out / Consts<R>::PI;
     return spec_prob + diff_prob;
@@ -191,7 +202,7 @@ template <typename R> GD_D V3<R> eval_roughdielectric(const BCtx<R> &c, const V3
     roughness = clampr(roughness, R(0.01), R(1));
     R h_dot_in = dot(h, c.dir_in);
     R F = fresnel_dielectric(h_dot_in, eta);
-    R D = GTR2(dot(f.n, h), roughness);
+    R D = GTR2_at(f, h, roughness);
     R G = smith_masking_gtr2(to_local(f, c.dir_in), roughness) * smith_masking_gtr2(to_local(f, dir_out), roughness);
     if (reflect) return Ks * (F * D * G) / (R(4) * fabs(dot(f.n, c.dir_in)));
     R eta_factor = R(1) / (eta * eta);   // TransportDirection::TO_LIGHT (default argument everywhere on this path)
@@ -208,7 +219,7 @@ template <typename R> GD_D R pdf_roughdielectric(const BCtx<R> &c, const V3<R> &
     R roughness = clampr(c.t1(m.tex[2]), R(0.01), R(1));
     R h_dot_in = dot(h, c.dir_in);
     R F = fresnel_dielectric(h_dot_in, eta);
-    R D = GTR2(dot(h, f.n), roughness);
+    R D = GTR2_at(f, h, roughness);
     R G_in = smith_masking_gtr2(to_local(f, c.dir_in), roughness);
     if (reflect) return (F * D * G_in) / (R(4) * fabs(dot(f.n, c.dir_in)));
     R h_dot_out = dot(h, dir_out);

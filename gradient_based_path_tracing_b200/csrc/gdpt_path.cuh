@@ -40,7 +40,18 @@ GD_D void path_finish(const WaveParams &wp, const PathState<R> &ps) {
     size_t p = ((size_t)ps.py * wp.width + ps.px) * 3;
     double inv_spp = 1.0 / (double)wp.spp_total;
     double rd[3] = {(double)ps.rad.x, (double)ps.rad.y, (double)ps.rad.z};
+    // float mode: a sample whose products left the float range (near-specular chains) is dropped instead of poisoning the
+    // pixel; the double mode keeps whatever the reference's arithmetic gives
+    if (sizeof(R) == 4 && !(isfinite(rd[0]) && isfinite(rd[1]) && isfinite(rd[2]))) return;
     for (int c = 0; c < 3; c++) if (rd[c] != 0.0) atomicAdd(wp.img + p + c, rd[c] * inv_spp);
+}
+
+// power heuristic p_a^2 / (p_a^2 + p_b^2) (p_a > 0).  double: the reference's expression, literally; float: the same
+// number from the ratio, because the squares of specular pdfs leave the float range (inf / inf)
+template <typename R> GD_D R mis_weight(R pa, R pb) {
+    if (sizeof(R) == 8) return (pa * pa) / (pa * pa + pb * pb);
+    R r = pb / pa;
+    return R(1) / (R(1) + r * r);
 }
 
 GD_D void disable_ray(RayF &r) { r.ox = r.oy = r.oz = 0.f; r.dx = r.dy = r.dz = 0.f; r.tnear = 0.f; r.tfar = -1.f; }
@@ -68,7 +79,7 @@ GD_D bool path_begin_iteration(const DScene<R> &sc, const Vertex<R> &vtx, const 
             V3<R> L = light_emission<R>(sc, light_id, -dir_light, pl);
             V3<R> C1 = (G * fl) * L;
             R p2l = bsdf_pdf_ms<R, MS>(sc, vtx, dir_view, dir_light) * G;
-            R w1 = (p1 * p1) / (p1 * p1 + p2l * p2l);
+            R w1 = mis_weight<R>(p1, p2l);
             C1 = C1 / p1;
             ps.nee = (ps.thr * C1) * w1;
             if (ps.nee.x != R(0) || ps.nee.y != R(0) || ps.nee.z != R(0)) {
@@ -123,7 +134,7 @@ GD_D bool path_finish_iteration(const DScene<R> &sc, PathState<R> &ps, bool shad
         V3<R> C2 = (G * ps.f) * L;
         LightPoint<R> lp; lp.position = V3<R>(R(0), R(0), R(0)); lp.normal = -ps.dir;
         R p1 = light_pmf<R>(sc, sc.env_light) * env_pdf_point<R>(sc, lp);
-        R w2 = (p2 * p2) / (p1 * p1 + p2 * p2);
+        R w2 = mis_weight<R>(p2, p1);
         C2 = C2 / p2;
         ps.rad = ps.rad + (ps.thr * C2) * w2;
     }
