@@ -96,31 +96,11 @@ struct gdpt_ctx {
 
 namespace gdpt {
 
-// make_mipmap (mipmap.h:28-44): 2x2 box filter, at most 8 levels.  The reference indexes
-// prev(2x+1, 2y+1) even when a dimension has already collapsed to 1, i.e. it reads the flat
-// element y*width+x beyond the row / the image; we reproduce the flat indexing and clamp
-// the final out-of-bounds element (documented in DESIGN.md "quirks kept").
-inline void build_mips(int w, int h, int C, const std::vector<double> &lvl0, DImage &im, std::vector<double> &pool) {
-    int size = w > h ? w : h;
-    int levels = std::min((int)ceil(log2((double)size) + 1), 8);
-    im.n_levels = levels; im.channels = C;
-    std::vector<double> prev = lvl0; int pw = w, ph = h;
-    for (int l = 0; l < levels; l++) {
-        if (l > 0) {
-            int nw = std::max(pw / 2, 1), nh = std::max(ph / 2, 1);
-            std::vector<double> next((size_t)nw * nh * C);
-            size_t plast = (size_t)pw * ph - 1;
-            auto at = [&](int x, int y, int c) { size_t i = (size_t)y * pw + x; if (i > plast) i = plast; return prev[i * C + c]; };
-            for (int y = 0; y < nh; y++) for (int x = 0; x < nw; x++) for (int c = 0; c < C; c++)
-                next[((size_t)y * nw + x) * C + c] = (at(2 * x, 2 * y, c) + at(2 * x + 1, 2 * y, c) + at(2 * x, 2 * y + 1, c) + at(2 * x + 1, 2 * y + 1, c)) * (1.0 / 4.0);
-            prev.swap(next); pw = nw; ph = nh;
-        }
-        im.w[l] = pw; im.h[l] = ph; im.off[l] = (long long)(pool.size() / C);
-        pool.insert(pool.end(), prev.begin(), prev.end());
-    }
-    for (int l = levels; l < 8; l++) { im.w[l] = im.h[l] = 1; im.off[l] = 0; }
-}
+// Level 0 of every image is expanded, mip-mapped (make_mipmap, mipmap.h:28-44) and copied to float on the device:
+// gdpt_textures.cu.
+int build_texture_pools(gdpt_ctx *c, const gdpt_scene_desc *d, std::vector<DImage> &im3, std::vector<DImage> &im1);
 
+// level 0 of one image on the host (only the environment map's sampling table needs it there)
 inline int decode_image(const gdpt_image &gi, int C, std::vector<double> &out) {
     if (gi.channels != C || gi.width <= 0 || gi.height <= 0) return fail(GDPT_ERR_ARG, "bad image (%d x %d x %d)", gi.width, gi.height, gi.channels);
     size_t n = (size_t)gi.width * gi.height * C;
@@ -225,43 +205,10 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         tf[i].uscale = (float)t[9]; tf[i].vscale = (float)t[10]; tf[i].uoffset = (float)t[11]; tf[i].voffset = (float)t[12];
     }
     if (int r = upload(c->tex_d, td)) return r; if (int r = upload(c->tex_f, tf)) return r;
-    std::vector<DImage> im3(d->n_images3), im1(d->n_images1);
-    std::vector<double> pool3, pool1;
-    {   // one task per image: decode + mip chain into a private pool, then splice the pools in image order
-        const int n3 = d->n_images3, n1 = d->n_images1, nimg = n3 + n1;
-        std::vector<std::vector<double>> local(nimg);
-        std::vector<int> rc(nimg, 0);
-        std::atomic<int> cursor{0};
-        auto task = [&] {
-            std::vector<double> t;
-            for (;;) {
-                int i = cursor.fetch_add(1);
-                if (i >= nimg) break;
-                const gdpt_image &gi = i < n3 ? d->images3[i] : d->images1[i - n3];
-                const int C = i < n3 ? 3 : 1;
-                rc[i] = decode_image(gi, C, t);
-                if (!rc[i]) build_mips(gi.width, gi.height, C, t, i < n3 ? im3[i] : im1[i - n3], local[i]);
-            }
-        };
-        unsigned nt = std::max(1u, std::min({8u, std::thread::hardware_concurrency(), (unsigned)std::max(nimg, 1)}));
-        std::vector<std::thread> pool;
-        for (unsigned t = 1; t < nt; t++) pool.emplace_back(task);
-        task();
-        for (auto &t : pool) t.join();
-        for (int i = 0; i < nimg; i++) if (rc[i]) return rc[i];
-        for (int i = 0; i < nimg; i++) {
-            std::vector<double> &dst = i < n3 ? pool3 : pool1;
-            DImage &im = i < n3 ? im3[i] : im1[i - n3];
-            const long long base = (long long)(dst.size() / (i < n3 ? 3 : 1));
-            for (int l = 0; l < im.n_levels; l++) im.off[l] += base;
-            dst.insert(dst.end(), local[i].begin(), local[i].end());
-        }
-    }
-    lap("decode + mips");
+    std::vector<DImage> im3, im1;
+    if (int r = build_texture_pools(c, d, im3, im1)) return r;
+    lap("textures (device)");
     if (int r = upload(c->img3, im3)) return r; if (int r = upload(c->img1, im1)) return r;
-    if (int r = upload(c->texels3_d, pool3)) return r; if (int r = upload(c->texels1_d, pool1)) return r;
-    { std::vector<float4> p4(pool3.size() / 3); for (size_t i = 0; i < p4.size(); i++) p4[i] = make_float4((float)pool3[3 * i], (float)pool3[3 * i + 1], (float)pool3[3 * i + 2], 0.f);
-      if (int r = upload(c->texels3_f, p4)) return r; if (int r = upload(c->texels1_f, to_f(pool1))) return r; }
     std::vector<double> li(3 * (size_t)std::max(d->n_lights, 1), 0.0);
     for (int i = 0; i < d->n_lights; i++) for (int k = 0; k < 3; k++) li[3 * i + k] = d->lights[5 * i + 2 + k];
     if (int r = upload(c->light_d, li)) return r; if (int r = upload(c->light_f, to_f(li))) return r;
@@ -297,7 +244,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
         shape_area = area;
     }
 
-    lap("texel upload");
+    lap("light tables");
     bvh_thread.join();
     lap("bvh build (rest)");
     if (3 * bvh.max_depth + 1 > STACK_TOTAL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
@@ -334,7 +281,9 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
                 if (tid >= d->n_textures || td[tid].kind != TEX_IMAGE || d->textures[14 * tid + 1] == 0) return fail(GDPT_ERR_UNSUPPORTED, "environment map %d is not an RGB image texture", i);
                 const DImage &im = im3[td[tid].image_id];
                 const int w = im.w[0], h = im.h[0];
-                const double *tex = pool3.data() + 3 * (size_t)im.off[0];
+                std::vector<double> env0;
+                if (int r = decode_image(d->images3[td[tid].image_id], 3, env0)) return r;
+                const double *tex = env0.data();
                 auto imod = [](int a, int b) { int r = a % b; return r < 0 ? r + b : r; };
                 std::vector<double> f((size_t)w * h);
                 for (int y = 0; y < h; y++) {
@@ -426,6 +375,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     c->sc_d.tri_cdf = c->tcdf_d.as<double>(); c->sc_f.tri_cdf = c->tcdf_f.as<float>();
     c->sc_d.shape_area = c->area_d.as<double>(); c->sc_f.shape_area = c->area_f.as<float>();
     c->sc_d.light_shape = c->sc_f.light_shape = c->lshape.as<int>();
+    GD_CUDA(cudaDeviceSynchronize());   // pageable uploads above went through the legacy stream; the context's stream does not wait on it
     return 0;
 }
 
