@@ -38,6 +38,8 @@ def parse():
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="target CPU time of one reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--offsets", default="reference", choices=["reference", "shift"],
+                    help="gradpath offset semantics: the reference's (the metric's config) or shift-mapped offsets (opt-in mode, DESIGN.md 12)")
     ap.add_argument("--solver", default="auto", choices=["auto", "gather", "distributed"],
                     help="N>1 Poisson solve: bands summed onto rank 0, or the all-to-all transposed solve (auto: distributed from 4K up)")
     return ap.parse_args()
@@ -195,7 +197,7 @@ def run_native(args):
         return {k: getattr(s, k) for k, _ in s._fields_}
 
     for _ in range(args.warmup):
-        R.render(spp, precision=args.precision)
+        R.render(spp, precision=args.precision, offsets=args.offsets)
     barrier()
     s0 = stats()
     sampler = ClockSampler(local)
@@ -204,7 +206,7 @@ def run_native(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        R.render(spp, precision=args.precision)
+        R.render(spp, precision=args.precision, offsets=args.offsets)
     e1.record()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
@@ -223,11 +225,11 @@ def run_native(args):
         sc2 = g.Scene(sc.a)
         y0, y1 = R.bands[rank]
         if world == 1:
-            r = g.gradient_path_render(sc2, device=local, spp=spp, precision=args.precision)
+            r = g.gradient_path_render(sc2, device=local, spp=spp, precision=args.precision, offsets=args.offsets)
             sc2.close()
             return r
         R2 = multi.DistributedRenderer(sc2, local, dist_, torch, solver=args.solver)
-        r = R2.render(spp, precision=args.precision, to_host=True)
+        r = R2.render(spp, precision=args.precision, to_host=True, offsets=args.offsets)
         sc2.close()
         return r
     scene_bytes = sum(v.nbytes for k, v in sc.a.items())
@@ -267,7 +269,7 @@ def run_native(args):
                 pass
         nb = ncu.get("bounce")
         issue_peak = 148 * 4 * (clocks["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)) * 1e6     # warp instructions / s
-        roof = {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+        roof = {"bound": "hbm", "kernel": "k_trace" if args.offsets == "reference" else "k_shift (ray casts + shading in one kernel; bytes = its rays x the traversal bytes per ray)", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                 "frac": achieved / peaks["hbm_gbs"] if achieved else None,
                 "traffic": nb["dram_bytes"] if nb else None, "peak_source": how,
                 "bytes_per_ray": bytes_per_ray, "nodes_per_ray": cnt[0], "prims_per_ray": cnt[1],
@@ -285,7 +287,7 @@ def run_native(args):
         line = {"metric": METRIC if (w, h) == (1920, 1080) else METRIC.replace("1920x1080", "%dx%d" % (w, h)), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": args.precision, "data": "synthetic",
-                "config": {"workload": "%s gradpath %dx%d %d spp, reference offset semantics, image split into %d row band(s)" % (args.scene, w, h, spp, world),
+                "config": {"workload": "%s gradpath %dx%d %d spp, %s, image split into %d row band(s)" % (args.scene, w, h, spp, "reference offset semantics" if args.offsets == "reference" else "shift-mapped offsets (opt-in mode)", world),
                            "precision": args.precision + " traversal/shading, f64 accumulation + Poisson",
                            "poisson_solver": R.solver if world > 1 else "single GPU",
                            "l2_flush": "inputs larger than L2: each step streams %.1f GB of path state" % (paths / 5 * 900 / 1e9)},

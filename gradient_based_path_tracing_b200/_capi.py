@@ -10,6 +10,8 @@ LIB_PATH = os.path.join(_HERE, "libgdpt.so")
 
 PRECISION_F64 = 0
 PRECISION_F32 = 1
+OFFSETS_REFERENCE = 0
+OFFSETS_SHIFT = 1
 DEFAULT_SEED = 0x31E241F862A1FB5E
 
 dp = C.POINTER(C.c_double)
@@ -39,7 +41,7 @@ class GdptSceneDesc(C.Structure):
 class GdptRenderParams(C.Structure):
     _fields_ = [("spp", C.c_int32), ("sample0", C.c_int32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32),
                 ("seed", C.c_uint64), ("data_cost", C.c_double), ("precision", C.c_int32),
-                ("y0", C.c_int32), ("y1", C.c_int32), ("wave_samples", C.c_int32)]
+                ("y0", C.c_int32), ("y1", C.c_int32), ("wave_samples", C.c_int32), ("offset_mode", C.c_int32)]
 
 
 class GdptImages(C.Structure):

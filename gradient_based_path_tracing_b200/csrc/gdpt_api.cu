@@ -9,6 +9,9 @@ namespace gdpt {
 template <typename R> int run_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp);
 extern template int run_wave<double>(gdpt_ctx *, DScene<double>, WaveParams);
 extern template int run_wave<float>(gdpt_ctx *, DScene<float>, WaveParams);
+template <typename R> int run_shift_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp);
+extern template int run_shift_wave<double>(gdpt_ctx *, DScene<double>, WaveParams);
+extern template int run_shift_wave<float>(gdpt_ctx *, DScene<float>, WaveParams);
 template <typename R> int run_path_wave(gdpt_ctx *c, DScene<R> sc, WaveParams wp);
 extern template int run_path_wave<double>(gdpt_ctx *, DScene<double>, WaveParams);
 extern template int run_path_wave<float>(gdpt_ctx *, DScene<float>, WaveParams);
@@ -42,7 +45,7 @@ using namespace gdpt;
 
 namespace {
 
-struct Resolved { int spp, sample0, y0, y1, precision, wave; unsigned long long seed; double alpha; int max_depth, rr_depth; };
+struct Resolved { int spp, sample0, y0, y1, precision, wave; unsigned long long seed; double alpha; int max_depth, rr_depth, offset_mode; };
 
 int resolve(gdpt_ctx *c, const gdpt_render_params *p, Resolved &r) {
     if (!c || !p) return fail(GDPT_ERR_ARG, "null argument");
@@ -57,6 +60,8 @@ int resolve(gdpt_ctx *c, const gdpt_render_params *p, Resolved &r) {
     r.max_depth = p->max_depth == -2 ? c->max_depth : p->max_depth;
     r.rr_depth = p->rr_depth == -2 ? c->rr_depth : p->rr_depth;
     r.wave = p->wave_samples;
+    r.offset_mode = p->offset_mode;
+    if (r.offset_mode != GDPT_OFFSETS_REFERENCE && r.offset_mode != GDPT_OFFSETS_SHIFT) return fail(GDPT_ERR_ARG, "unknown offset mode %d", r.offset_mode);
     return 0;
 }
 
@@ -84,7 +89,7 @@ int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, dou
         long long n = wp.npix_pad * kk;
         if (n > 0x7fffffffLL / 8) return fail(GDPT_ERR_ARG, "wave too large");
         wp.n_paths = (int)n;
-        if (int rc = PATH ? run_path_wave<R>(c, sc, wp) : run_wave<R>(c, sc, wp)) return rc;
+        if (int rc = PATH ? run_path_wave<R>(c, sc, wp) : r.offset_mode == GDPT_OFFSETS_SHIFT ? run_shift_wave<R>(c, sc, wp) : run_wave<R>(c, sc, wp)) return rc;
     }
     return 0;
 }
@@ -406,8 +411,9 @@ int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, co
     wp.xs = ctx->xs.as<int>(); wp.ys = ctx->ys.as<int>(); wp.streams = ctx->streams.as<unsigned long long>();
     wp.rec_out = ctx->recout.as<double>();
     int rc;
-    if (r.precision == GDPT_PRECISION_F64) { DScene<double> sc = ctx->sc_d; sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth; rc = run_wave<double>(ctx, sc, wp); }
-    else { DScene<float> sc = ctx->sc_f; sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth; rc = run_wave<float>(ctx, sc, wp); }
+    const bool shift = r.offset_mode == GDPT_OFFSETS_SHIFT;
+    if (r.precision == GDPT_PRECISION_F64) { DScene<double> sc = ctx->sc_d; sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth; rc = shift ? run_shift_wave<double>(ctx, sc, wp) : run_wave<double>(ctx, sc, wp); }
+    else { DScene<float> sc = ctx->sc_f; sc.max_depth = r.max_depth; sc.rr_depth = r.rr_depth; rc = shift ? run_shift_wave<float>(ctx, sc, wp) : run_wave<float>(ctx, sc, wp); }
     if (rc) return rc;
     GD_CUDA(cudaStreamSynchronize(ctx->stream));
     GD_CUDA(cudaMemcpy(rec, ctx->recout.p, (size_t)n * 23 * 8, cudaMemcpyDeviceToHost));

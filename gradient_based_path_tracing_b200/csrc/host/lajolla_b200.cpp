@@ -57,10 +57,10 @@ static void describe_scene(const FlatScene &s) {
 
 int main(int argc, char *argv[]) {
     if (argc <= 1) {
-        std::cout << "[Usage] ./lajolla_b200 [-o output_file_name] [-overlay camera.gdpt] [-spp n] [-precision f32|f64] [-device d] [-seed s] filename.gdpt[.z]" << std::endl;
+        std::cout << "[Usage] ./lajolla_b200 [-o output_file_name] [-overlay camera.gdpt] [-spp n] [-precision f32|f64] [-offsets reference|shift] [-device d] [-seed s] filename.gdpt[.z]" << std::endl;
         return 0;
     }
-    std::string outputfile, overlay, precision = "f32";
+    std::string outputfile, overlay, precision = "f32", offsets = "reference";
     int spp = 0, device = 0; unsigned long long seed = 0;
     bool describe = false;
     int integrator_override = -1;   // Integrator enum value (src/scene.h:14-23): 5 Path, 7 GradPath
@@ -73,6 +73,7 @@ int main(int argc, char *argv[]) {
         else if (a == "-overlay") overlay = value();
         else if (a == "-spp") spp = std::stoi(value());
         else if (a == "-precision") precision = value();
+        else if (a == "-offsets") offsets = value();              // gradpath only: the shipped offset semantics, or shift-mapped offsets (gdpt.h)
         else if (a == "-device") device = std::stoi(value());
         else if (a == "-seed") seed = std::stoull(value());
         else if (a == "-integrator") { std::string v = value(); const char *names[] = {"depth", "shadingNormal", "meanCurvature", "rayDifferential", "mipmapLevel", "path", "volpath", "gradpath"};   // parse_scene.cpp:520-566
@@ -82,6 +83,7 @@ int main(int argc, char *argv[]) {
         else filenames.push_back(a);
     }
     if (precision != "f32" && precision != "f64") { std::cerr << "-precision must be f32 or f64" << std::endl; return 2; }
+    if (offsets != "reference" && offsets != "shift") { std::cerr << "-offsets must be reference or shift" << std::endl; return 2; }
     if (!describe && gdpt_device_count() < 1) { std::cerr << "no CUDA device: lajolla_b200 has no CPU fallback" << std::endl; return 1; }
 
     for (const std::string &filename : filenames) {
@@ -111,6 +113,7 @@ int main(int argc, char *argv[]) {
         p.spp = spp > 0 ? spp : scene.desc.samples_per_pixel;
         p.max_depth = -2; p.rr_depth = -2; p.seed = seed; p.data_cost = 0.04;
         p.precision = precision == "f64" ? GDPT_PRECISION_F64 : GDPT_PRECISION_F32;
+        p.offset_mode = offsets == "shift" ? GDPT_OFFSETS_SHIFT : GDPT_OFFSETS_REFERENCE;
         gdpt_images img{primal.data(), dx.data(), dy.data(), out.data()};
         const bool path = scene.integrator == 5;          // Integrator::Path -> path_render (render.cpp:385-386): one image
         int rc = aux ? gdpt_render_aux(ctx, scene.integrator, p.precision, out.data()) : path ? gdpt_render_path(ctx, &p, out.data()) : gdpt_render(ctx, &p, &img);

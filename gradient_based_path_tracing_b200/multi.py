@@ -215,7 +215,7 @@ class DistributedRenderer:
         img.zero_()
         torch.cuda.current_stream().synchronize()
         if y1 > y0:
-            p = _params(self.scene, spp=spp, precision=precision, seed=seed, rows=(y0, y1))
+            p = _params(self.scene, spp=spp, precision=precision, seed=seed, rows=(y0, y1), offsets=offsets)
             if y0 == 0:
                 p.y0 = 0
             check(lib.gdpt_render_path_accumulate_device(self.ctx, C.byref(p), C.c_void_p(img.data_ptr())))
@@ -227,7 +227,7 @@ class DistributedRenderer:
             return img.cpu().numpy().reshape(self.scene.height, self.scene.width, 3)
         return None
 
-    def render(self, spp, precision="f32", seed=0, data_cost=0.04, to_host=False):
+    def render(self, spp, precision="f32", seed=0, data_cost=0.04, to_host=False, offsets="reference"):
         from .render import _params
         lib, check = self._capi.lib(), self._capi.check
         torch = self.torch

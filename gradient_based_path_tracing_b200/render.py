@@ -23,7 +23,7 @@ class RenderResult(dict):
 
 
 def _params(scene, spp=None, precision="f64", seed=0, sample0=0, max_depth=None, rr_depth=None, data_cost=0.04,
-            rows=None, wave_samples=0):
+            rows=None, wave_samples=0, offsets="reference"):
     p = _capi.GdptRenderParams()
     p.spp = int(spp if spp is not None else scene.options.samples_per_pixel)
     p.sample0 = int(sample0)
@@ -34,6 +34,7 @@ def _params(scene, spp=None, precision="f64", seed=0, sample0=0, max_depth=None,
     p.precision = {"f64": _capi.PRECISION_F64, "f32": _capi.PRECISION_F32}[precision]
     p.y0, p.y1 = (0, 0) if rows is None else (int(rows[0]), int(rows[1]))
     p.wave_samples = int(wave_samples)
+    p.offset_mode = {"reference": _capi.OFFSETS_REFERENCE, "shift": _capi.OFFSETS_SHIFT}[offsets]
     return p
 
 

@@ -30,6 +30,11 @@ extern "C" {
 #define GDPT_PRECISION_F64 0 /* arithmetic in double like the reference (Real = double, lajolla.h:23) */
 #define GDPT_PRECISION_F32 1 /* float shading/traversal, double accumulation and Poisson */
 
+#define GDPT_OFFSETS_REFERENCE 0 /* grad_path_tracing as shipped (path_tracing.h:354-1050): the drop-in default */
+#define GDPT_OFFSETS_SHIFT 1     /* shift-mapped offsets, the algorithm of small_gdpt.cpp:153-352 on lajolla scenes: random-number
+                                  * replay, reconnection at the first diffuse-diffuse vertex pair, MIS-weighted gradients, y offsets
+                                  * paired consistently (opt-in; gradpath integrator only) */
+
 typedef struct gdpt_ctx gdpt_ctx;
 
 /* One image of a TexturePool mip chain, level 0 only (src/texture.h:13-19, src/mipmap.h:28-44;
@@ -87,6 +92,7 @@ typedef struct {
     int32_t precision;        /* GDPT_PRECISION_* */
     int32_t y0, y1;           /* row band [y0,y1) to render; y1 <= 0: whole image */
     int32_t wave_samples;     /* samples per pixel per wave; 0: auto */
+    int32_t offset_mode;      /* GDPT_OFFSETS_*; 0 = the reference's semantics */
 } gdpt_render_params;
 
 /* Host output images; any pointer may be NULL.  primal/dx/dy/poisson = c/cx/cy/out of render.cpp:336-353. */
