@@ -215,7 +215,7 @@ class DistributedRenderer:
         img.zero_()
         torch.cuda.current_stream().synchronize()
         if y1 > y0:
-            p = _params(self.scene, spp=spp, precision=precision, seed=seed, rows=(y0, y1), offsets=offsets)
+            p = _params(self.scene, spp=spp, precision=precision, seed=seed, rows=(y0, y1))
             if y0 == 0:
                 p.y0 = 0
             check(lib.gdpt_render_path_accumulate_device(self.ctx, C.byref(p), C.c_void_p(img.data_ptr())))
@@ -236,7 +236,7 @@ class DistributedRenderer:
             b.zero_()
         torch.cuda.current_stream().synchronize()
         if y1 > y0:
-            p = _params(self.scene, spp=spp, precision=precision, seed=seed, rows=(y0, y1))
+            p = _params(self.scene, spp=spp, precision=precision, seed=seed, rows=(y0, y1), offsets=offsets)
             if y0 == 0:
                 p.y0 = 0
             ptrs = [C.c_void_p(b.data_ptr()) for b in self.acc]

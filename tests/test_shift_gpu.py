@@ -123,3 +123,25 @@ def test_unknown_offset_mode_is_rejected(g):
     imgs = _capi.GdptImages()
     assert _capi.lib().gdpt_render(sc.context(0), C.byref(p), C.byref(imgs)) != 0
     assert b"offset mode" in _capi.lib().gdpt_last_error()
+
+
+def test_band_renderer_carries_the_offset_mode(g):
+    """multi.DistributedRenderer (the bench's and the multi-GPU path's front end) with one rank equals gdpt_render."""
+    import torch
+    from gradient_based_path_tracing_b200 import multi
+
+    class Solo:
+        ReduceOp = type("R", (), {"SUM": 0})
+        def get_rank(self): return 0
+        def get_world_size(self): return 1
+        def reduce(self, *a, **k): pass
+        def barrier(self): pass
+
+    sc = g.Scene.named("cbox_gdpt_64")
+    want = g.gradient_path_render(sc, spp=4, precision="f64", offsets="shift")
+    R = multi.DistributedRenderer(sc, 0, Solo(), torch)
+    got = R.render(4, precision="f64", to_host=True, offsets="shift")
+    for k in ("primal", "dx", "dy", "poisson"):
+        assert np.allclose(got[k], getattr(want, k), rtol=1e-9, atol=1e-13), k
+    ref = R.render(4, precision="f64", to_host=True)
+    assert not np.allclose(ref["dx"], got["dx"])

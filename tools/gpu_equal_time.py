@@ -5,7 +5,9 @@ the shipped Cornell box (scenes/cbox/cbox_gdpt.xml, 512x512).  relMSE = mean((I 
 Every estimator is compared with ITS OWN converged image, rendered here on the GPU in f64-accumulated f32 mode at REF_SPP:
 the two reference integrators do not converge to the same picture (as shipped, `path` adds BSDF-sampled light hits
 without the MIS weight w2, path_tracing.h:228-232, and gradpath has no next-event estimation), so a common target would
-measure their bias, not their noise.  Usage: python tools/gpu_equal_time.py [scene] [ref_spp]"""
+measure their bias, not their noise.  Usage: python tools/gpu_equal_time.py [scene] [ref_spp] [shift]
+With a third argument only the shift-mapped gradpath (offsets="shift") is measured: primal and Poisson image
+against the converged primal of that mode (its Poisson image converges to the same picture)."""
 import os
 import sys
 import time
@@ -26,6 +28,18 @@ def relmse(i, r):
 
 sc = g.Scene.named(name)
 w, h = sc.width, sc.height
+if len(sys.argv) > 3:
+    g.gradient_path_render(sc, spp=1, precision="f32", offsets="shift")
+    t = time.perf_counter(); Rs = g.gradient_path_render(sc, spp=REF_SPP, precision="f32", seed=99, offsets="shift"); ts = time.perf_counter() - t
+    rate_s = REF_SPP / ts
+    print("%s %dx%d shift-mapped gradpath: reference at %d spp in %.1f s (%.1f Msamples/s); converged Poisson vs primal relMSE %.2e"
+          % (name, w, h, REF_SPP, ts, w * h * rate_s / 1e6, relmse(Rs.poisson, Rs.primal)), flush=True)
+    for T in BUDGETS:
+        n = max(1, int(rate_s * T))
+        t = time.perf_counter(); a = g.gradient_path_render(sc, spp=n, precision="f32", seed=7, offsets="shift"); ta = time.perf_counter() - t
+        print("%7.2fs | %5d spp %.2fs | primal %.2e | Poisson %.2e | ratio %.2f" % (T, n, ta, relmse(a.primal, Rs.primal), relmse(a.poisson, Rs.primal),
+              relmse(a.primal, Rs.primal) / relmse(a.poisson, Rs.primal)), flush=True)
+    sys.exit(0)
 g.gradient_path_render(sc, spp=1, precision="f32")
 g.path_render(sc, spp=1, precision="f32")
 t = time.perf_counter(); Rg = g.gradient_path_render(sc, spp=REF_SPP, precision="f32", seed=99); tg = time.perf_counter() - t
