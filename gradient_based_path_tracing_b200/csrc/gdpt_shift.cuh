@@ -20,8 +20,10 @@
 // probability), the two MIS weights of a pixel pair would no longer sum to one and the gradients would be biased.  A
 // constant multiplies base and offset alike: it cancels in w and scales both contributions.
 //
-// One thread walks one pixel-sample: base path and four offsets, ray casts inline (trace_closest / trace_occluded) —
-// the offsets need the base path's vertices and random numbers, which would otherwise travel through HBM per bounce.
+// One thread walks one pixel-sample: base path and four offsets, ray casts inline — the offsets need the base path's
+// vertices and random numbers, which would otherwise travel through HBM per bounce.  Two forms of the same arithmetic:
+// k_shift (program order, kept as the readable statement and the A/B baseline) and k_shift_sm (per-lane state machine
+// with one ray-cast site and persistent lanes, the default).
 #pragma once
 #include "gdpt_wave.cuh"
 
@@ -215,6 +217,218 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_shift(DScene<R> sc, WaveParams 
     if ((threadIdx.x & 31) == 0 && n_rays) atomicAdd(ray_counter, (unsigned long long)n_rays);
 }
 
+// ---------------------------------------------------------------- the same algorithm as a per-lane state machine
+// k_shift above walks base path and offsets in program order: lanes of a warp leave the base loop at different bounces
+// and then sit in four different ray-cast call sites, and a warp lasts as long as its longest path — ncu shows 6.2 of
+// 32 lanes active per instruction.  Here every lane carries a phase (fetch / base / offset / reconnect), ALL ray casts go
+// through one call site per trip of the loop, and a lane that finishes its pixel-sample fetches the next one, so the
+// traversal — most of the time — runs with whatever lanes have a ray, whichever stage they are in.  Same arithmetic in
+// the same order: records are bit-identical to k_shift's (tests/test_shift_gpu.py).
+enum { SH_FETCH = 0, SH_BASE = 1, SH_OFFSET = 2, SH_RECONNECT = 3 };
+
+template <bool EXACT>
+GD_D Hit shift_trace(const DBvh &bvh, const float o[3], const float d[3], float tnear, float tfar, bool any, int2 *smem_stack) {
+    RayState r; r.init(make_float4(o[0], o[1], o[2], tnear), make_float4(d[0], d[1], d[2], tfar));
+    if (bvh.n_nodes == 0) return r.hit;
+    TraceStack st; st.smem = smem_stack;
+    int sp = 0, cur = 0;
+    while (cur != TRACE_DONE) {
+        while (cur >= 0) cur = trace_node<0, 0>(bvh, cur, r, st, sp);
+        if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, nullptr);
+        if (any && r.hit.shape_id >= 0) break;
+    }
+    return r.hit;
+}
+
+template <typename R, int MS, bool EXACT, int MINB>
+__global__ void __launch_bounds__(TRACE_BLOCK, MINB) k_shift_sm(DScene<R> sc, WaveParams wp, DBvh bvh, unsigned long long *ray_counter, int *next_sample) {
+    __shared__ int2 stack[STACK_SMEM * TRACE_BLOCK];
+    const float inf = __int_as_float(0x7f800000);
+    const R spread0 = R(0.25) / R(sc.width > sc.height ? sc.width : sc.height);
+    const int ox[4] = {-1, 0, 1, 0}, oy[4] = {0, -1, 0, 1};
+    unsigned n_rays = 0;
+    int phase = SH_FETCH;
+    // the sample
+    int i = 0, px = 0, py = 0; R rx = R(0), ry = R(0); Pcg rng;
+    // the ray in flight
+    V3<R> ro(0, 0, 0), rd(0, 0, 1); float rtnear = 0.f, rtfar = inf; bool rany = false;
+    // base path
+    R pu0[SHIFT_MAX_PREFIX], pu1[SHIFT_MAX_PREFIX], pw[SHIFT_MAX_PREFIX], pp[SHIFT_MAX_PREFIX];
+    unsigned char pclass[SHIFT_MAX_PREFIX + 1];
+    int j = 0, L = -1, dr = -1, jend = 0;
+    bool prev_diffuse = false, offsets_ok = true;
+    double C[3], P = 1, inv_rr = 1, Sf[3], Sp = 1, contrib[3], cS[4][3], wS[4];
+    V3<R> Le(0, 0, 0), wr(0, 0, 1), pos_dr(0, 0, 0), rad(0, 0, 0);
+    Vertex<R> vr;
+    // offset in flight
+    int k = 0, oj = 0;
+    double Cs[3], Ps = 1, J = 1;
+
+    for (;;) {
+        if (phase == SH_FETCH) {
+            i = atomicAdd(next_sample, 1);
+            if (i >= wp.n_paths) break;
+            unsigned long long stream;
+            if (wp.xs) { px = wp.xs[i]; py = wp.ys[i]; stream = wp.streams[i]; }
+            else {
+                long long s = i / wp.npix_pad, p = i % wp.npix_pad;
+                int tile = (int)(p >> 5), lane = (int)(p & 31);
+                px = (tile % wp.tiles_x) * 8 + (lane & 7); py = wp.y0 + (tile / wp.tiles_x) * 4 + (lane >> 3);
+                if (px >= wp.width || py >= wp.y1) continue;
+                stream = (unsigned long long)(wp.sample0 + s) * (unsigned long long)wp.width * wp.height + (unsigned long long)py * wp.width + px;
+            }
+            for (int q = 0; q < 4; q++) { cS[q][0] = cS[q][1] = cS[q][2] = 0.0; wS[q] = 1.0; }
+            for (int c = 0; c < 3; c++) { C[c] = 1; Sf[c] = 1; contrib[c] = 0; }
+            P = 1; inv_rr = 1; Sp = 1; L = -1; dr = -1; j = 0; prev_diffuse = false; offsets_ok = true;
+            rad = V3<R>(0, 0, 0); Le = V3<R>(0, 0, 0);
+            rng = pcg_init(stream, wp.seed);
+            rx = pcg_real<R>(rng); ry = pcg_real<R>(rng);
+            sample_primary<R>(sc, (R(px) + rx) / R(sc.width), (R(py) + ry) / R(sc.height), ro, rd);
+            pos_dr = ro;
+            rtnear = 0.f; rtfar = inf; rany = false; phase = SH_BASE;
+        }
+        // ---- the one ray-cast site
+        Hit h;
+        {
+            const float of[3] = {(float)ro.x, (float)ro.y, (float)ro.z}, df[3] = {(float)rd.x, (float)rd.y, (float)rd.z};
+            n_rays++;
+            h = shift_trace<EXACT>(bvh, of, df, rtnear, rtfar, rany, stack);
+        }
+        bool next_offset = false;
+        if (phase == SH_BASE) {
+            bool over = true, base_ok = false;
+            if (h.shape_id >= 0) {
+                Vertex<R> v;
+                make_vertex_ms<R, MS>(sc, ro, rd, rtnear, inf, h, R(0), j == 0 ? spread0 : R(0), v);
+                const int cls = shift_class(sc, v);
+                if (dr < 0 && j > 0 && prev_diffuse && (cls & 1)) { dr = j - 1; vr = v; pos_dr = ro; }
+                if (dr < 0 || j <= dr) { if (j <= SHIFT_MAX_PREFIX) pclass[j] = (unsigned char)cls; else offsets_ok = false; }
+                if (cls & 2) { Le = emission<R>(sc, v, -rd); L = j; base_ok = true; }
+                else if (j + 1 < SHIFT_MAX_VERTS && !(sc.max_depth != -1 && j + 2 > sc.max_depth)) {
+                    const R u0 = pcg_real<R>(rng), u1 = pcg_real<R>(rng), w = pcg_real<R>(rng);
+                    BsdfSample<R> s;
+                    if (bsdf_sample_ms<R, MS>(sc, v, -rd, u0, u1, w, s)) {
+                        const V3<R> f = bsdf_eval_ms<R, MS>(sc, v, -rd, s.dir_out);
+                        const R p = bsdf_pdf_ms<R, MS>(sc, v, -rd, s.dir_out);
+                        if (p > R(0) && (f.x > R(0) || f.y > R(0) || f.z > R(0))) {
+                            if (dr < 0) { if (j < SHIFT_MAX_PREFIX) { pu0[j] = u0; pu1[j] = u1; pw[j] = w; pp[j] = p; } else offsets_ok = false; }
+                            else if (j == dr + 1) wr = s.dir_out;
+                            else { Sf[0] *= (double)f.x; Sf[1] *= (double)f.y; Sf[2] *= (double)f.z; Sp *= (double)p; }
+                            C[0] *= (double)f.x; C[1] *= (double)f.y; C[2] *= (double)f.z; P *= (double)p;
+                            bool alive = true;
+                            if (j + 2 >= sc.rr_depth) {
+                                if (!(pcg_real<R>(rng) <= R(SHIFT_RR_SURVIVAL))) alive = false;
+                                else inv_rr /= SHIFT_RR_SURVIVAL;
+                            }
+                            if (alive) {
+                                prev_diffuse = (cls & 1) != 0;
+                                ro = v.position; rd = s.dir_out; rtnear = (float)sc.eps; j++;
+                                over = false;
+                            }
+                        }
+                    }
+                }
+            }
+            if (!over) continue;
+            if (!base_ok) {
+                if (wp.rec_out) finish_path<R>(wp, px, py, i, rad, contrib, 1.0, cS, wS);
+                phase = SH_FETCH; continue;
+            }
+            for (int c = 0; c < 3; c++) contrib[c] = C[c] * (double)(c == 0 ? Le.x : c == 1 ? Le.y : Le.z) * inv_rr;
+            rad = V3<R>((R)(contrib[0] / P), (R)(contrib[1] / P), (R)(contrib[2] / P));
+            jend = dr >= 0 ? dr : L;
+            k = -1; next_offset = true;
+        } else if (phase == SH_OFFSET) {
+            bool ok = h.shape_id >= 0, done = false;
+            if (ok) {
+                Vertex<R> vo;
+                make_vertex_ms<R, MS>(sc, ro, rd, rtnear, inf, h, R(0), oj == 0 ? spread0 : R(0), vo);
+                if (shift_class(sc, vo) != (int)pclass[oj]) ok = false;
+                else if (oj < jend) {                             // replay the base's random numbers at this vertex
+                    BsdfSample<R> s;
+                    if (!bsdf_sample_ms<R, MS>(sc, vo, -rd, pu0[oj], pu1[oj], pw[oj], s)) ok = false;
+                    else {
+                        const V3<R> f = bsdf_eval_ms<R, MS>(sc, vo, -rd, s.dir_out);
+                        const R p = bsdf_pdf_ms<R, MS>(sc, vo, -rd, s.dir_out);
+                        if (!(p > R(0))) ok = false;
+                        else {
+                            Cs[0] *= (double)f.x; Cs[1] *= (double)f.y; Cs[2] *= (double)f.z; Ps *= (double)p; J *= (double)pp[oj] / (double)p;
+                            ro = vo.position; rd = s.dir_out; rtnear = (float)sc.eps; oj++;
+                            continue;
+                        }
+                    }
+                } else if (dr < 0) {                              // replayed all the way: the offset's own light vertex
+                    const V3<R> e = emission<R>(sc, vo, -rd);
+                    Cs[0] *= (double)e.x; Cs[1] *= (double)e.y; Cs[2] *= (double)e.z;
+                    done = true;
+                } else {                                          // reconnect vo -> b_{dr+1}: everything but the visibility ray
+                    const V3<R> dv = vr.position - vo.position;
+                    const R d2s = dot(dv, dv);
+                    ok = d2s > R(0);
+                    if (ok) {
+                        const R dist = sqrt(d2s);
+                        const V3<R> ds = dv / dist;
+                        const V3<R> f = bsdf_eval_ms<R, MS>(sc, vo, -rd, ds);
+                        const R p = bsdf_pdf_ms<R, MS>(sc, vo, -rd, ds);
+                        const V3<R> bv = vr.position - pos_dr;
+                        const R d2b = dot(bv, bv);
+                        const R cos_s = fabs(dot(ds, vr.gn)), cos_b = fabs(dot(bv, vr.gn)) / sqrt(d2b);
+                        ok = p > R(0) && cos_b > R(0) && d2b > R(0);
+                        if (ok) {
+                            J *= ((double)cos_s / (double)d2s) / ((double)cos_b / (double)d2b);
+                            Cs[0] *= (double)f.x; Cs[1] *= (double)f.y; Cs[2] *= (double)f.z; Ps *= (double)p;
+                            if (L == dr + 1) {
+                                const V3<R> e = emission<R>(sc, vr, -ds);
+                                Cs[0] *= (double)e.x; Cs[1] *= (double)e.y; Cs[2] *= (double)e.z;
+                            } else {
+                                const V3<R> ft = bsdf_eval_ms<R, MS>(sc, vr, -ds, wr);
+                                const R pt = bsdf_pdf_ms<R, MS>(sc, vr, -ds, wr);
+                                ok = pt > R(0);
+                                Cs[0] *= (double)ft.x * Sf[0] * (double)Le.x; Cs[1] *= (double)ft.y * Sf[1] * (double)Le.y; Cs[2] *= (double)ft.z * Sf[2] * (double)Le.z;
+                                Ps *= (double)pt * Sp;
+                            }
+                        }
+                        if (ok) {
+                            ro = vo.position; rd = ds; rtnear = (float)sc.eps; rtfar = (float)((R(1) - sc.eps) * dist); rany = true;
+                            phase = SH_RECONNECT;
+                            continue;
+                        }
+                    }
+                }
+            }
+            if (ok && done && J > 0.0 && isfinite(J) && isfinite(Ps)) {
+                for (int c = 0; c < 3; c++) cS[k][c] = Cs[c] * J * inv_rr;
+                wS[k] = P / (P + Ps * J);
+            }
+            next_offset = true;
+        } else {                                                  // SH_RECONNECT: the visibility ray is back
+            if (h.shape_id < 0 && J > 0.0 && isfinite(J) && isfinite(Ps)) {
+                for (int c = 0; c < 3; c++) cS[k][c] = Cs[c] * J * inv_rr;
+                wS[k] = P / (P + Ps * J);
+            }
+            next_offset = true;
+        }
+        if (next_offset) {
+            for (k++; k < 4; k++) {
+                if (!offsets_ok) { k = 4; break; }
+                if (!wp.rec_out && (px + ox[k] < 0 || px + ox[k] >= wp.width || py + oy[k] < 0 || py + oy[k] >= wp.height)) continue;
+                break;
+            }
+            if (k < 4) {
+                sample_primary<R>(sc, (R(px + ox[k]) + rx) / R(sc.width), (R(py + oy[k]) + ry) / R(sc.height), ro, rd);
+                rtnear = 0.f; rtfar = inf; rany = false; oj = 0;
+                Cs[0] = Cs[1] = Cs[2] = 1; Ps = 1; J = 1;
+                phase = SH_OFFSET;
+            } else {
+                finish_shift<R>(wp, px, py, i, rad, contrib, P, cS, wS);
+                phase = SH_FETCH;
+            }
+        }
+    }
+    for (int s = 16; s > 0; s >>= 1) n_rays += __shfl_xor_sync(0xffffffffu, n_rays, s);
+    if ((threadIdx.x & 31) == 0 && n_rays) atomicAdd(ray_counter, (unsigned long long)n_rays);
+}
+
 template <typename R, int MS>
 int run_shift_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     const int N = wp.n_paths;
@@ -223,9 +437,14 @@ int run_shift_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     unsigned long long *cnt = reinterpret_cast<unsigned long long *>(c->counters.as<char>() + 32);
     cudaStream_t st = c->stream;
     cudaEvent_t e0 = c->ev[4], e1 = c->ev[5];
-    GD_CUDA(cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), st));
+    GD_CUDA(cudaMemsetAsync(cnt, 0, 2 * sizeof(unsigned long long), st));      // rays traced; next sample (k_shift_sm)
     GD_CUDA(cudaEventRecord(e0, st));
-    k_shift<R, MS, ModeSel<R>::exact><<<blocks_for(N, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(sc, wp, c->bvh, cnt);
+    // default: the state machine at 8 blocks per SM (64 registers; B200, Sponza 1080p, 8 spp: 87 ms — 5 blocks 100 ms, 3 blocks
+    // 117 ms; k_shift 116 ms, 103 ms at 8 blocks per SM).  GDPT_SHIFT_KERNEL=0 runs k_shift (A/B, bit-identity test).
+    const bool straight = getenv("GDPT_SHIFT_KERNEL") && atoi(getenv("GDPT_SHIFT_KERNEL")) == 0;
+    const int nb = blocks_for(N, TRACE_BLOCK);
+    if (straight) k_shift<R, MS, ModeSel<R>::exact><<<nb, TRACE_BLOCK, 0, st>>>(sc, wp, c->bvh, cnt);
+    else k_shift_sm<R, MS, ModeSel<R>::exact, 8><<<std::min(nb, SM_COUNT * 8), TRACE_BLOCK, 0, st>>>(sc, wp, c->bvh, cnt, reinterpret_cast<int *>(cnt + 1));
     GD_CUDA(cudaEventRecord(e1, st));
     unsigned long long h = 0;
     GD_CUDA(cudaMemcpyAsync(&h, cnt, sizeof(h), cudaMemcpyDeviceToHost, st));

@@ -145,3 +145,26 @@ def test_band_renderer_carries_the_offset_mode(g):
         assert np.allclose(got[k], getattr(want, k), rtol=1e-9, atol=1e-13), k
     ref = R.render(4, precision="f64", to_host=True)
     assert not np.allclose(ref["dx"], got["dx"])
+
+
+def test_state_machine_kernel_equals_the_straight_one(g, monkeypatch):
+    """k_shift_sm (per-lane phases, one ray-cast site, lanes fetch their next sample) against k_shift (program order):
+    same arithmetic in the same order, so FP64 records are bit-identical; images agree up to the order of the atomics."""
+    out, img = {}, {}
+    rng = np.random.default_rng(5)
+    for name in ("veach_mi_small", "sponza_small"):
+        sc0 = g.Scene.named(name)
+        n = 3000
+        xs, ys = rng.integers(0, sc0.width, n), rng.integers(0, sc0.height, n)
+        st = np.arange(n, dtype=np.uint64) + 11
+        for tag in ("0", "1"):
+            monkeypatch.setenv("GDPT_SHIFT_KERNEL", tag)
+            out[tag] = g.grad_samples(sc0, xs, ys, st, precision="f64", offsets="shift")
+        assert np.array_equal(out["0"], out["1"]), name
+        assert name != "veach_mi_small" or (out["1"][:, 3:6] > 0).any()
+    sc = g.Scene.named("cbox_gdpt_64")
+    for tag in ("0", "1"):
+        monkeypatch.setenv("GDPT_SHIFT_KERNEL", tag)
+        img[tag] = g.gradient_path_render(sc, spp=8, precision="f64", offsets="shift")
+    for k in ("primal", "dx", "dy", "poisson"):
+        assert np.allclose(getattr(img["0"], k), getattr(img["1"], k), rtol=1e-9, atol=1e-13), k
