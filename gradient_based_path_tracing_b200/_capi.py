@@ -12,6 +12,7 @@ PRECISION_F64 = 0
 PRECISION_F32 = 1
 OFFSETS_REFERENCE = 0
 OFFSETS_SHIFT = 1
+CREATE_NO_BVH = 1
 DEFAULT_SEED = 0x31E241F862A1FB5E
 
 dp = C.POINTER(C.c_double)
@@ -60,7 +61,7 @@ class GdptDistGeom(C.Structure):
 
 
 # every symbol include/gdpt.h declares
-EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_destroy", "gdpt_scene_bounds", "gdpt_render",
+EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_create_ex", "gdpt_bvh_info", "gdpt_bvh_adopt", "gdpt_destroy", "gdpt_scene_bounds", "gdpt_render",
            "gdpt_render_accumulate_device", "gdpt_merge_device", "gdpt_poisson", "gdpt_poisson_device", "gdpt_get_stats",
            "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill",
            "gdpt_render_path", "gdpt_render_path_accumulate_device", "gdpt_path_samples", "gdpt_sample_light", "gdpt_occluded", "gdpt_render_aux",
@@ -78,6 +79,9 @@ def lib():
         vp = C.c_void_p
         L.gdpt_last_error.restype = C.c_char_p
         L.gdpt_create.argtypes = [C.POINTER(GdptSceneDesc), C.c_int, C.POINTER(vp)]
+        L.gdpt_create_ex.argtypes = [C.POINTER(GdptSceneDesc), C.c_int, C.c_int, C.POINTER(vp)]
+        L.gdpt_bvh_info.argtypes = [vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(vp), C.POINTER(vp)]
+        L.gdpt_bvh_adopt.argtypes = [vp, vp, C.c_int64, vp, C.c_int64, C.c_int32]
         L.gdpt_destroy.argtypes = [vp]
         L.gdpt_destroy.restype = None
         L.gdpt_scene_bounds.argtypes = [vp, dp]

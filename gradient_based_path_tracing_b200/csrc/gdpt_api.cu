@@ -49,6 +49,7 @@ struct Resolved { int spp, sample0, y0, y1, precision, wave; unsigned long long 
 
 int resolve(gdpt_ctx *c, const gdpt_render_params *p, Resolved &r) {
     if (!c || !p) return fail(GDPT_ERR_ARG, "null argument");
+    if (c->bvh_pending) return fail(GDPT_ERR_ARG, "the context was created with GDPT_CREATE_NO_BVH and has not been given a BVH (gdpt_bvh_adopt)");
     r.spp = p->spp > 0 ? p->spp : c->spp;
     r.sample0 = p->sample0;
     r.y0 = p->y0 > 0 ? p->y0 : 0; r.y1 = p->y1 > 0 ? std::min(p->y1, c->height) : c->height;
@@ -114,12 +115,44 @@ const char *gdpt_last_error(void) { return last_error().c_str(); }
 
 int gdpt_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
 
-int gdpt_create(const gdpt_scene_desc *scene, int device, gdpt_ctx **out) {
+int gdpt_create_ex(const gdpt_scene_desc *scene, int device, int flags, gdpt_ctx **out) {
     if (out) *out = nullptr;
+    if (flags & ~GDPT_CREATE_NO_BVH) return fail(GDPT_ERR_ARG, "unknown creation flags %d", flags);
     gdpt_ctx *c = nullptr;
-    int r = create_context(scene, device, &c);
+    int r = create_context(scene, device, flags, &c);
     if (r != 0) { destroy_context(c); return r; }
     *out = c; return 0;
+}
+
+int gdpt_create(const gdpt_scene_desc *scene, int device, gdpt_ctx **out) { return gdpt_create_ex(scene, device, 0, out); }
+
+int gdpt_bvh_info(gdpt_ctx *ctx, int64_t *n_nodes, int64_t *n_prims, int32_t *depth, void **d_nodes, void **d_prims) {
+    if (!ctx) return fail(GDPT_ERR_ARG, "null argument");
+    if (ctx->bvh_pending) return fail(GDPT_ERR_ARG, "the context has no BVH yet");
+    if (n_nodes) *n_nodes = ctx->bvh.n_nodes;
+    if (n_prims) *n_prims = ctx->bvh.n_prims;
+    if (depth) *depth = ctx->bvh_depth;
+    if (d_nodes) *d_nodes = ctx->bvh_nodes.p;
+    if (d_prims) *d_prims = ctx->bvh_prims.p;
+    return 0;
+}
+
+int gdpt_bvh_adopt(gdpt_ctx *ctx, const void *d_nodes, int64_t n_nodes, const void *d_prims, int64_t n_prims, int32_t depth) {
+    if (!ctx || n_nodes < 0 || n_prims < 0 || (n_nodes > 0 && !d_nodes) || (n_prims > 0 && !d_prims)) return fail(GDPT_ERR_ARG, "bad argument");
+    if (!ctx->bvh_pending) return fail(GDPT_ERR_ARG, "the context already has a BVH");
+    if (n_nodes > 0x7fffffff || n_prims > 0x7fffffff || depth < 0) return fail(GDPT_ERR_ARG, "bad BVH size");
+    if (3 * depth + 1 > STACK_TOTAL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", depth);
+    GD_CUDA(cudaSetDevice(ctx->device));
+    if (int r = ctx->bvh_nodes.ensure(std::max<size_t>((size_t)n_nodes * sizeof(BvhNode), 16))) return r;
+    if (int r = ctx->bvh_prims.ensure(std::max<size_t>((size_t)n_prims * sizeof(BvhPrim), 16))) return r;
+    if (n_nodes) GD_CUDA(cudaMemcpyAsync(ctx->bvh_nodes.p, d_nodes, (size_t)n_nodes * sizeof(BvhNode), cudaMemcpyDefault, ctx->stream));
+    if (n_prims) GD_CUDA(cudaMemcpyAsync(ctx->bvh_prims.p, d_prims, (size_t)n_prims * sizeof(BvhPrim), cudaMemcpyDefault, ctx->stream));
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->bvh.nodes = ctx->bvh_nodes.as<float4>(); ctx->bvh.prims = ctx->bvh_prims.as<float4>();
+    ctx->bvh.n_nodes = (int)n_nodes; ctx->bvh.n_prims = (int)n_prims;
+    ctx->bvh_depth = depth;
+    ctx->bvh_pending = false;
+    return 0;
 }
 
 void gdpt_destroy(gdpt_ctx *ctx) { destroy_context(ctx); }

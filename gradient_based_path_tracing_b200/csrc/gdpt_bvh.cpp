@@ -204,6 +204,26 @@ inline void presplit(std::vector<Ref> &refs, const std::vector<BvhPrim> &src, si
 
 } // namespace
 
+// scene bounds as rtcGetSceneBounds reports them: float min/max of the primitive bounds,
+// spheres contributing (float)(c -/+ r) exactly (no conservative nudge)
+void scene_bounds(const std::vector<HostShape> &shapes, float lo[3], float hi[3]) {
+    for (int k = 0; k < 3; k++) { lo[k] = std::numeric_limits<float>::infinity(); hi[k] = -lo[k]; }
+    for (int s = 0; s < (int)shapes.size(); s++) {
+        const HostShape &sh = shapes[s];
+        if (sh.kind == 1) {
+            for (int t = 0; t < sh.ntris; t++) for (int c = 0; c < 3; c++) for (int k = 0; k < 3; k++) {
+                float f = (float)sh.positions[3 * (size_t)sh.indices[3 * t + c] + k];
+                lo[k] = std::min(lo[k], f); hi[k] = std::max(hi[k], f);
+            }
+        } else {
+            for (int k = 0; k < 3; k++) {
+                lo[k] = std::min(lo[k], (float)(sh.sphere[k] - sh.sphere[3]));
+                hi[k] = std::max(hi[k], (float)(sh.sphere[k] + sh.sphere[3]));
+            }
+        }
+    }
+}
+
 void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
     const bool verbose = getenv("GDPT_VERBOSE") != nullptr;
     auto t_last = std::chrono::steady_clock::now();
@@ -255,22 +275,7 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
     out.nodes.clear(); out.prims.clear();
     for (int k = 0; k < 3; k++) { out.lo[k] = std::numeric_limits<float>::infinity(); out.hi[k] = -out.lo[k]; }
     if (B.refs.empty()) return;
-    // scene bounds as rtcGetSceneBounds reports them: float min/max of the primitive bounds,
-    // spheres contributing (float)(c -/+ r) exactly (no conservative nudge)
-    for (int s = 0; s < (int)shapes.size(); s++) {
-        const HostShape &sh = shapes[s];
-        if (sh.kind == 1) {
-            for (int t = 0; t < sh.ntris; t++) for (int c = 0; c < 3; c++) for (int k = 0; k < 3; k++) {
-                float f = (float)sh.positions[3 * (size_t)sh.indices[3 * t + c] + k];
-                out.lo[k] = std::min(out.lo[k], f); out.hi[k] = std::max(out.hi[k], f);
-            }
-        } else {
-            for (int k = 0; k < 3; k++) {
-                out.lo[k] = std::min(out.lo[k], (float)(sh.sphere[k] - sh.sphere[3]));
-                out.hi[k] = std::max(out.hi[k], (float)(sh.sphere[k] + sh.sphere[3]));
-            }
-        }
-    }
+    scene_bounds(shapes, out.lo, out.hi);
     if (const char *e = getenv("GDPT_BVH_CI")) B.ci = atof(e);                                   // tuning knobs (tools/gpu_bvh_sweep.py)
     if (const char *e = getenv("GDPT_BVH_MAX_LEAF")) B.max_leaf = std::min(7, std::max(1, atoi(e)));
     double split_budget = 2.0;      // extra references allowed, as a fraction of the primitive count (B200 sweep: profiles/r1_bvh_sweep.txt)

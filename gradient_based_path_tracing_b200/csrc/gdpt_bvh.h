@@ -48,5 +48,8 @@ struct Bvh {
 
 // Binned-SAH binary build collapsed to 4-wide. Deterministic.
 void build_bvh(const std::vector<HostShape> &shapes, Bvh &out);
+// Only Bvh::lo / hi (what rtcGetSceneBounds reports), without building anything: for a context whose tree arrives from
+// another process (gdpt_create_ex + gdpt_bvh_adopt).  build_bvh computes its bounds with this function.
+void scene_bounds(const std::vector<HostShape> &shapes, float lo[3], float hi[3]);
 
 } // namespace gdpt

@@ -91,6 +91,7 @@ struct gdpt_ctx {
     bool lambertian_only = false;     // every material is a Lambertian -> specialised shade kernels
     bool count_traversal = false;     // bench-only: count nodes/primitives per ray
     bool own_stream = true;
+    bool bvh_pending = false;         // created with GDPT_CREATE_NO_BVH and not yet given a tree (gdpt_bvh_adopt)
     gdpt::DevBuf trav_counters;
 };
 
@@ -118,7 +119,7 @@ template <typename R> void fill_scene_common(DScene<R> &s, const gdpt_scene_desc
     s.max_depth = d->max_depth; s.rr_depth = d->rr_depth;
 }
 
-inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) {
+inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_ctx **out) {
     if (!d || !out) return fail(GDPT_ERR_ARG, "null argument");
     if (d->width <= 1 || d->height <= 1) return fail(GDPT_ERR_ARG, "film must be at least 2x2");
     int ndev = 0;
@@ -161,7 +162,8 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     }
     // the BVH is built on its own host thread(s) while this one decodes textures and uploads the pools
     Bvh bvh;
-    std::thread bvh_thread([&] { build_bvh(hs, bvh); });
+    const bool no_bvh = (flags & GDPT_CREATE_NO_BVH) != 0;     // the tree comes from another process: only the bounds are needed here
+    std::thread bvh_thread([&] { if (no_bvh) scene_bounds(hs, bvh.lo, bvh.hi); else build_bvh(hs, bvh); });
     struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } bvh_joiner{bvh_thread};
     // ---- geometry pools
     std::vector<double> pos(d->positions, d->positions + 3 * (size_t)d->n_positions), nrm(d->normals, d->normals + 3 * (size_t)d->n_normals),
@@ -256,6 +258,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, gdpt_ctx **out) 
     if (int r = upload(c->bvh_prims, bvh.prims)) return r;
     c->bvh.nodes = c->bvh_nodes.as<float4>(); c->bvh.prims = c->bvh_prims.as<float4>(); c->bvh.spheres = c->spheres.as<double>();
     c->bvh.n_nodes = bvh.prims.empty() ? 0 : (int)bvh.nodes.size(); c->bvh.n_prims = (int)bvh.prims.size();
+    c->bvh_pending = no_bvh;
     // bounds sphere (scene.cpp:30-34): float box from the "Embree" scene, arithmetic in double
     {
         double lb[3] = {bvh.lo[0], bvh.lo[1], bvh.lo[2]}, ub[3] = {bvh.hi[0], bvh.hi[1], bvh.hi[2]};

@@ -180,17 +180,52 @@ class DistributedPoisson:
             q.wait()
 
 
+def share_bvh_from_rank0(scene, device, dist, torch):
+    """Rank 0's BVH (gdpt_bvh_info) -> every other rank's context (gdpt_bvh_adopt): sizes in one broadcast, the 128-byte
+    nodes and the 48-byte primitive records in two more, device to device."""
+    dev = torch.device("cuda", device)
+    rank = dist.get_rank()
+    meta = torch.zeros(3, dtype=torch.int64, device=dev)
+    if rank == 0:
+        nn, npr, depth, pn, pp = scene.bvh_info(device)
+        meta[0], meta[1], meta[2] = nn, npr, depth
+    dist.broadcast(meta, src=0)
+    nn, npr, depth = (int(v) for v in meta.tolist())
+    nodes = torch.empty(max(nn, 1) * 128, dtype=torch.uint8, device=dev)
+    prims = torch.empty(max(npr, 1) * 48, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        nodes.copy_(_as_u8(torch, pn, nn * 128, dev)); prims.copy_(_as_u8(torch, pp, npr * 48, dev))
+    dist.broadcast(nodes, src=0)
+    dist.broadcast(prims, src=0)
+    torch.cuda.current_stream().synchronize()
+    if rank != 0:
+        scene.adopt_bvh(nodes.data_ptr(), nn, prims.data_ptr(), npr, depth, device=device)
+
+
+def _as_u8(torch, ptr, nbytes, dev):
+    """A torch view of `nbytes` of device memory at `ptr` (memory owned by the gdpt context)."""
+    class _Cai:
+        __cuda_array_interface__ = {"shape": (max(nbytes, 1),), "typestr": "|u1", "data": (ptr, False), "version": 2}
+    return torch.as_tensor(_Cai(), device=dev)
+
+
 class DistributedRenderer:
     """render() across the ranks of an initialised torch.distributed process group."""
 
-    def __init__(self, scene, device, dist, torch, solver="auto"):
+    def __init__(self, scene, device, dist, torch, solver="auto", share_bvh=False):
         """solver: "gather" (sum the bands onto rank 0 and solve there), "distributed" (all-to-all transposed
-        solve on all ranks) or "auto" (distributed from 3840x2160 pixels up when every rank has rows)."""
+        solve on all ranks) or "auto" (distributed from 3840x2160 pixels up when every rank has rows).
+        share_bvh: rank 0 builds the BVH, the others create their context without one and receive rank 0's through a
+        broadcast (the ranks of a box share its host cores: N identical builds side by side cost N times the core time)."""
         from . import _capi
         self.scene, self.device, self.dist, self.torch, self._capi = scene, device, dist, torch, _capi
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
         self.bands = partition_rows(scene.height, self.world)
-        self.ctx = scene.context(device)
+        if share_bvh and self.world > 1 and device not in scene._ctx:
+            self.ctx = scene.context(device, build_bvh=self.rank == 0)
+            share_bvh_from_rank0(scene, device, dist, torch)
+        else:
+            self.ctx = scene.context(device)
         n = scene.height * scene.width * 3
         dev = torch.device("cuda", device)
         self.acc = [torch.zeros(n, dtype=torch.float64, device=dev) for _ in range(5)]

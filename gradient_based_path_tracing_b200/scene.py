@@ -184,13 +184,24 @@ class Scene:
             d.envmap_to_local = _capi.as_dp(dbl("envmap.to_local", 4))
         return d
 
-    def context(self, device=0):
+    def context(self, device=0, build_bvh=True):
+        """gdpt_create on `device` (once per scene and device).  build_bvh=False: gdpt_create_ex(GDPT_CREATE_NO_BVH) — the
+        caller hands a tree over with adopt_bvh() before rendering (multi.DistributedRenderer broadcasts rank 0's)."""
         if device not in self._ctx:
             h = C.c_void_p()
             d = self.desc()
-            _capi.check(_capi.lib().gdpt_create(C.byref(d), device, C.byref(h)))
+            _capi.check(_capi.lib().gdpt_create_ex(C.byref(d), device, 0 if build_bvh else _capi.CREATE_NO_BVH, C.byref(h)))
             self._ctx[device] = h
         return self._ctx[device]
+
+    def bvh_info(self, device=0):
+        """(n_nodes, n_prims, depth, device pointer of the nodes, device pointer of the primitive records)"""
+        nn, npr, dep, pn, pp = C.c_int64(), C.c_int64(), C.c_int32(), C.c_void_p(), C.c_void_p()
+        _capi.check(_capi.lib().gdpt_bvh_info(self.context(device), C.byref(nn), C.byref(npr), C.byref(dep), C.byref(pn), C.byref(pp)))
+        return nn.value, npr.value, dep.value, pn.value, pp.value
+
+    def adopt_bvh(self, nodes_ptr, n_nodes, prims_ptr, n_prims, depth, device=0):
+        _capi.check(_capi.lib().gdpt_bvh_adopt(self._ctx[device], C.c_void_p(nodes_ptr), n_nodes, C.c_void_p(prims_ptr), n_prims, depth))
 
     def close(self):
         for h in self._ctx.values():

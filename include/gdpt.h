@@ -107,9 +107,20 @@ typedef struct {
 const char *gdpt_last_error(void);
 int gdpt_device_count(void);
 
+#define GDPT_CREATE_NO_BVH 1 /* gdpt_create_ex: everything but the BVH build */
+
 /* Upload the scene to `device`, rebuild mip chains, build the BVH (replaces Scene::Scene's
  * Embree registration/commit, scene.cpp:19-34). */
 int gdpt_create(const gdpt_scene_desc *scene, int device, gdpt_ctx **out);
+/* gdpt_create with flags.  GDPT_CREATE_NO_BVH: the context gets everything but the tree and refuses to render until a BVH
+ * built for the SAME scene is handed over with gdpt_bvh_adopt.  With one process per GPU the tree is then built once and
+ * broadcast over NCCL (multi.DistributedRenderer) instead of N times on the same host cores (the reference builds one
+ * Embree scene per process, scene.cpp:19-34; there is one process there). */
+int gdpt_create_ex(const gdpt_scene_desc *scene, int device, int flags, gdpt_ctx **out);
+/* The BVH of a context: node count (128 B each), primitive-record count (48 B each), depth, and the device arrays. */
+int gdpt_bvh_info(gdpt_ctx *ctx, int64_t *n_nodes, int64_t *n_prims, int32_t *depth, void **d_nodes, void **d_prims);
+/* Copy a BVH (device or host pointers) into a context created with GDPT_CREATE_NO_BVH. */
+int gdpt_bvh_adopt(gdpt_ctx *ctx, const void *d_nodes, int64_t n_nodes, const void *d_prims, int64_t n_prims, int32_t depth);
 void gdpt_destroy(gdpt_ctx *ctx);
 /* scene bounds radius / centre as scene.cpp:30-34 derives them (for parity checks) */
 int gdpt_scene_bounds(gdpt_ctx *ctx, double *radius_center4);

@@ -405,3 +405,27 @@ def test_cpp_host_cli_default_film_is_exr(g, scenes, tmp_path):
     for suffix, img in (("", want.poisson), ("_primal", want.primal), ("_dx", want.dx), ("_dy", want.dy)):
         got = _read_exr(str(tmp_path / ("image" + suffix + ".exr")))
         assert np.allclose(got, img.astype(np.float32).astype(np.float16).astype(np.float32), rtol=2e-3, atol=1e-7), suffix
+
+
+@pytest.mark.gpu
+def test_bvh_can_be_built_once_and_adopted(g):
+    """gdpt_create_ex(GDPT_CREATE_NO_BVH) + gdpt_bvh_adopt: the multi-GPU front end builds the tree on rank 0 only and
+    broadcasts it; a context that adopted a tree renders exactly what the context that built it renders."""
+    from gradient_based_path_tracing_b200 import _capi
+    a = g.Scene.named("sponza_small")
+    b = g.Scene(a.a)
+    b.context(0, build_bvh=False)
+    with pytest.raises(_capi.GdptError, match="GDPT_CREATE_NO_BVH"):
+        g.gradient_path_render(b, spp=1, precision="f64")
+    nn, npr, depth, pn, pp = a.bvh_info(0)
+    assert nn > 0 and npr >= a.a["indices"].shape[0] and depth > 0
+    with pytest.raises(_capi.GdptError):
+        a.adopt_bvh(pn, nn, pp, npr, depth)                       # a context that has a tree keeps it
+    b.adopt_bvh(pn, nn, pp, npr, depth)
+    assert b.bvh_info(0)[:3] == (nn, npr, depth)
+    ra = g.gradient_path_render(a, spp=2, precision="f64")
+    rb = g.gradient_path_render(b, spp=2, precision="f64")
+    for k in ("primal", "dx", "dy", "poisson"):
+        assert np.allclose(getattr(ra, k), getattr(rb, k), rtol=1e-12, atol=1e-15), k
+    assert np.array_equal(g.scene_bounds(a), g.scene_bounds(b))
+    b.close()
