@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--offsets", default="reference", choices=["reference", "shift"],
                     help="gradpath offset semantics: the reference's (the metric's config) or shift-mapped offsets (opt-in mode, DESIGN.md 12)")
+    ap.add_argument("--share-bvh", type=int, default=-1, help="N>1: 1 = rank 0 builds the BVH and broadcasts it, 0 = every rank builds its own, -1 = the library default")
     ap.add_argument("--solver", default="auto", choices=["auto", "gather", "distributed"],
                     help="N>1 Poisson solve: bands summed onto rank 0, or the all-to-all transposed solve (auto: distributed from 4K up)")
     return ap.parse_args()
@@ -183,7 +184,8 @@ def run_native(args):
     spp = args.spp or sc.options.samples_per_pixel
     w, h = sc.width, sc.height
     lib, check = _capi.lib(), _capi.check
-    R = multi.DistributedRenderer(sc, local, dist_, torch, solver=args.solver)
+    share = {} if args.share_bvh < 0 else {"share_bvh": bool(args.share_bvh)}
+    R = multi.DistributedRenderer(sc, local, dist_, torch, solver=args.solver, **share)
     check(lib.gdpt_set_stream(R.ctx, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
 
     def barrier():
@@ -228,7 +230,7 @@ def run_native(args):
             r = g.gradient_path_render(sc2, device=local, spp=spp, precision=args.precision, offsets=args.offsets)
             sc2.close()
             return r
-        R2 = multi.DistributedRenderer(sc2, local, dist_, torch, solver=args.solver)
+        R2 = multi.DistributedRenderer(sc2, local, dist_, torch, solver=args.solver, **share)
         r = R2.render(spp, precision=args.precision, to_host=True, offsets=args.offsets)
         sc2.close()
         return r

@@ -45,6 +45,14 @@ if rank == 0:
     want = g.path_render(sc, spp=2, precision="f64")
     assert np.abs(img - want).max() < 1e-12
     print("PATH OK")
+# the BVH built on rank 0 only and broadcast (gdpt_create_ex + gdpt_bvh_adopt)
+sc2 = g.Scene(sc.a)
+r = DistributedRenderer(sc2, rank, dist, torch, solver="gather", share_bvh=True)
+assert sc2.bvh_info(rank)[:3] == sc.bvh_info(rank)[:3]
+shared = r.render(spp=2, precision="f64", to_host=True)
+if rank == 0:
+    assert np.array_equal(shared["primal"], res["gather"]["primal"]) and np.array_equal(shared["poisson"], res["gather"]["poisson"])
+    print("SHARED BVH OK")
 dist.barrier()
 dist.destroy_process_group()
 '''
