@@ -50,6 +50,7 @@ def lib():
         L.gdpt_ref_render_aux.argtypes = [C.c_void_p, C.c_int, dp]
         L.gdpt_ref_imread3.argtypes = [C.c_char_p, ip, ip, dp]
         L.gdpt_ref_path_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, dp]
+        L.gdpt_ref_shift_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_uint64, dp]
         L.gdpt_ref_sample_light.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
         L.gdpt_ref_occluded.argtypes = [C.c_void_p, C.c_int, dp, ip]
         L.gdpt_ref_render_path_pixelseed.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, dp]
@@ -217,6 +218,13 @@ class RefScene:
         rad = np.zeros(3)
         lib().gdpt_ref_path_sample(self.h, x, y, stream, seed, _dp(rad))
         return rad
+
+    def shift_sample(self, x, y, stream, seed=DEFAULT_SEED):
+        """One shift-mapped gradpath sample (the product's opt-in offset mode) restated on the reference's own primitives
+        (ref_hooks.cpp: gdpt_ref_shift_sample) -> the 23-double record, offsets X0=(x-1,y), Y0=(x,y-1), X1, Y1."""
+        rec = np.zeros(23)
+        lib().gdpt_ref_shift_sample(self.h, x, y, stream, seed, _dp(rec))
+        return rec
 
     def render_path_pixelseed(self, spp, seed=DEFAULT_SEED, sample0=0):
         img = self._img()

@@ -42,6 +42,7 @@ void fourierSolve(int width, int height, const double *imgData, const double *im
 extern "C" {
 typedef struct { uint64_t state, inc; } gdpt_pcg32;
 void gdpt_oracle_pcg_init(gdpt_pcg32 *r, uint64_t stream, uint64_t seed);
+double gdpt_oracle_pcg_real(gdpt_pcg32 *r);   // next_pcg32_real<double> (src/pcg.h:52-68), bit-exact restatement (oracle/pcg_oracle.c)
 }
 
 namespace {
@@ -469,6 +470,154 @@ int gdpt_ref_export(void *hs, const char *path) {
     export_images<Real>(w, "img1", s->texture_pool.image1s);
     fclose(f);
     return 0;
+}
+
+// Shift-mapped gradpath sample (the product's opt-in offset mode, csrc/gdpt_shift.cuh) restated on the reference's OWN
+// primitives — sample_primary, intersect, occluded, sample_bsdf / eval / pdf_sample_bsdf, emission — in double, operation
+// for operation, so the GPU's FP64 records can be compared bit for bit.  It follows small_gdpt.cpp:153-352 (base path that
+// must end on a light, random-number replay, reconnection at the first diffuse pair, J = p/p' resp. the geometry ratio,
+// w = P/(P + P_s J)); it is NOT code of the reference, which has no such mode on lajolla scenes: this pins the GPU kernel
+// to an independent CPU statement of the same algorithm, not to a golden of the reference.
+// rec[23]: radiance3, contrib3, contribX0 3, contribX1 3, contribY0 3, contribY1 3, prob, wX0, wY0, wX1, wY1
+// with X0 = (x-1, y), Y0 = (x, y-1), X1 = (x+1, y), Y1 = (x, y+1).
+void gdpt_ref_shift_sample(void *hs, int x, int y, uint64_t stream, uint64_t seed, double *rec) {
+    const Scene &scene = *(Scene *)hs;
+    const int MAX_VERTS = 24, MAX_PREFIX = 12;
+    const double SURVIVAL = 0.75;
+    const int w = scene.camera.width, h = scene.camera.height;
+    const int max_depth = scene.options.max_depth, rr_depth = scene.options.rr_depth;
+    const Real eps = get_intersection_epsilon(scene);
+    auto diffuse = [&](int material_id) {
+        const Material &m = scene.materials[material_id];
+        return std::holds_alternative<Lambertian>(m) || std::holds_alternative<DisneyDiffuse>(m);
+    };
+    auto cls_of = [&](const PathVertex &v) {
+        bool light = is_light(scene.shapes[v.shape_id]);
+        return ((light || diffuse(v.material_id)) ? 1 : 0) | (light ? 2 : 0);
+    };
+    double cS[4][3], wS[4], contrib[3] = {0, 0, 0}, rad[3] = {0, 0, 0}, prob = 1.0;
+    for (int k = 0; k < 4; k++) { cS[k][0] = cS[k][1] = cS[k][2] = 0.0; wS[k] = 1.0; }
+    auto write = [&]() {
+        rec[0] = rad[0]; rec[1] = rad[1]; rec[2] = rad[2]; rec[3] = contrib[0]; rec[4] = contrib[1]; rec[5] = contrib[2];
+        const int slot[4] = {0, 2, 1, 3};     // record order X0, X1, Y0, Y1; offsets here X0, Y0, X1, Y1
+        for (int k = 0; k < 4; k++) for (int c = 0; c < 3; c++) rec[6 + 3 * slot[k] + c] = cS[k][c];
+        rec[18] = prob; rec[19] = wS[0]; rec[20] = wS[1]; rec[21] = wS[2]; rec[22] = wS[3];
+    };
+    gdpt_pcg32 rng; gdpt_oracle_pcg_init(&rng, stream, seed);
+    const Real rx = gdpt_oracle_pcg_real(&rng), ry = gdpt_oracle_pcg_real(&rng);
+    const RayDifferential rd0 = init_ray_differential(w, h);
+
+    // ---- base path
+    Real pu0[MAX_PREFIX], pu1[MAX_PREFIX], pw[MAX_PREFIX], pp[MAX_PREFIX];
+    int pclass[MAX_PREFIX + 1];
+    Ray ray = sample_primary(scene.camera, Vector2((x + rx) / w, (y + ry) / h));
+    std::optional<PathVertex> hit = intersect(scene, ray, rd0);
+    bool base_ok = false, offsets_ok = true, prev_diffuse = false;
+    int L = -1, dr = -1;
+    double C[3] = {1, 1, 1}, P = 1, inv_rr = 1, Sf[3] = {1, 1, 1}, Sp = 1;
+    Spectrum Le{0, 0, 0};
+    Vector3 wr{0, 0, 1}, pos_dr = ray.org, prev_pos = ray.org, dir_in = ray.dir;
+    PathVertex vr;
+    if (hit) {
+        PathVertex v = *hit;
+        for (int j = 0; j < MAX_VERTS; j++) {
+            const int cls = cls_of(v);
+            if (dr < 0 && j > 0 && prev_diffuse && (cls & 1)) { dr = j - 1; vr = v; pos_dr = prev_pos; }
+            if (dr < 0 || j <= dr) { if (j <= MAX_PREFIX) pclass[j] = cls; else offsets_ok = false; }
+            if (cls & 2) { Le = emission(v, -dir_in, scene); L = j; base_ok = true; break; }
+            if (j + 1 >= MAX_VERTS) break;
+            if (max_depth != -1 && j + 2 > max_depth) break;
+            const Real u0 = gdpt_oracle_pcg_real(&rng), u1 = gdpt_oracle_pcg_real(&rng), uw = gdpt_oracle_pcg_real(&rng);
+            const Material &mat = scene.materials[v.material_id];
+            std::optional<BSDFSampleRecord> s = sample_bsdf(mat, -dir_in, v, scene.texture_pool, Vector2{u0, u1}, uw);
+            if (!s) break;
+            const Spectrum f = eval(mat, -dir_in, s->dir_out, v, scene.texture_pool);
+            const Real p = pdf_sample_bsdf(mat, -dir_in, s->dir_out, v, scene.texture_pool);
+            if (!(p > 0) || !(f.x > 0 || f.y > 0 || f.z > 0)) break;
+            if (dr < 0) { if (j < MAX_PREFIX) { pu0[j] = u0; pu1[j] = u1; pw[j] = uw; pp[j] = p; } else offsets_ok = false; }
+            else if (j == dr + 1) wr = s->dir_out;
+            else { Sf[0] *= f.x; Sf[1] *= f.y; Sf[2] *= f.z; Sp *= p; }
+            C[0] *= f.x; C[1] *= f.y; C[2] *= f.z; P *= p;
+            if (j + 2 >= rr_depth) {
+                if (!(gdpt_oracle_pcg_real(&rng) <= Real(SURVIVAL))) break;
+                inv_rr /= SURVIVAL;
+            }
+            Ray next{v.position, s->dir_out, eps, infinity<Real>()};
+            hit = intersect(scene, next);
+            if (!hit) break;
+            prev_pos = v.position; prev_diffuse = (cls & 1) != 0; dir_in = s->dir_out;
+            v = *hit;
+        }
+    }
+    if (!base_ok) { write(); return; }
+    contrib[0] = C[0] * Le.x * inv_rr; contrib[1] = C[1] * Le.y * inv_rr; contrib[2] = C[2] * Le.z * inv_rr;
+    for (int c = 0; c < 3; c++) rad[c] = contrib[c] / P;
+    prob = P;
+
+    // ---- offsets
+    const int ox[4] = {-1, 0, 1, 0}, oy[4] = {0, -1, 0, 1};
+    const int jend = dr >= 0 ? dr : L;
+    for (int k = 0; k < 4 && offsets_ok; k++) {
+        Ray ro = sample_primary(scene.camera, Vector2(((x + ox[k]) + rx) / w, ((y + oy[k]) + ry) / h));
+        std::optional<PathVertex> ho = intersect(scene, ro, rd0);
+        if (!ho) continue;
+        PathVertex vo = *ho;
+        Vector3 din = ro.dir;
+        double Cs[3] = {1, 1, 1}, Ps = 1, J = 1;
+        bool ok = true;
+        for (int j = 0; ; j++) {
+            if (cls_of(vo) != pclass[j]) { ok = false; break; }
+            if (j == jend) break;
+            const Material &mat = scene.materials[vo.material_id];
+            std::optional<BSDFSampleRecord> s = sample_bsdf(mat, -din, vo, scene.texture_pool, Vector2{pu0[j], pu1[j]}, pw[j]);
+            if (!s) { ok = false; break; }
+            const Spectrum f = eval(mat, -din, s->dir_out, vo, scene.texture_pool);
+            const Real p = pdf_sample_bsdf(mat, -din, s->dir_out, vo, scene.texture_pool);
+            if (!(p > 0)) { ok = false; break; }
+            Cs[0] *= f.x; Cs[1] *= f.y; Cs[2] *= f.z; Ps *= p; J *= pp[j] / p;
+            Ray next{vo.position, s->dir_out, eps, infinity<Real>()};
+            ho = intersect(scene, next);
+            if (!ho) { ok = false; break; }
+            din = s->dir_out;
+            vo = *ho;
+        }
+        if (!ok) continue;
+        if (dr < 0) {
+            const Spectrum e = emission(vo, -din, scene);
+            Cs[0] *= e.x; Cs[1] *= e.y; Cs[2] *= e.z;
+        } else {
+            const Vector3 dv = vr.position - vo.position;
+            const Real d2s = dot(dv, dv);
+            if (!(d2s > 0)) continue;
+            const Real dist = sqrt(d2s);
+            const Vector3 ds = dv / dist;
+            const Material &mat = scene.materials[vo.material_id];
+            const Spectrum f = eval(mat, -din, ds, vo, scene.texture_pool);
+            const Real p = pdf_sample_bsdf(mat, -din, ds, vo, scene.texture_pool);
+            const Vector3 bv = vr.position - pos_dr;
+            const Real d2b = dot(bv, bv);
+            const Real cos_s = fabs(dot(ds, vr.geometric_normal)), cos_b = fabs(dot(bv, vr.geometric_normal)) / sqrt(d2b);
+            if (!(p > 0 && cos_b > 0 && d2b > 0)) continue;
+            J *= (cos_s / d2s) / (cos_b / d2b);
+            Cs[0] *= f.x; Cs[1] *= f.y; Cs[2] *= f.z; Ps *= p;
+            if (L == dr + 1) {
+                const Spectrum e = emission(vr, -ds, scene);
+                Cs[0] *= e.x; Cs[1] *= e.y; Cs[2] *= e.z;
+            } else {
+                const Material &mr = scene.materials[vr.material_id];
+                const Spectrum ft = eval(mr, -ds, wr, vr, scene.texture_pool);
+                const Real pt = pdf_sample_bsdf(mr, -ds, wr, vr, scene.texture_pool);
+                if (!(pt > 0)) continue;
+                Cs[0] *= ft.x * Sf[0] * Le.x; Cs[1] *= ft.y * Sf[1] * Le.y; Cs[2] *= ft.z * Sf[2] * Le.z;
+                Ps *= pt * Sp;
+            }
+            if (occluded(scene, Ray{vo.position, ds, eps, (1 - eps) * dist})) continue;
+        }
+        if (!(J > 0.0) || !std::isfinite(J) || !std::isfinite(Ps)) continue;
+        for (int c = 0; c < 3; c++) cS[k][c] = Cs[c] * J * inv_rr;
+        wS[k] = P / (P + Ps * J);
+    }
+    write();
 }
 
 } // extern "C"
