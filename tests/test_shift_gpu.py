@@ -193,3 +193,53 @@ def test_records_match_the_cpu_statement_on_the_reference_primitives(g, name):
         # a last-ulp difference may flip a branch (roulette, lobe choice, a grazing shadow ray): a handful of samples at most
         assert bad.sum() <= max(2, 0.002 * len(want)), "%s kernel %s: %d of %d records differ (%d of them among the %d base paths that reached a light)" % (
             name, kernel, bad.sum(), len(want), (bad & hit).sum(), hit.sum())
+
+
+def test_image_pipeline_equals_the_oracle_records_accumulated_in_numpy(g):
+    """The whole image path of the mode — accumulation signs, the y pairing, the border rule, the merge, the screened
+    Poisson solve — against the CPU statement: every (pixel, sample) record from the oracle, accumulated here in numpy
+    the way finish_shift / k_merge do it, solved with the oracle's fourierSolve restatement."""
+    from oracle import ref, cport
+    if not (ref.available() and ref.scenes_available()):
+        pytest.skip("oracle/_ref not built")
+    sc = g.Scene.named("cbox_gdpt_64")
+    W, H, spp = sc.width, sc.height, 2
+    rs = ref.RefScene(ref.scene_path("cbox_gdpt_64"), threads=1)
+    img = np.zeros((H, W, 3)); cx0 = np.zeros((H, W, 3)); cy0 = np.zeros((H, W, 3)); cx1 = np.zeros((H, W, 3)); cy1 = np.zeros((H, W, 3))
+    try:
+        for s in range(spp):
+            for y in range(H):
+                for x in range(W):
+                    r = rs.shift_sample(x, y, s * W * H + y * W + x)
+                    c, p = r[3:6], r[18]
+                    img[y, x] += r[0:3] / spp
+                    vx0 = (c - r[6:9]) * (r[19] / (p * spp)); vx1 = (r[9:12] - c) * (r[21] / (p * spp))
+                    vy0 = (c - r[12:15]) * (r[20] / (p * spp)); vy1 = (r[15:18] - c) * (r[22] / (p * spp))
+                    if x > 0:
+                        cx0[y, x] += vx0
+                        if x == 1:
+                            cx0[y, 0] -= vx0
+                    if y > 0:
+                        cy0[y, x] += vy0
+                        if y == 1:
+                            cy0[0, x] -= vy0
+                    if x < W - 1:
+                        cx1[y, x] += vx1
+                        if x == 0:
+                            cx0[y, 0] -= vx1
+                    if y < H - 1:
+                        cy1[y, x] += vy1
+                        if y == 0:
+                            cy0[0, x] -= vy1
+    finally:
+        rs.close()
+    cx = cx0.copy(); cx[:, 1:] += cx1[:, :-1]
+    cy = cy0.copy(); cy[1:] += cy1[:-1]
+    want_poisson = cport.poisson(img, cx, cy, 0.04)
+    got = g.gradient_path_render(sc, spp=spp, precision="f64", offsets="shift")
+    assert img.any() and cx.any() and cy.any()
+    for name, a, b in (("primal", got.primal, img), ("dx", got.dx, cx), ("dy", got.dy, cy)):
+        close = np.abs(a - b) <= 1e-9 * (1e-12 + np.abs(b))
+        assert close.all(axis=2).mean() > 0.998, "%s: %d pixels differ" % (name, (~close.all(axis=2)).sum())
+    rel = np.linalg.norm(got.poisson - want_poisson) / np.linalg.norm(want_poisson)
+    assert rel < 1e-5, rel
