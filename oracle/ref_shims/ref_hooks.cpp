@@ -3,8 +3,10 @@
 // C entry points around the REAL reference (compiled from /root/reference/src
 // into oracle/_ref/liblajolla_ref.so by oracle/build_ref.sh) so that tests, the
 // golden-vector generator and bench.py's CPU arm can drive it through ctypes.
-// Nothing here re-implements the path; it only calls the reference's own
-// functions:
+// Nothing here re-implements the reference's path; it only calls the reference's own
+// functions (the one exception, gdpt_ref_shift_sample at the end, is the checker of the product's
+// opt-in shift-mapped mode, which the reference does not have: a statement of that algorithm
+// built from the reference's own routines, and marked as such):
 //   parse_scene      src/parsers/parse_scene.cpp:1615-1630
 //   render           src/render.cpp:374-394  (GradPath arm -> gradient_path_render :257-370)
 //   fourierSolve     src/render.cpp:172-254
