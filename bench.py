@@ -37,7 +37,9 @@ def parse():
     ap.add_argument("--spp", type=int, default=0, help="0 = the config's sample count (512)")
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="target CPU time of one reference sample")
+    ap.add_argument("--ref-total-seconds", type=float, default=150.0, help="--impl reference: target wall time of all warm-up + timed steps together")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--f64-steps", type=int, default=1, help="N=1: full-size steps of the FP64 (reference-precision) mode timed beside the headline (0 = skip)")
     ap.add_argument("--offsets", default="reference", choices=["reference", "shift"],
                     help="gradpath offset semantics: the reference's (the metric's config) or shift-mapped offsets (opt-in mode, DESIGN.md 12)")
     ap.add_argument("--share-bvh", type=int, default=-1, help="N>1: 1 = rank 0 builds the BVH and broadcasts it, 0 = every rank builds its own, -1 = the library default")
@@ -96,38 +98,106 @@ def measured_peaks():
 
 
 # --------------------------------------------------------------------------------------- reference arm
+def metric_name(w, h):
+    return METRIC if (w, h) == (1920, 1080) else METRIC.replace("1920x1080", "%dx%d" % (w, h))
+
+
+def workload_name(scene, w, h, spp, offsets="reference"):
+    """The ONE workload string both arms print (config.workload)."""
+    return "%s gradpath %dx%d %d spp, %s" % (scene, w, h, spp, "reference offset semantics" if offsets == "reference" else "shift-mapped offsets (opt-in mode)")
+
+
+class RefTimer:
+    """Times the compiled reference's render() (oracle/_ref) and models its cost as AFFINE in the sample count:
+    cost(spp) = fixed + spp * per_spp.  `fixed` is what render.cpp does once per frame on one thread — image
+    allocation, the merge (render.cpp:340-350) and fourierSolve (:353) — `per_spp` is the sampling loop (:277-330)
+    on all host threads.  Two calibration renders (1 spp and `hi` spp) give the fit; every timed step is one
+    render at `spp_step` whose slope is re-derived with the calibrated `fixed`."""
+
+    def __init__(self, scene_name, cores):
+        from oracle import ref
+        self.ref = ref
+        self.cores = cores
+        ref.init(cores)
+        self.s = ref.RefScene(ref.scene_path(scene_name))
+        self.w, self.h, self.full_spp = self.s.width, self.s.height, self.s.spp
+
+    def render(self, spp):
+        ref = self.ref
+        self.s.set_options(spp=spp)
+        ref.rtc_stats(True)
+        c0 = ref.tsc(); t0 = time.perf_counter()
+        self.s.render()
+        dt = time.perf_counter() - t0
+        ticks, calls = ref.rtc_stats()
+        hz = (ref.tsc() - c0) / dt
+        return dt, ticks / hz          # wall seconds, thread-seconds inside rtcIntersect1/rtcOccluded1
+
+    def calibrate(self, budget_s):
+        t1, r1 = self.render(1)
+        hi = max(2, min(8, int(budget_s / max(t1, 1e-3))))
+        th, rh = self.render(hi)
+        self.per_spp = max((th - t1) / (hi - 1), 1e-9)
+        self.fixed = max(t1 - self.per_spp, 0.0)
+        self.rtc_per_spp = max((rh - r1) / (hi - 1), 0.0)      # thread-seconds per spp inside the stand-in ray caster
+        return hi
+
+    def solve_alone(self):
+        import numpy as np
+        u = np.zeros((self.h, self.w, 3)); u[::7, ::5] = 1.0
+        t0 = time.perf_counter(); self.ref.fourier_solve(u, u, u); return time.perf_counter() - t0
+
+    def close(self):
+        self.s.close()
+
+
+def reference_line(args, timer, full_spp, step_times, spp_step, hi):
+    w, h, cores = timer.w, timer.h, timer.cores
+    slopes = [max((t - timer.fixed) / spp_step, 1e-9) for t in step_times] or [timer.per_spp]
+    per_spp = sum(slopes) / len(slopes)
+    cost = timer.fixed + full_spp * per_spp                     # seconds for the full workload
+    mpaths = 5.0 * w * h * full_spp / cost / 1e6
+    rtc_frac = min(1.0, timer.rtc_per_spp / (timer.per_spp * cores)) if timer.per_spp > 0 else None
+    # the same run with the ray caster free of charge: a bound no Embree build could beat
+    cost_free = timer.fixed + full_spp * per_spp * (1.0 - (rtc_frac or 0.0))
+    sample = ("%dx%d: render() timed at 1 and %d spp for the affine fit cost(spp) = %.2f s + spp * %.3f s, then %d step(s) at %d spp "
+              "(of %d), %d host threads; fourierSolve alone %.2f s; ray casting = oracle stand-in (BVH4, SSE slab tests, double "
+              "Moeller-Trumbore; no Embree on this box) = %.0f %% of the sampling loop's thread time" %
+              (w, h, hi, timer.fixed, per_spp, len(step_times), spp_step, full_spp, cores, timer.solve_s, 100 * (rtc_frac or 0)))
+    cb = {"value": mpaths, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample,
+          "fixed_s": timer.fixed, "per_spp_s": per_spp, "solve_alone_s": timer.solve_s, "rtc_fraction": rtc_frac,
+          "value_if_ray_casting_were_free": 5.0 * w * h * full_spp / cost_free / 1e6}
+    return mpaths, cost, cb
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle import ref
-    import numpy as np
     if not ref.scenes_available():
         emit({"impl": "reference", "unavailable": "oracle/_ref (compiled reference + staged scenes) is missing"})
         return
     cores = os.cpu_count() or 1
-    ref.init(cores)
-    s = ref.RefScene(ref.scene_path(args.scene))
-    full_spp = args.spp or s.spp
-    w, h = s.width, s.height
-    # bounded sample: the same film at reduced spp (cost is linear in spp, render.cpp:303); calibrate with 1 spp
-    s.set_options(spp=1)
-    t0 = time.time(); s.render(); t1 = time.time() - t0
-    spp = max(1, min(full_spp, int(args.cpu_seconds / max(t1, 1e-3))))
-    s.set_options(spp=spp)
+    timer = RefTimer(args.scene, cores)
+    full_spp = args.spp or timer.full_spp
+    hi = timer.calibrate(args.cpu_seconds)
+    timer.solve_s = timer.solve_alone()
+    # every step is one bounded render; the whole --steps/--warmup run is held to about --ref-total-seconds
+    n = max(1, args.warmup + args.steps)
+    spp_step = max(1, min(full_spp, int((args.ref_total_seconds / n - timer.fixed) / timer.per_spp)))
     times = []
-    for i in range(args.warmup + args.steps):
-        t0 = time.time(); s.render(); dt = time.time() - t0
+    for i in range(n):
+        dt, _ = timer.render(spp_step)
         if i >= args.warmup:
             times.append(dt)
-    dt = sum(times) / len(times)
-    mpaths = 5.0 * w * h * spp / dt / 1e6
-    sample = "%dx%d at %d spp (of %d; cost linear in spp), render() incl. merge + fourierSolve, %d host threads; ray casting = oracle stand-in BVH (no Embree on this box)" % (w, h, spp, full_spp, cores)
-    line = {"metric": METRIC, "value": mpaths, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": dt * 1e3 * full_spp / spp, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+    mpaths, cost, cb = reference_line(args, timer, full_spp, times, spp_step, hi)
+    timer.close()
+    line = {"metric": metric_name(timer.w, timer.h), "value": mpaths, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": cost * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "impl": "reference",
-            "config": {"workload": "%s gradpath %dx%d %d spp (reference semantics)" % (args.scene, w, h, full_spp)},
-            "cpu_baseline": {"value": mpaths, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+            "config": {"workload": workload_name(args.scene, timer.w, timer.h, full_spp)},
+            "cpu_baseline": cb,
             "e2e": {"value": mpaths, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
 
@@ -138,17 +208,12 @@ def cpu_baseline(args, scene_name, full_spp):
         from oracle import ref
         if not ref.scenes_available():
             return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref missing on this box"}
-        cores = os.cpu_count() or 1
-        ref.init(cores)
-        s = ref.RefScene(ref.scene_path(scene_name))
-        s.set_options(spp=1)
-        t0 = time.time(); s.render(); t1 = time.time() - t0
-        spp = max(1, min(full_spp, int(args.cpu_seconds / max(t1, 1e-3))))
-        s.set_options(spp=spp)
-        t0 = time.time(); s.render(); dt = time.time() - t0
-        s.close()
-        return {"value": 5.0 * s.width * s.height * spp / dt / 1e6, "unit": UNIT, "cores": cores, "kind": "reference",
-                "sample": "%dx%d at %d spp of %d (cost linear in spp), %.1f s wall on %d threads; stand-in BVH, no Embree" % (s.width, s.height, spp, full_spp, dt, cores)}
+        timer = RefTimer(scene_name, os.cpu_count() or 1)
+        hi = timer.calibrate(args.cpu_seconds)
+        timer.solve_s = timer.solve_alone()
+        _, _, cb = reference_line(args, timer, full_spp, [], 1, hi)
+        timer.close()
+        return cb
     except Exception as e:  # the baseline must never take the bench down
         return {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "failed: %r" % (e,)}
 
@@ -246,6 +311,32 @@ def run_native(args):
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
     e2e_val = paths / (float(e2e_ms.item()) * 1e-3) / 1e6
 
+    # ---- the reference's own precision (Real = double, lajolla.h:23): the same workload in the FP64 mode that carries the
+    # bit-level parity evidence, device-resident and end to end, a bounded number of full-size steps
+    f64 = None
+    if args.precision != "f64" and args.f64_steps > 0:
+        R.render(max(1, spp // 64), precision="f64", offsets=args.offsets)       # warm-up: kernels + allocations of the double records
+        barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(args.f64_steps):
+            R.render(spp, precision="f64", offsets=args.offsets)
+        f1.record()
+        barrier()
+        fms = torch.tensor([f0.elapsed_time(f1) / args.f64_steps], dtype=torch.float64, device="cuda")
+        saved = args.precision
+        args.precision = "f64"
+        t0 = time.perf_counter()
+        e2e_step()
+        barrier()
+        fe = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device="cuda")
+        args.precision = saved
+        if world > 1:
+            dist.all_reduce(fms, op=dist.ReduceOp.MAX); dist.all_reduce(fe, op=dist.ReduceOp.MAX)
+        f64 = {"value": paths / (float(fms.item()) * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": float(fms.item()), "steps": args.f64_steps,
+               "e2e": {"value": paths / (float(fe.item()) * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": float(fe.item()), "steps": 1},
+               "note": "same workload in GDPT_PRECISION_F64 (double traversal tests + shading, -fmad=false): the mode whose per-sample records equal the compiled reference's"}
+
     if rank == 0:
         # ---- roofline of the traversal kernel (k_trace): algorithmic bytes per ray from a counting pass
         peaks, how = measured_peaks()
@@ -271,25 +362,26 @@ def run_native(args):
                 pass
         nb = ncu.get("bounce")
         issue_peak = 148 * 4 * (clocks["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)) * 1e6     # warp instructions / s
-        roof = {"bound": "hbm", "kernel": "k_trace" if args.offsets == "reference" else "k_shift (ray casts + shading in one kernel; bytes = its rays x the traversal bytes per ray)", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                "frac": achieved / peaks["hbm_gbs"] if achieved else None,
-                "traffic": nb["dram_bytes"] if nb else None, "peak_source": how,
+        l2_peak = float(l2[0]) or None
+        roof = {"bound": "l2", "kernel": "k_trace" if args.offsets == "reference" else "k_shift (ray casts + shading in one kernel; bytes = its rays x the traversal bytes per ray)",
+                "achieved": achieved, "peak": l2_peak, "unit": "GB/s", "frac": (achieved / l2_peak) if achieved and l2_peak else None,
+                "peak_source": "live L2 read microbenchmark in this run (gdpt_measure_l2_read: 48 MB buffer, ld.global.cg, all SMs); MEASURED_PEAKS.json has no L2 figure",
+                "traffic": nb["dram_bytes"] if nb else None, "traffic_source": "committed ncu capture (profiles/), not this run",
                 "bytes_per_ray": bytes_per_ray, "nodes_per_ray": cnt[0], "prims_per_ray": cnt[1],
-                "l2": {"peak": float(l2[0]) or None, "frac": (achieved / float(l2[0])) if achieved and l2[0] > 0 else None,
-                       "how": "live read microbenchmark, 48 MB buffer, ld.global.cg, all SMs"},
+                "hbm": {"peak": peaks["hbm_gbs"], "peak_source": how, "frac": achieved / peaks["hbm_gbs"] if achieved else None,
+                        "note": "not a bound: the scene is cache-resident, DRAM sees only the ray / hit / permutation streams (`traffic`)"},
                 "issue": ({"issue_active_frac": nb["issue_active_pct"] / 100.0, "threads_per_inst": nb["threads_per_inst"],
                            "lane_slot_frac": nb["issue_active_pct"] / 100.0 * nb["threads_per_inst"] / 32.0,
-                           "issue_peak_winst_per_s": issue_peak, "source": "profiles/r1_k_trace_bounce.json (ncu --set full, bounce launch)"}
+                           "issue_peak_winst_per_s": issue_peak, "source": "committed ncu capture of a bounce launch (profiles/), not this run"}
                           if nb else None),
-                "note": "algorithmic bytes = 32 B ray + 20 B hit + 128 B x nodes + 48 B x primitives per ray, served almost entirely by L1/L2 "
-                        "(scene ~45 MB is cache-resident; ncu DRAM traffic per bounce launch in `traffic`), so the fraction of the HBM peak can "
-                        "exceed 1; the binding limits are issue rate and L1/L2 latency under divergence (`issue`, DESIGN.md 4.1)",
+                "note": "algorithmic bytes = 32 B ray + 20 B hit + node bytes x nodes + 48 B x primitives per ray (counting pass of this run), served by L1/L2: "
+                        "the binding limits are L2/L1 bandwidth-latency and issue slots under divergence (DESIGN.md 4.1)",
                 "share_of_step": {"k_trace": ms_trace / (ms_step * args.steps), "shade_kernels": ms_shade / (ms_step * args.steps)},
                 "mrays_per_s": rays / (ms_trace * 1e-3) / 1e6 if ms_trace > 0 else None}
-        line = {"metric": METRIC if (w, h) == (1920, 1080) else METRIC.replace("1920x1080", "%dx%d" % (w, h)), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        line = {"metric": metric_name(w, h), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": args.precision, "data": "synthetic",
-                "config": {"workload": "%s gradpath %dx%d %d spp, %s, image split into %d row band(s)" % (args.scene, w, h, spp, "reference offset semantics" if args.offsets == "reference" else "shift-mapped offsets (opt-in mode)", world),
+                "config": {"workload": workload_name(args.scene, w, h, spp, args.offsets), "row_bands": world,
                            "precision": args.precision + " traversal/shading, f64 accumulation + Poisson",
                            "poisson_solver": R.solver if world > 1 else "single GPU",
                            "l2_flush": "inputs larger than L2: each step streams %.1f GB of path state" % (paths / 5 * 900 / 1e9)},
@@ -298,6 +390,8 @@ def run_native(args):
                         "ms_per_step": float(e2e_ms.item())},
                 "roofline": roof,
                 "msamples_per_s": value / 5.0}
+        if f64:
+            line["f64"] = f64
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, args.scene, spp)
         emit(line)

@@ -382,9 +382,9 @@ int gdpt_path_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, co
     if (int rc = ctx->ys.ensure((size_t)n * 4)) return rc;
     if (int rc = ctx->streams.ensure((size_t)n * 8)) return rc;
     if (int rc = ctx->recout.ensure((size_t)n * 3 * 8)) return rc;
-    GD_CUDA(cudaMemcpy(ctx->xs.p, xs, (size_t)n * 4, cudaMemcpyHostToDevice));
-    GD_CUDA(cudaMemcpy(ctx->ys.p, ys, (size_t)n * 4, cudaMemcpyHostToDevice));
-    GD_CUDA(cudaMemcpy(ctx->streams.p, streams, (size_t)n * 8, cudaMemcpyHostToDevice));
+    GD_CUDA(cudaMemcpyAsync(ctx->xs.p, xs, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    GD_CUDA(cudaMemcpyAsync(ctx->ys.p, ys, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    GD_CUDA(cudaMemcpyAsync(ctx->streams.p, streams, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
     GD_CUDA(cudaMemsetAsync(ctx->recout.p, 0, (size_t)n * 3 * 8, ctx->stream));
     WaveParams wp; memset(&wp, 0, sizeof(wp));
     wp.width = ctx->width; wp.height = ctx->height; wp.y0 = 0; wp.y1 = ctx->height; wp.tiles_x = (ctx->width + 7) / 8;
@@ -434,9 +434,9 @@ int gdpt_grad_samples(gdpt_ctx *ctx, const gdpt_render_params *params, int n, co
     if (int rc = ctx->ys.ensure((size_t)n * 4)) return rc;
     if (int rc = ctx->streams.ensure((size_t)n * 8)) return rc;
     if (int rc = ctx->recout.ensure((size_t)n * 23 * 8)) return rc;
-    GD_CUDA(cudaMemcpy(ctx->xs.p, xs, (size_t)n * 4, cudaMemcpyHostToDevice));
-    GD_CUDA(cudaMemcpy(ctx->ys.p, ys, (size_t)n * 4, cudaMemcpyHostToDevice));
-    GD_CUDA(cudaMemcpy(ctx->streams.p, streams, (size_t)n * 8, cudaMemcpyHostToDevice));
+    GD_CUDA(cudaMemcpyAsync(ctx->xs.p, xs, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    GD_CUDA(cudaMemcpyAsync(ctx->ys.p, ys, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    GD_CUDA(cudaMemcpyAsync(ctx->streams.p, streams, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
     if (int rc = fill_default_records(ctx, n, ctx->recout.as<double>())) return rc;
     WaveParams wp; memset(&wp, 0, sizeof(wp));
     wp.width = ctx->width; wp.height = ctx->height; wp.y0 = 0; wp.y1 = ctx->height; wp.tiles_x = (ctx->width + 7) / 8;

@@ -122,6 +122,9 @@ template <typename R> void fill_scene_common(DScene<R> &s, const gdpt_scene_desc
 inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_ctx **out) {
     if (!d || !out) return fail(GDPT_ERR_ARG, "null argument");
     if (d->width <= 1 || d->height <= 1) return fail(GDPT_ERR_ARG, "film must be at least 2x2");
+    if (d->n_positions < 0 || d->n_triangles < 0 || d->n_normals < 0 || d->n_uvs < 0 || d->n_positions > 0x7fffffffLL / 4 || d->n_triangles > 0x7fffffffLL / 4 ||
+        d->n_normals > 0x7fffffffLL / 4 || d->n_uvs > 0x7fffffffLL / 4 || d->n_shapes < 0 || d->n_materials < 0 || d->n_textures < 0 || d->n_lights < 0)
+        return fail(GDPT_ERR_ARG, "pool sizes out of range");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(GDPT_ERR_CUDA, "no CUDA device: libgdpt has no CPU fallback");
     if (device < 0 || device >= ndev) return fail(GDPT_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
@@ -152,6 +155,14 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
         ds.kind = s[0]; ds.material_id = s[1]; ds.area_light_id = s[2]; ds.flags = s[5];
         ds.vtx_off = (int)o[0]; ds.tri_off = (int)o[1]; ds.nrm_off = (int)o[2]; ds.uv_off = (int)o[3];
         ds.n_tris = s[4]; ds.cdf_off = -1;
+        // every range the builder and the shading kernels will index must lie inside the pools
+        if (s[0] != 0 && s[0] != 1) return fail(GDPT_ERR_ARG, "shape %d: unknown kind %d", i, s[0]);
+        for (int k = 0; k < 4; k++) if (o[k] < 0 || o[k] > 0x7fffffffLL / 4) return fail(GDPT_ERR_ARG, "shape %d: pool offset %lld out of range", i, (long long)o[k]);
+        if (s[0] == 1) {
+            if (s[3] < 0 || s[4] < 0 || o[0] + s[3] > d->n_positions || o[1] + s[4] > d->n_triangles) return fail(GDPT_ERR_ARG, "shape %d: vertex / triangle range outside the pools", i);
+            if ((s[5] & 1) && o[2] + s[3] > d->n_normals) return fail(GDPT_ERR_ARG, "shape %d: normal range outside the pool", i);
+            if ((s[5] & 2) && o[3] + s[3] > d->n_uvs) return fail(GDPT_ERR_ARG, "shape %d: uv range outside the pool", i);
+        }
         if (ds.material_id < 0 || ds.material_id >= d->n_materials) return fail(GDPT_ERR_ARG, "shape %d: material id %d out of range", i, ds.material_id);
         if (ds.area_light_id >= d->n_lights) return fail(GDPT_ERR_ARG, "shape %d: light id out of range", i);
         HostShape &h = hs[i];

@@ -43,7 +43,7 @@ std::string read_container(const std::string &path, Container &out) {
     }
     if (raw.size() < 8 || memcmp(raw.data(), "GDPT1", 5) != 0) return path + " is not a GDPT1 container";
     size_t pos = 8;
-    auto need = [&](size_t n) { return pos + n <= raw.size(); };
+    auto need = [&](size_t n) { return pos <= raw.size() && n <= raw.size() - pos; };   // no wrap-around on a file-controlled length
     while (pos < raw.size()) {
         uint32_t nl, nd; uint64_t nb;
         if (!need(4)) return path + ": truncated record";

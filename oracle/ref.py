@@ -54,6 +54,8 @@ def lib():
         L.gdpt_ref_sample_light.argtypes = [C.c_void_p, C.c_int, dp, dp, dp]
         L.gdpt_ref_occluded.argtypes = [C.c_void_p, C.c_int, dp, ip]
         L.gdpt_ref_render_path_pixelseed.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, dp]
+        L.gdpt_rtc_standin_stats.argtypes = [C.POINTER(C.c_uint64), C.c_int]
+        L.gdpt_rtc_standin_tsc.restype = C.c_uint64
         _lib = L
     return _lib
 
@@ -96,6 +98,17 @@ def init(threads=None):
         lib().gdpt_ref_init(threads)
         _threads = threads
     return threads
+
+
+def rtc_stats(reset=False):
+    """(TSC ticks inside the stand-in's rtcIntersect1/rtcOccluded1 summed over threads, calls)."""
+    out = (C.c_uint64 * 2)()
+    lib().gdpt_rtc_standin_stats(out, 1 if reset else 0)
+    return int(out[0]), int(out[1])
+
+
+def tsc():
+    return int(lib().gdpt_rtc_standin_tsc())
 
 
 def make_variant(xml_path, out_dir=None, **subs):
