@@ -65,7 +65,8 @@ EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_create_e
            "gdpt_render_accumulate_device", "gdpt_merge_device", "gdpt_poisson", "gdpt_poisson_device", "gdpt_get_stats",
            "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill",
            "gdpt_render_path", "gdpt_render_path_accumulate_device", "gdpt_path_samples", "gdpt_sample_light", "gdpt_occluded", "gdpt_render_aux",
-           "gdpt_merge_rows_device", "gdpt_poisson_dist_rows_forward", "gdpt_poisson_dist_columns", "gdpt_poisson_dist_rows_inverse"]
+           "gdpt_merge_rows_device", "gdpt_poisson_dist_rows_forward", "gdpt_poisson_dist_columns", "gdpt_poisson_dist_rows_inverse",
+           "gdpt_poisson_device_noalloc"]
 
 _lib = None
 
@@ -90,6 +91,7 @@ def lib():
         L.gdpt_merge_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
         L.gdpt_poisson.argtypes = [C.c_int, C.c_int, C.c_int, dp, dp, dp, C.c_double, dp]
         L.gdpt_poisson_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_double, vp]
+        L.gdpt_poisson_device_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_double, vp, vp]
         L.gdpt_merge_rows_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp, vp]
         L.gdpt_poisson_dist_rows_forward.argtypes = [vp, C.POINTER(GdptDistGeom), vp, vp, vp, C.c_double, vp, vp]
         L.gdpt_poisson_dist_columns.argtypes = [vp, C.POINTER(GdptDistGeom), C.c_double, vp, vp, vp]

@@ -137,6 +137,17 @@ int gdpt_merge_device(gdpt_ctx *ctx, int w, int h, const double *d_cx0, const do
 /* fourierSolve (render.cpp:172-254): host buffers / device buffers.  `device` selects the GPU for the host form. */
 int gdpt_poisson(int device, int w, int h, const double *u, const double *gx, const double *gy, double alpha, double *out);
 int gdpt_poisson_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  gdpt_poisson_device with every work
+ * buffer in a fixed file-scope __device__ array (4.03 MiB, held by every GPU that loads the library until exit): the call
+ * makes no cudaMalloc / cudaFree and needs no context.  Device pointers in and out (W*H*3 doubles each), launched on
+ * `cuda_stream` (a cudaStream_t; NULL = the legacy default stream), asynchronous.  Images larger than
+ * GDPT_NOALLOC_MAX_DIM in either dimension are refused with GDPT_ERR_ARG.  All calls share the array: calls that overlap on
+ * the GPU race — serialise them.  The first call on a device resolves the array's address (cudaGetSymbolAddress); make it
+ * outside graph capture. */
+#define GDPT_NOALLOC_MAX_DIM 256
+int gdpt_poisson_device_noalloc(int device, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha,
+                                double *d_out, void *cuda_stream);
 
 /* ---- distributed screened-Poisson solve (BASELINE configs[4]: 3840x2160 on 8 GPUs) ----
  * fourierSolve (render.cpp:172-254) over the ranks of one box.  Rank r owns the row band [y0,y1) of the
