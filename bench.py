@@ -344,9 +344,26 @@ def run_native(args):
         cnt = np.zeros(3)
         check(lib.gdpt_traversal_counts(R.ctx, C.byref(p), _capi.as_dp(cnt)))
         bytes_per_ray = 32 + 20 + 128.0 * cnt[0] + 48.0 * cnt[1]
-        rays = s1["rays_traced"] - s0["rays_traced"]
-        ms_trace = s1["ms_trace"] - s0["ms_trace"]
-        ms_shade = s1["ms_shade"] - s0["ms_shade"]
+        # kernel durations: a separate pass of the same workload at fewer spp with the host-synchronised wave loop and CUDA events
+        # around every k_trace / shade launch on the launching stream (in the timed region above two waves overlap on two
+        # streams without read-backs, where per-launch events would time the neighbour's kernels too)
+        check(lib.gdpt_set_option(R.ctx, b"time_kernels", 1))
+        roof_spp = min(spp, 32)
+        R.render(2, precision=args.precision, offsets=args.offsets)
+        barrier()
+        r0 = stats()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        R.render(roof_spp, precision=args.precision, offsets=args.offsets)
+        g1.record()
+        barrier()
+        r1 = stats()
+        check(lib.gdpt_set_option(R.ctx, b"time_kernels", 0))
+        ms_pass = g0.elapsed_time(g1)
+        rays = r1["rays_traced"] - r0["rays_traced"]
+        ms_trace = r1["ms_trace"] - r0["ms_trace"]
+        ms_shade = r1["ms_shade"] - r0["ms_shade"]
+        rays_step = (s1["rays_traced"] - s0["rays_traced"]) / args.steps
         achieved = rays * bytes_per_ray / (ms_trace * 1e-3) / 1e9 if ms_trace > 0 else None
         l2 = np.zeros(1)
         try:
@@ -376,7 +393,10 @@ def run_native(args):
                           if nb else None),
                 "note": "algorithmic bytes = 32 B ray + 20 B hit + node bytes x nodes + 48 B x primitives per ray (counting pass of this run), served by L1/L2: "
                         "the binding limits are L2/L1 bandwidth-latency and issue slots under divergence (DESIGN.md 4.1)",
-                "share_of_step": {"k_trace": ms_trace / (ms_step * args.steps), "shade_kernels": ms_shade / (ms_step * args.steps)},
+                "kernel_timing_pass": {"spp": roof_spp, "ms": ms_pass, "ms_k_trace": ms_trace, "ms_shade_kernels": ms_shade, "rays": rays,
+                                       "how": "host-synchronised wave loop, CUDA events around every launch on the launching stream"},
+                "share_of_step": {"k_trace": ms_trace / ms_pass, "shade_kernels": ms_shade / ms_pass},
+                "rays_per_step": rays_step,
                 "mrays_per_s": rays / (ms_trace * 1e-3) / 1e6 if ms_trace > 0 else None}
         line = {"metric": metric_name(w, h), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,

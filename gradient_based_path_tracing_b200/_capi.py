@@ -66,7 +66,7 @@ EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_create_e
            "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill",
            "gdpt_render_path", "gdpt_render_path_accumulate_device", "gdpt_path_samples", "gdpt_sample_light", "gdpt_occluded", "gdpt_render_aux",
            "gdpt_merge_rows_device", "gdpt_poisson_dist_rows_forward", "gdpt_poisson_dist_columns", "gdpt_poisson_dist_rows_inverse",
-           "gdpt_poisson_device_noalloc"]
+           "gdpt_poisson_device_noalloc", "gdpt_set_option"]
 
 _lib = None
 
@@ -98,6 +98,7 @@ def lib():
         L.gdpt_poisson_dist_rows_inverse.argtypes = [vp, C.POINTER(GdptDistGeom), vp, vp]
         L.gdpt_get_stats.argtypes = [vp, C.POINTER(GdptStats)]
         L.gdpt_synchronize.argtypes = [vp]
+        L.gdpt_set_option.argtypes = [vp, C.c_char_p, C.c_int]
         L.gdpt_set_stream.argtypes = [vp, vp]
         L.gdpt_traversal_counts.argtypes = [vp, C.POINTER(GdptRenderParams), dp]
         L.gdpt_measure_l2_read.argtypes = [C.c_int, C.c_int, C.c_int, dp]

@@ -84,6 +84,7 @@ int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, dou
     wp.img = d_img; wp.cx0 = d_cx0; wp.cy0 = d_cy0; wp.cx1 = d_cx1; wp.cy1 = d_cy1;
     long long target = 4LL << 20;     // ~4M paths in flight per wave
     int k = r.wave > 0 ? r.wave : (int)std::max<long long>(1, target / wp.npix_pad);
+    if (int rc = join_wave_streams(c)) return rc;      // (a failed earlier call may have left the second wave stream forked)
     for (int s0 = 0; s0 < r.spp; s0 += k) {
         int kk = std::min(k, r.spp - s0);
         wp.sample0 = r.sample0 + s0; wp.n_samples = kk;
@@ -92,7 +93,7 @@ int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, dou
         wp.n_paths = (int)n;
         if (int rc = PATH ? run_path_wave<R>(c, sc, wp) : r.offset_mode == GDPT_OFFSETS_SHIFT ? run_shift_wave<R>(c, sc, wp) : run_wave<R>(c, sc, wp)) return rc;
     }
-    return 0;
+    return join_wave_streams(c);
 }
 
 int path_supported(gdpt_ctx *c) {
@@ -244,7 +245,31 @@ int gdpt_measure_l2_read(int device, int mbytes, int iters, double *gbs) {
 
 int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out) {
     if (!ctx || !out) return fail(GDPT_ERR_ARG, "null argument");
+    // rays of launches whose size was only known on the device (waves launched without host read-backs)
+    GD_CUDA(cudaSetDevice(ctx->device));
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    unsigned long long dev_rays = 0;
+    GD_CUDA(cudaMemcpy(&dev_rays, ctx->dev_stats.p, 8, cudaMemcpyDeviceToHost));
+    GD_CUDA(cudaMemset(ctx->dev_stats.p, 0, 8));
+    ctx->stats.rays_traced += (long long)dev_rays;
     *out = ctx->stats; return 0;
+}
+
+int gdpt_set_option(gdpt_ctx *ctx, const char *name, int value) {
+    if (!ctx || !name) return fail(GDPT_ERR_ARG, "null argument");
+    const std::string n(name);
+    GD_CUDA(cudaSetDevice(ctx->device));
+    GD_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (n == "async_waves") ctx->async_waves = value != 0;
+    else if (n == "wave_streams") ctx->wave_streams = std::min((int)gdpt_ctx::MAX_SLOTS, std::max(1, value));
+    else if (n == "time_kernels") ctx->time_kernels = value != 0;
+    else if (n == "tail_paths") ctx->tail_paths = value;
+    else if (n == "sort_rays") ctx->sort_rays = value != 0;
+    else if (n == "trace_variant") ctx->trace_variant = value;
+    else if (n == "shade_variant") ctx->shade_variant = value;
+    else return fail(GDPT_ERR_ARG, "unknown option '%s'", name);
+    ctx->cal.valid = false;
+    return 0;
 }
 
 int gdpt_render_accumulate_device(gdpt_ctx *ctx, const gdpt_render_params *params, double *d_img, double *d_cx0, double *d_cy0,

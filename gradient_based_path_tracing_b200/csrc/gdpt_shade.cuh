@@ -179,19 +179,22 @@ template <typename R, int MS, int MINB = 1>
 __global__ void __launch_bounds__(128, MINB) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
                                                 const HitRec *hits, const int *in_count, int in_max,
                                                 PathRec<R> *out, RayF *rays_out, int *out_count) {
-    int n = min(*in_count, in_max);
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    bool alive = false;
-    PathRec<R> pr; RayF ray;
-    if (i < n) {
-        load_soa(pr, in, i, wp.n_paths);
-        const bool first = off_in != nullptr;          // iteration with num_vertices == 3
-        OffRec<R> off; if (first) load_soa(off, off_in, i, wp.n_paths);
-        Hit h = load_hit(hits + i);
-        alive = bounce_step<R, MS>(sc, wp, pr, first ? &off : nullptr, h, ray);
+    const int n = min(*in_count, in_max);
+    // grid-stride over whole warps: the launch may be sized by an estimate of n (no host read-back of the count)
+    for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+        const int i = base + threadIdx.x;
+        bool alive = false;
+        PathRec<R> pr; RayF ray;
+        if (i < n) {
+            load_soa(pr, in, i, wp.n_paths);
+            const bool first = off_in != nullptr;          // iteration with num_vertices == 3
+            OffRec<R> off; if (first) load_soa(off, off_in, i, wp.n_paths);
+            Hit h = load_hit(hits + i);
+            alive = bounce_step<R, MS>(sc, wp, pr, first ? &off : nullptr, h, ray);
+        }
+        int slot = warp_slot(alive, out_count);
+        if (alive) { store_soa(out, slot, wp.n_paths, pr); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
     }
-    int slot = warp_slot(alive, out_count);
-    if (alive) { store_soa(out, slot, wp.n_paths, pr); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
 }
 
 // ---------------------------------------------------------------- tail
@@ -200,10 +203,10 @@ __global__ void __launch_bounds__(128, MINB) k_bounce(DScene<R> sc, WaveParams w
 // in one launch — trace and shade in the same thread, no queues.
 template <typename R, int MS, bool EXACT>
 __global__ void __launch_bounds__(TRACE_BLOCK) k_tail(DScene<R> sc, WaveParams wp, DBvh bvh, const PathRec<R> *in, const OffRec<R> *off_in,
-                                                      const RayF *rays, int n) {
+                                                      const RayF *rays, int n, const int *n_ptr = nullptr) {
     __shared__ int2 stack[STACK_SMEM * TRACE_BLOCK];
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (n_ptr) n = min(n, *n_ptr);                      // live count on the device; n is then only an upper bound
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     PathRec<R> pr; RayF ray;
     load_soa(pr, in, i, wp.n_paths); load_rec(ray, rays + i);
     bool first = off_in != nullptr;
@@ -217,6 +220,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_tail(DScene<R> sc, WaveParams w
         bool alive = bounce_step<R, MS>(sc, wp, pr, first ? &off : nullptr, h, ray);
         first = false;
         if (!alive) break;
+    }
     }
 }
 

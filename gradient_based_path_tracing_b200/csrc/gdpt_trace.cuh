@@ -106,6 +106,7 @@ GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3],
 }
 
 constexpr int TRACE_DONE = (int)0x80000000;   // "no more work for this ray" (never a valid leaf encoding)
+constexpr int TRACE_POP = (int)0x80000001;    // "take the next stack entry" (loop form with one shared pop site; never a valid leaf encoding either)
 
 // Per-ray traversal state kept in registers.
 struct RayState {
@@ -134,7 +135,7 @@ GD_D int trace_pop(const ST &st, int &sp, float best) {
 }
 
 // Inner node: slab-test the 4 children, descend into the nearest, push the rest far-to-near.
-template <int SORT = 0, int FMA = 0, typename ST>
+template <int SORT = 0, int FMA = 0, bool NOPOP = false, typename ST>
 GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, ST &st, int &sp) {
     const float4 *n = bvh.nodes + 8 * (size_t)cur;
     const float INF = __int_as_float(0x7f800000);
@@ -191,6 +192,7 @@ GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, ST &st, int &sp
     if (dist[2] < INF) st.put(sp++, cid[2], dist[2]);
     if (dist[1] < INF) st.put(sp++, cid[1], dist[1]);
     if (dist[0] < INF) return cid[0];
+    if (NOPOP) return TRACE_POP;
     return trace_pop(st, sp, r.best);
 }
 

@@ -139,9 +139,12 @@ static __global__ void __launch_bounds__(1024) k_sort_chunks(int *chunk_sum, int
     __syncthreads();
     if (threadIdx.x < n_chunks) chunk_sum[threadIdx.x] = warp_sum[wid] + incl - t;
 }
-static __global__ void __launch_bounds__(256) k_sort_scatter(const int *keys, int *offsets, const int *chunk_off, int n, int *order) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) { int k = keys[i]; order[atomicAdd(offsets + k, 1) + __ldg(chunk_off + k / SORT_CHUNK)] = i; }
+// n_ptr (optional): the live count on the device, for launches sized by an upper bound (no host read-back)
+static __global__ void __launch_bounds__(256) k_sort_scatter(const int *keys, int *offsets, const int *chunk_off, int n, int *order, const int *n_ptr = nullptr) {
+    if (n_ptr) n = min(n, *n_ptr);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int k = keys[i]; order[atomicAdd(offsets + k, 1) + __ldg(chunk_off + k / SORT_CHUNK)] = i;
+    }
 }
 
 // Records move between registers and HBM as 16-byte vectors (the compiler's own struct copy
@@ -240,7 +243,8 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 //        selected by the ray octant at load time (6 instead of 12 min/max per child)
 //   STACKSEL 0: 20, 1: 16, 2: 12, 3: 8 shared-memory stack entries per thread (rest spills)
 //   OCC  0: launch bound 8 blocks/SM (64 regs), 1: 7 (72), 2: 9 (56), 3: 10 (48)
-//   LOOP (x10000) bit 0: a node step that lands on a leaf tests it in the same trip; bit 1: triangle test without early exits
+//   LOOP (x10000) bit 0: a node step that lands on a leaf tests it in the same trip; bit 1: triangle test without early exits;
+//        bit 2: one pop site per trip (node misses and finished leaves pop together at the top of the next trip)
 // COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
 // (bench.py derives the algorithmic bytes per ray from them; never in timed runs).
 constexpr int trace_variant_depth(int v) { return ((v / 100) % 10) == 0 ? 20 : ((v / 100) % 10) == 1 ? 16 : ((v / 100) % 10) == 2 ? 12 : 8; }
@@ -249,10 +253,12 @@ constexpr int trace_variant_blocks(int v) { return ((v / 1000) % 10) == 0 ? 8 : 
 // ANY: occlusion query (rtcOccluded1, intersection.cpp:66-85): the walk stops at the first accepted hit.
 template <bool EXACT, bool COUNT, int V, bool ANY = false>
 __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(DBvh bvh, const RayF *rays, HitRec *hits, const int *order, int count_max,
-                                                                               unsigned long long *counters) {
+                                                                               unsigned long long *counters, const int *count_ptr = nullptr,
+                                                                               unsigned long long *rays_total = nullptr) {
     constexpr int SORT = V % 10, FMA = (V / 10) % 10, DEPTH = trace_variant_depth(V), LOOP = V / 10000;
     __shared__ int2 stack[DEPTH * TRACE_BLOCK];
-    const int n = count_max;
+    const int n = count_ptr ? min(*count_ptr, count_max) : count_max;   // count_ptr: live count on the device (launch sized by an upper bound)
+    if (rays_total && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(rays_total, (unsigned long long)n);
     TraceStackT<DEPTH> st; st.smem = stack;
     unsigned long long tn = 0, tp = 0;
     for (int j = blockIdx.x * TRACE_BLOCK + threadIdx.x; j < n; j += gridDim.x * TRACE_BLOCK) {
@@ -263,6 +269,19 @@ __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(
         unsigned cn = 0, cp = 0;
         if (!(b.w < a.w) && bvh.n_nodes != 0) {   // tfar < tnear: never hits
             int sp = 0, cur = 0;
+            if (LOOP & 4) {   // one pop site at the top of the trip, shared by the lanes coming from a node miss and from a leaf
+                while (true) {
+                    if (cur == TRACE_POP) { cur = trace_pop(st, sp, r.best); if (cur == TRACE_DONE) break; }
+                    if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA, true>(bvh, cur, r, st, sp); }
+                    else {
+                        int enc = ~cur, first = enc >> 3, cnt = enc & 7;
+                        if (COUNT) cp += cnt;
+                        for (int q = 0; q < cnt; q++) test_prim<EXACT, false>(bvh, first + q, r.o, r.d, r.tnear, r.best, r.hit);
+                        if (ANY && r.hit.shape_id >= 0) break;
+                        cur = TRACE_POP;
+                    }
+                }
+            } else
             while (cur != TRACE_DONE) {
                 if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA>(bvh, cur, r, st, sp); if ((LOOP & 1) == 0) continue; }
                 if (cur < 0 && cur != TRACE_DONE) cur = trace_leaf<EXACT, (LOOP & 2) != 0>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);

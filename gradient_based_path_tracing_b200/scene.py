@@ -67,7 +67,10 @@ def write_container(path, arrays):
 
 # camera/options-only containers and the full container they sit on
 OVERLAY_BASE = {"sponza_2160p": "sponza_1080p", "sponza_native": "sponza_1080p", "sponza_small": "sponza_1080p",
-                "disney_small": "disney_gradpath"}
+                "disney_small": "disney_gradpath",
+                # pixel-filter variants of the 64x64 Cornell box: Box(width 2), Tent(width 2), Gaussian(stddev 2) — the three
+                # filters of src/tests/filter.cpp:15-66
+                "cbox_gdpt_64_box": "cbox_gdpt_64", "cbox_gdpt_64_tent": "cbox_gdpt_64", "cbox_gdpt_64_gauss2": "cbox_gdpt_64"}
 
 
 class RenderOptions:
@@ -202,6 +205,10 @@ class Scene:
 
     def adopt_bvh(self, nodes_ptr, n_nodes, prims_ptr, n_prims, depth, device=0):
         _capi.check(_capi.lib().gdpt_bvh_adopt(self._ctx[device], C.c_void_p(nodes_ptr), n_nodes, C.c_void_p(prims_ptr), n_prims, depth))
+
+    def set_option(self, name, value, device=0):
+        """gdpt_set_option: scheduling / tuning knobs of the context ("async_waves", "wave_streams", "time_kernels", ...)."""
+        _capi.check(_capi.lib().gdpt_set_option(self.context(device), name.encode(), int(value)))
 
     def close(self):
         for h in self._ctx.values():

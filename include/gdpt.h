@@ -180,6 +180,12 @@ int gdpt_poisson_dist_columns(gdpt_ctx *ctx, const gdpt_dist_geom *geom, double 
 int gdpt_poisson_dist_rows_inverse(gdpt_ctx *ctx, const gdpt_dist_geom *geom, const double *d_recv_back, double *d_out);
 
 int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out);
+/* Scheduling / tuning knobs of a context (no effect on results; no counterpart in the reference, whose only knob is -t threads,
+ * src/main.cpp:20-23).  "async_waves" 1|0: launch the waves of a render from the first wave's measured path counts without
+ * per-bounce host read-backs (default 1); "wave_streams" 1..4: waves in flight on separate streams (default 2); "time_kernels"
+ * 1|0: keep the host-synchronised loop and fill gdpt_stats.ms_trace / ms_shade with per-kernel event times (default 0: those two
+ * fields stay 0); "tail_paths" n; "sort_rays" 1|0; "trace_variant" v; "shade_variant" v. */
+int gdpt_set_option(gdpt_ctx *ctx, const char *name, int value);
 /* Run all of the context's work on the caller's CUDA stream (a cudaStream_t; NULL restores the context's own). */
 int gdpt_set_stream(gdpt_ctx *ctx, void *cuda_stream);
 /* Measurement aid: render `spp` samples with a counting traversal and return the mean number of BVH nodes

@@ -136,6 +136,11 @@ def make_variant(xml_path, out_dir=None, **subs):
     for key, name in (("width", "width"), ("height", "height"), ("spp", "sampleCount")):
         if key in subs:
             txt = re.sub(r'(name="%s"\s+value=")[^"]*"' % name, r'\g<1>%d"' % subs[key], txt)
+    if "rfilter" in subs:      # (type, parameter name, value): replaces the film's reconstruction filter (parse_scene.cpp:620-650)
+        t, n, v = subs["rfilter"]
+        txt, k = re.subn(r'<rfilter\s+type="[^"]*"\s*/>', '<rfilter type="%s"><float name="%s" value="%s"/></rfilter>' % (t, n, v), txt, count=1)
+        if k != 1:
+            raise RuntimeError("no <rfilter .../> to replace in " + xml_path)
     if subs.get("extra_xml"):
         txt = txt.replace("</scene>", subs["extra_xml"] + "\n</scene>")
     out = os.path.join(out_dir, subs.get("name", "variant") + ".xml")
@@ -316,6 +321,9 @@ VARIANTS = {
     "sponza_2160p": ("sponza", "sponza.xml", dict(integrator="gradpath", width=3840, height=2160, spp=1024)),
     "sponza_native": ("sponza", "sponza.xml", dict(integrator="gradpath")),
     "sponza_small": ("sponza", "sponza.xml", dict(integrator="gradpath", width=160, height=90, spp=4)),
+    "cbox_gdpt_64_box": ("cbox", "cbox_gdpt.xml", dict(width=64, height=64, rfilter=("box", "width", "2"))),
+    "cbox_gdpt_64_tent": ("cbox", "cbox_gdpt.xml", dict(width=64, height=64, rfilter=("tent", "width", "2"))),
+    "cbox_gdpt_64_gauss2": ("cbox", "cbox_gdpt.xml", dict(width=64, height=64, rfilter=("gaussian", "stddev", "2"))),
 }
 
 
