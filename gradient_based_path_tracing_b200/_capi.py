@@ -13,6 +13,8 @@ PRECISION_F32 = 1
 OFFSETS_REFERENCE = 0
 OFFSETS_SHIFT = 1
 CREATE_NO_BVH = 1
+CREATE_BVH_HOST = 2
+CREATE_BVH_DEVICE = 4
 DEFAULT_SEED = 0x31E241F862A1FB5E
 
 dp = C.POINTER(C.c_double)
@@ -42,7 +44,8 @@ class GdptSceneDesc(C.Structure):
 class GdptRenderParams(C.Structure):
     _fields_ = [("spp", C.c_int32), ("sample0", C.c_int32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32),
                 ("seed", C.c_uint64), ("data_cost", C.c_double), ("precision", C.c_int32),
-                ("y0", C.c_int32), ("y1", C.c_int32), ("wave_samples", C.c_int32), ("offset_mode", C.c_int32)]
+                ("y0", C.c_int32), ("y1", C.c_int32), ("wave_samples", C.c_int32), ("offset_mode", C.c_int32),
+                ("strip_count", C.c_int32), ("strip_phase", C.c_int32)]
 
 
 class GdptImages(C.Structure):
@@ -66,7 +69,8 @@ EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_create_e
            "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill",
            "gdpt_render_path", "gdpt_render_path_accumulate_device", "gdpt_path_samples", "gdpt_sample_light", "gdpt_occluded", "gdpt_render_aux",
            "gdpt_merge_rows_device", "gdpt_poisson_dist_rows_forward", "gdpt_poisson_dist_columns", "gdpt_poisson_dist_rows_inverse",
-           "gdpt_poisson_device_noalloc", "gdpt_set_option"]
+           "gdpt_poisson_device_noalloc", "gdpt_set_option", "gdpt_host_alloc", "gdpt_host_free",
+           "gdpt_multi_create", "gdpt_multi_render", "gdpt_multi_get_stats", "gdpt_multi_device_count", "gdpt_multi_destroy"]
 
 _lib = None
 
@@ -99,6 +103,15 @@ def lib():
         L.gdpt_get_stats.argtypes = [vp, C.POINTER(GdptStats)]
         L.gdpt_synchronize.argtypes = [vp]
         L.gdpt_set_option.argtypes = [vp, C.c_char_p, C.c_int]
+        L.gdpt_multi_create.argtypes = [C.POINTER(GdptSceneDesc), C.c_int, ip, C.POINTER(vp)]
+        L.gdpt_multi_render.argtypes = [vp, C.POINTER(GdptRenderParams), C.POINTER(GdptImages)]
+        L.gdpt_multi_get_stats.argtypes = [vp, C.POINTER(GdptStats)]
+        L.gdpt_multi_device_count.argtypes = [vp]
+        L.gdpt_multi_destroy.argtypes = [vp]
+        L.gdpt_multi_destroy.restype = None
+        L.gdpt_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+        L.gdpt_host_free.argtypes = [vp]
+        L.gdpt_host_free.restype = None
         L.gdpt_set_stream.argtypes = [vp, vp]
         L.gdpt_traversal_counts.argtypes = [vp, C.POINTER(GdptRenderParams), dp]
         L.gdpt_measure_l2_read.argtypes = [C.c_int, C.c_int, C.c_int, dp]
@@ -133,3 +146,31 @@ def as_dp(a):
 def f64(a, shape=None):
     a = np.ascontiguousarray(a, dtype=np.float64)
     return a.reshape(shape) if shape is not None else a
+
+
+# ---- page-locked host arrays for image outputs (gdpt_host_alloc), recycled through a small pool: pinning 50 MB costs more
+# than the copy it speeds up, so blocks go back to the pool when the array that wraps them is collected
+_pinned_free = {}
+
+
+def _pinned_return(ptr, nbytes):
+    _pinned_free.setdefault(nbytes, []).append(ptr)
+
+
+def pinned_empty(shape, dtype=np.float64):
+    """An uninitialised page-locked numpy array; falls back to a pageable one when no device is usable."""
+    import weakref
+    shape = tuple(int(v) for v in shape)
+    nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    free = _pinned_free.get(nbytes)
+    if free:
+        ptr = free.pop()
+    else:
+        h = C.c_void_p()
+        if nbytes == 0 or lib().gdpt_host_alloc(nbytes, C.byref(h)) != 0 or not h.value:
+            return np.empty(shape, dtype=dtype)
+        ptr = h.value
+    buf = (C.c_char * nbytes).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+    weakref.finalize(buf, _pinned_return, ptr, nbytes)
+    return arr

@@ -45,7 +45,7 @@ using namespace gdpt;
 
 namespace {
 
-struct Resolved { int spp, sample0, y0, y1, precision, wave; unsigned long long seed; double alpha; int max_depth, rr_depth, offset_mode; };
+struct Resolved { int strip_count, strip_phase; int spp, sample0, y0, y1, precision, wave; unsigned long long seed; double alpha; int max_depth, rr_depth, offset_mode; };
 
 int resolve(gdpt_ctx *c, const gdpt_render_params *p, Resolved &r) {
     if (!c || !p) return fail(GDPT_ERR_ARG, "null argument");
@@ -61,6 +61,8 @@ int resolve(gdpt_ctx *c, const gdpt_render_params *p, Resolved &r) {
     r.max_depth = p->max_depth == -2 ? c->max_depth : p->max_depth;
     r.rr_depth = p->rr_depth == -2 ? c->rr_depth : p->rr_depth;
     r.wave = p->wave_samples;
+    r.strip_count = p->strip_count > 1 ? p->strip_count : 1; r.strip_phase = p->strip_count > 1 ? p->strip_phase : 0;
+    if (r.strip_phase < 0 || r.strip_phase >= r.strip_count) return fail(GDPT_ERR_ARG, "strip_phase %d outside [0, %d)", r.strip_phase, r.strip_count);
     r.offset_mode = p->offset_mode;
     if (r.offset_mode != GDPT_OFFSETS_REFERENCE && r.offset_mode != GDPT_OFFSETS_SHIFT) return fail(GDPT_ERR_ARG, "unknown offset mode %d", r.offset_mode);
     return 0;
@@ -78,7 +80,10 @@ int accumulate(gdpt_ctx *c, const Resolved &r, double *d_img, double *d_cx0, dou
     WaveParams wp; memset(&wp, 0, sizeof(wp));
     wp.width = c->width; wp.height = c->height; wp.y0 = r.y0; wp.y1 = r.y1;
     wp.tiles_x = (c->width + 7) / 8;
-    int tiles_y = (r.y1 - r.y0 + 3) / 4;
+    int tiles_y = (r.y1 - r.y0 + 3) / 4;            // 4-row strips of the band ...
+    wp.strip_count = r.strip_count; wp.strip_phase = r.strip_phase;
+    if (r.strip_count > 1) tiles_y = tiles_y > r.strip_phase ? (tiles_y - r.strip_phase + r.strip_count - 1) / r.strip_count : 0;   // ... of which this call owns every strip_count-th
+    if (tiles_y == 0) return 0;
     wp.npix_pad = (long long)wp.tiles_x * tiles_y * 32;
     wp.spp_total = r.spp; wp.seed = r.seed;
     wp.img = d_img; wp.cx0 = d_cx0; wp.cy0 = d_cy0; wp.cx1 = d_cx1; wp.cy1 = d_cy1;
@@ -118,7 +123,8 @@ int gdpt_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSucce
 
 int gdpt_create_ex(const gdpt_scene_desc *scene, int device, int flags, gdpt_ctx **out) {
     if (out) *out = nullptr;
-    if (flags & ~GDPT_CREATE_NO_BVH) return fail(GDPT_ERR_ARG, "unknown creation flags %d", flags);
+    if (flags & ~(GDPT_CREATE_NO_BVH | GDPT_CREATE_BVH_HOST | GDPT_CREATE_BVH_DEVICE)) return fail(GDPT_ERR_ARG, "unknown creation flags %d", flags);
+    if ((flags & GDPT_CREATE_BVH_HOST) && (flags & GDPT_CREATE_BVH_DEVICE)) return fail(GDPT_ERR_ARG, "GDPT_CREATE_BVH_HOST and GDPT_CREATE_BVH_DEVICE exclude each other");
     gdpt_ctx *c = nullptr;
     int r = create_context(scene, device, flags, &c);
     if (r != 0) { destroy_context(c); return r; }
@@ -157,6 +163,15 @@ int gdpt_bvh_adopt(gdpt_ctx *ctx, const void *d_nodes, int64_t n_nodes, const vo
 }
 
 void gdpt_destroy(gdpt_ctx *ctx) { destroy_context(ctx); }
+
+int gdpt_host_alloc(size_t bytes, void **out) {
+    if (!out || bytes == 0) return fail(GDPT_ERR_ARG, "bad argument");
+    *out = nullptr;
+    GD_CUDA(cudaMallocHost(out, bytes));
+    return 0;
+}
+
+void gdpt_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 int gdpt_scene_bounds(gdpt_ctx *ctx, double *rc) {
     if (!ctx || !rc) return fail(GDPT_ERR_ARG, "null argument");
@@ -264,6 +279,7 @@ int gdpt_set_option(gdpt_ctx *ctx, const char *name, int value) {
     else if (n == "wave_streams") ctx->wave_streams = std::min((int)gdpt_ctx::MAX_SLOTS, std::max(1, value));
     else if (n == "time_kernels") ctx->time_kernels = value != 0;
     else if (n == "tail_paths") ctx->tail_paths = value;
+    else if (n == "poisson_fft") ctx->poisson_fft = value != 0;
     else if (n == "sort_rays") ctx->sort_rays = value != 0;
     else if (n == "trace_variant") ctx->trace_variant = value;
     else if (n == "shade_variant") ctx->shade_variant = value;

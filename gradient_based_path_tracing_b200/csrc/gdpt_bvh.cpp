@@ -205,7 +205,7 @@ inline void presplit(std::vector<Ref> &refs, const std::vector<BvhPrim> &src, si
 // The heap above is sequential; the references are therefore cut into a FIXED number of chunks (independent of the thread
 // count, so the tree is deterministic), each chunk gets the share of the extra references that its share of the total box area
 // calls for — the global rule "always split the largest box" ends with every box below one common area, i.e. with a piece
-// count proportional to area — and the chunks run side by side.  Sponza: 62 ms -> 7 ms on 16 host threads.
+// count proportional to area — and the chunks run side by side.  Sponza: 62 ms -> under 10 ms on 16 host threads.
 inline void presplit_parallel(std::vector<Ref> &refs, const std::vector<BvhPrim> &src, size_t budget) {
     constexpr int CHUNKS = 16;
     const size_t n = refs.size();
@@ -213,8 +213,10 @@ inline void presplit_parallel(std::vector<Ref> &refs, const std::vector<BvhPrim>
     std::vector<std::vector<Ref>> part(CHUNKS);
     double area[CHUNKS], total = 0;
     for (int c = 0; c < CHUNKS; c++) {
-        const size_t a = n * c / CHUNKS, b = n * (c + 1) / CHUNKS;
-        part[c].assign(refs.begin() + a, refs.begin() + b);
+        // dealt out round-robin: a mesh's large triangles (walls, floors) sit next to each other in the index order, and a
+        // contiguous cut would leave one chunk with most of the area, i.e. most of the splits
+        part[c].reserve(n / CHUNKS + 1);
+        for (size_t i = c; i < n; i += CHUNKS) part[c].push_back(refs[i]);
         area[c] = 0;
         for (const Ref &r : part[c]) if (src[r.idx].kind == 0) area[c] += r.b.area();
         total += area[c];
@@ -319,19 +321,17 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
     out.prims.resize(B.refs.size());
     for (size_t i = 0; i < B.refs.size(); i++) out.prims[i] = src[B.refs[i].idx];
 
-    // collapse to 4-wide
+    // collapse to 4-wide: a child is opened as long as fewer than four are held, largest surface area first.  The top of the
+    // tree is collapsed serially until enough independent subtrees are open, the subtrees then side by side into private
+    // node arrays that are appended in subtree order (so the result does not depend on the thread count).
     struct Item { int bnode; int wide; int depth; };
-    std::vector<Item> work;
-    auto new_wide = [&]() { BvhNode n; for (int c = 0; c < 4; c++) {
+    auto blank = []() { BvhNode n; for (int c = 0; c < 4; c++) {
             n.lox[c] = n.loy[c] = n.loz[c] = std::numeric_limits<float>::infinity();
             n.hix[c] = n.hiy[c] = n.hiz[c] = -std::numeric_limits<float>::infinity();
             n.child[c] = 0; n.count[c] = 0; }
-        out.nodes.push_back(n); return (int)out.nodes.size() - 1; };
-    int root = new_wide();
-    work.push_back({0, root, 1});
-    while (!work.empty()) {
-        Item it = work.back(); work.pop_back();
-        out.max_depth = std::max(out.max_depth, it.depth);
+        return n; };
+    // one collapse step of `it` inside `nodes`; children that are inner nodes are appended to `nodes` and to `work`
+    auto expand = [&](const Item &it, std::vector<BvhNode> &nodes, std::vector<Item> &work) {
         int kids[4]; int nk = 0;
         const BNode &bn = B.nodes[it.bnode];
         if (bn.left < 0) { kids[nk++] = it.bnode; }
@@ -340,7 +340,7 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
             int pick = -1; double pa = -1;
             for (int i = 0; i < nk; i++) {
                 const BNode &k = B.nodes[kids[i]];
-                if (k.left >= 0 && k.b.area() > pa) { pa = k.b.area(); pick = i; }
+                if (k.left >= 0) { double ar = k.b.area(); if (ar > pa) { pa = ar; pick = i; } }
             }
             if (pick < 0) break;
             int k = kids[pick];
@@ -348,15 +348,53 @@ void build_bvh(const std::vector<HostShape> &shapes, Bvh &out) {
         }
         for (int i = 0; i < nk; i++) {
             const BNode &k = B.nodes[kids[i]];
-            BvhNode &w = out.nodes[it.wide];
+            BvhNode &w = nodes[it.wide];
             w.lox[i] = k.b.lo[0]; w.loy[i] = k.b.lo[1]; w.loz[i] = k.b.lo[2];
             w.hix[i] = k.b.hi[0]; w.hiy[i] = k.b.hi[1]; w.hiz[i] = k.b.hi[2];
             if (k.left < 0) { w.child[i] = ~((k.first << 3) | k.count); w.count[i] = k.count; }
             else {
-                int c = new_wide();
-                out.nodes[it.wide].child[i] = c; out.nodes[it.wide].count[i] = 0;
+                nodes.push_back(blank());
+                const int c = (int)nodes.size() - 1;
+                nodes[it.wide].child[i] = c; nodes[it.wide].count[i] = 0;
                 work.push_back({kids[i], c, it.depth + 1});
             }
+        }
+    };
+    out.nodes.push_back(blank());
+    std::vector<Item> frontier(1, Item{0, 0, 1});
+    out.max_depth = std::max(out.max_depth, 1);
+    while (!frontier.empty() && frontier.size() < 256) {      // breadth first: the frontier items are roots of disjoint subtrees
+        std::vector<Item> next;
+        for (const Item &it : frontier) { out.max_depth = std::max(out.max_depth, it.depth); expand(it, out.nodes, next); }
+        frontier.swap(next);
+    }
+    if (!frontier.empty()) {
+        const int nitems = (int)frontier.size();
+        std::vector<std::vector<BvhNode>> sub(nitems);
+        std::vector<int> sub_depth(nitems, 0);
+        const int nthreads = std::max(1, std::min(B.max_workers + 1, nitems));
+        std::atomic<int> next_item{0};
+        auto worker = [&]() {
+            for (int q = next_item.fetch_add(1); q < nitems; q = next_item.fetch_add(1)) {
+                std::vector<BvhNode> &nodes = sub[q];
+                nodes.push_back(blank());                       // local 0 = the frontier item's own node
+                std::vector<Item> work(1, Item{frontier[q].bnode, 0, frontier[q].depth});
+                int md = 0;
+                while (!work.empty()) { Item it = work.back(); work.pop_back(); md = std::max(md, it.depth); expand(it, nodes, work); }
+                sub_depth[q] = md;
+            }
+        };
+        std::vector<std::thread> th;
+        for (int t = 1; t < nthreads; t++) th.emplace_back(worker);
+        worker();
+        for (auto &t : th) t.join();
+        // append: local node j > 0 of item q becomes global base_q + j - 1; local 0 is written over the frontier node
+        for (int q = 0; q < nitems; q++) {
+            const int base = (int)out.nodes.size();
+            auto fix = [&](BvhNode n) { for (int c = 0; c < 4; c++) if (n.child[c] > 0) n.child[c] = base + n.child[c] - 1; return n; };
+            out.nodes[frontier[q].wide] = fix(sub[q][0]);
+            for (size_t j = 1; j < sub[q].size(); j++) out.nodes.push_back(fix(sub[q][j]));
+            out.max_depth = std::max(out.max_depth, sub_depth[q]);
         }
     }
     lap("collapse to 4");

@@ -70,10 +70,16 @@ template <typename T> int upload(DevBuf &b, const std::vector<T> &v) {
     return 0;
 }
 
-struct PoissonCache {                 // DCT matrices per image size
+struct DctPlanBufs {                  // tables of the FFT form of the DCT-I for one line length (gdpt_poisson_fft.cuh)
+    int N = 0, M = 0, P = 0, logP = 0;
+    DevBuf tw, chirp, bhat, wpost;
+    void release() { tw.release(); chirp.release(); bhat.release(); wpost.release(); N = 0; }
+};
+struct PoissonCache {                 // DCT matrices / FFT plans per image size
     int w = 0, h = 0;
     DevBuf Dw, DhT, work, work2, partial, dc;
-    void release() { Dw.release(); DhT.release(); work.release(); work2.release(); partial.release(); dc.release(); w = h = 0; }
+    DctPlanBufs plan_w, plan_h;
+    void release() { Dw.release(); DhT.release(); work.release(); work2.release(); partial.release(); dc.release(); plan_w.release(); plan_h.release(); w = h = 0; }
 };
 
 } // namespace gdpt
@@ -91,7 +97,7 @@ struct WaveSlot {
 // every bounce.  Later waves of the same configuration are launched from these numbers without reading anything back.
 struct WaveCalibration {
     bool valid = false;
-    long long n_paths = 0; int max_depth = 0, rr_depth = 0, precision = -1, width = 0, y0 = 0, y1 = 0, tail_paths = 0;
+    long long n_paths = 0; int max_depth = 0, rr_depth = 0, precision = -1, width = 0, y0 = 0, y1 = 0, tail_paths = 0, strip_count = 0, strip_phase = 0;
     std::vector<int> counts;           // counts[0] after k_primary, counts[b] after bounce b
 };
 } // namespace gdpt
@@ -126,6 +132,7 @@ struct gdpt_ctx {
     cudaEvent_t ev_fork = nullptr;
     unsigned forked = 0;              // bit k: slot k's stream has work of the current accumulation in flight
     int wave_index = 0;
+    bool poisson_fft = true;          // the FFT form of the DCT-I (gdpt_poisson_fft.cuh); 0: the dense-matrix form ("poisson_fft")
     bool time_kernels = false;        // keep the host-synchronised wave loop with per-kernel event timing ("time_kernels"; bench.py's roofline pass)
     gdpt::DevBuf dev_stats;           // [0] rays traced by launches sized on the device (folded into stats.rays_traced by gdpt_get_stats)
     int *h_counts = nullptr;          // pinned
@@ -153,6 +160,8 @@ namespace gdpt {
 // Level 0 of every image is expanded, mip-mapped (make_mipmap, mipmap.h:28-44) and copied to float on the device:
 // gdpt_textures.cu.
 int build_texture_pools(gdpt_ctx *c, const gdpt_scene_desc *d, std::vector<DImage> &im3, std::vector<DImage> &im1);
+// gdpt_bvh_gpu.cu: the tree built on the device (0: done; > 0: fall back to the host builder; < 0: error)
+int build_bvh_device(gdpt_ctx *c, const std::vector<DShape> &shapes, double split_budget);
 
 // level 0 of one image on the host (only the environment map's sampling table needs it there)
 inline int decode_image(const gdpt_image &gi, int C, std::vector<double> &out) {
@@ -202,6 +211,7 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     if (int r = c->dev_stats.ensure(64)) return r;
     GD_CUDA(cudaMemset(c->dev_stats.p, 0, 64));
     if (const char *e = getenv("GDPT_ASYNC_WAVES")) c->async_waves = atoi(e) != 0;
+    if (const char *e = getenv("GDPT_POISSON_FFT")) c->poisson_fft = atoi(e) != 0;
     if (const char *e = getenv("GDPT_WAVE_STREAMS")) c->wave_streams = std::min(gdpt_ctx::MAX_SLOTS, std::max(1, atoi(e)));
 
     const bool verbose = getenv("GDPT_VERBOSE") != nullptr;
@@ -240,7 +250,16 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     // the BVH is built on its own host thread(s) while this one decodes textures and uploads the pools
     Bvh bvh;
     const bool no_bvh = (flags & GDPT_CREATE_NO_BVH) != 0;     // the tree comes from another process: only the bounds are needed here
-    std::thread bvh_thread([&] { if (no_bvh) scene_bounds(hs, bvh.lo, bvh.hi); else build_bvh(hs, bvh); });
+    // Two builders (Embree's build-quality levels, scene.cpp:22, in this library's terms): the host's binned SAH with triangle
+    // pre-splitting (gdpt_bvh.cpp: ~45 ms for Sponza, the better tree: 17.4 nodes + 2.8 primitives per ray) and the device's PLOC
+    // (gdpt_bvh_gpu.cu: ~9 ms, 18.1 nodes + 4.7 primitives per ray, 5-6 % slower rendering).  Without a flag the planned work
+    // decides: the host build pays for itself from about 2e8 pixel-samples (Sponza 1080p at ~100 spp on one GPU).
+    const char *bvh_mode = getenv("GDPT_BVH");
+    const double planned = (double)d->width * d->height * std::max(1, d->samples_per_pixel);
+    bool device_bvh = (flags & GDPT_CREATE_BVH_DEVICE) ? true : (flags & GDPT_CREATE_BVH_HOST) ? false : planned < 2e8;
+    if (bvh_mode) device_bvh = std::string(bvh_mode) != "host";
+    if (no_bvh) device_bvh = false;
+    std::thread bvh_thread([&] { if (no_bvh || device_bvh) scene_bounds(hs, bvh.lo, bvh.hi); else build_bvh(hs, bvh); });
     struct Joiner { std::thread &t; ~Joiner() { if (t.joinable()) t.join(); } } bvh_joiner{bvh_thread};
     // ---- geometry pools
     std::vector<double> pos(d->positions, d->positions + 3 * (size_t)d->n_positions), nrm(d->normals, d->normals + 3 * (size_t)d->n_normals),
@@ -252,6 +271,17 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     if (int r = upload(c->indices, idx)) return r;
 
     lap("geometry upload");
+    if (device_bvh) {
+        if (int r = upload(c->shapes, shapes)) return r;          // (uploaded again below once the light tables have set cdf_off)
+        { std::vector<double> sp(d->spheres, d->spheres + 4 * (size_t)d->n_shapes); if (int r = upload(c->spheres, sp)) return r; }
+        c->bvh.spheres = c->spheres.as<double>();
+        double split_budget = 0.0;      // the device pre-split exists (k_bvh_split) but does not pay under bottom-up clustering: DESIGN.md 4.1
+        if (const char *e = getenv("GDPT_BVH_SPLIT_DEVICE")) split_budget = atof(e);
+        const int rb = build_bvh_device(c, shapes, split_budget);
+        if (rb < 0) return rb;
+        if (rb > 0) { device_bvh = false; bvh_thread.join(); build_bvh(hs, bvh); }     // too deep for the traversal stack: host builder
+        lap("bvh build (device)");
+    }
     // ---- materials / textures / images
     std::vector<DMaterial> mats(d->n_materials);
     for (int i = 0; i < d->n_materials; i++) {
@@ -324,17 +354,22 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     }
 
     lap("light tables");
-    bvh_thread.join();
+    if (bvh_thread.joinable()) bvh_thread.join();
     lap("bvh build (rest)");
-    if (3 * bvh.max_depth + 1 > STACK_TOTAL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
-    c->bvh_depth = bvh.max_depth;
+    if (!device_bvh) {
+        if (3 * bvh.max_depth + 1 > STACK_TOTAL) return fail(GDPT_ERR_UNSUPPORTED, "BVH depth %d exceeds the traversal stack", bvh.max_depth);
+        c->bvh_depth = bvh.max_depth;
+    }
     for (int k = 0; k < 3; k++) { c->box_lo[k] = bvh.lo[k]; c->box_hi[k] = bvh.hi[k]; }
     if (int r = upload(c->shapes, shapes)) return r;
     { std::vector<double> sp(d->spheres, d->spheres + 4 * (size_t)d->n_shapes); if (int r = upload(c->spheres, sp)) return r; }
-    if (int r = upload(c->bvh_nodes, bvh.nodes)) return r;
-    if (int r = upload(c->bvh_prims, bvh.prims)) return r;
-    c->bvh.nodes = c->bvh_nodes.as<float4>(); c->bvh.prims = c->bvh_prims.as<float4>(); c->bvh.spheres = c->spheres.as<double>();
-    c->bvh.n_nodes = bvh.prims.empty() ? 0 : (int)bvh.nodes.size(); c->bvh.n_prims = (int)bvh.prims.size();
+    c->bvh.spheres = c->spheres.as<double>();
+    if (!device_bvh) {
+        if (int r = upload(c->bvh_nodes, bvh.nodes)) return r;
+        if (int r = upload(c->bvh_prims, bvh.prims)) return r;
+        c->bvh.nodes = c->bvh_nodes.as<float4>(); c->bvh.prims = c->bvh_prims.as<float4>();
+        c->bvh.n_nodes = bvh.prims.empty() ? 0 : (int)bvh.nodes.size(); c->bvh.n_prims = (int)bvh.prims.size();
+    }
     c->bvh_pending = no_bvh;
     // bounds sphere (scene.cpp:30-34): float box from the "Embree" scene, arithmetic in double
     {

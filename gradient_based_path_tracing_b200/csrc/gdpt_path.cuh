@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(128) k_path_generate(DScene<R> sc, WaveParams 
     else {
         long long s = i / wp.npix_pad, p = i % wp.npix_pad;
         int tile = (int)(p >> 5), lane = (int)(p & 31);
-        int x = (tile % wp.tiles_x) * 8 + (lane & 7), y = wp.y0 + (tile / wp.tiles_x) * 4 + (lane >> 3);
+        int x = (tile % wp.tiles_x) * 8 + (lane & 7), y = wave_row(wp, tile / wp.tiles_x, lane);
         if (x < wp.width && y < wp.y1) {
             ps.px = x; ps.py = y; active = true;
             stream = (unsigned long long)(wp.sample0 + s) * (unsigned long long)wp.width * wp.height + (unsigned long long)y * wp.width + x;

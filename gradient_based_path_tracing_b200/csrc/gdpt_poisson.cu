@@ -1,6 +1,7 @@
 // Host side of the screened-Poisson solve (kernels: gdpt_poisson.cuh).
 #include "gdpt_context.cuh"
 #include "gdpt_poisson.cuh"
+#include "gdpt_poisson_fft.cuh"
 
 namespace gdpt {
 
@@ -32,8 +33,78 @@ static int ensure_poisson(gdpt_ctx *c, int w, int h) {
     return ensure_matrices(c, w, h);
 }
 
+// ---------------------------------------------------------------- FFT form (gdpt_poisson_fft.cuh)
+constexpr int FFT_MIN_N = 16, FFT_MAX_P = 8192;      // P complex + N real of shared memory per block: 160 KB at P = 8192 (N <= 4097)
+static size_t fft_smem(int P, int N) { return (size_t)P * sizeof(double2) + (size_t)((N + 1) & ~1) * sizeof(double); }
+static bool fft_eligible(int N) {
+    if (N < FFT_MIN_N) return false;
+    int P = 16; while (P < 2 * (N - 1) - 1) P <<= 1;
+    return P <= FFT_MAX_P;
+}
+static int ensure_plan(gdpt_ctx *c, DctPlanBufs &b, int N) {
+    if (b.N == N) return 0;
+    const int M = N - 1;
+    int P = 16, logP = 4; while (P < 2 * M - 1) { P <<= 1; logP++; }
+    if (int r = b.tw.ensure((size_t)P * sizeof(double2))) return r;
+    if (int r = b.chirp.ensure((size_t)M * sizeof(double2))) return r;
+    if (int r = b.wpost.ensure((size_t)M * sizeof(double2))) return r;
+    if (int r = b.bhat.ensure((size_t)P * sizeof(double2))) return r;
+    static bool attr_set = false;
+    if (!attr_set) {
+        GD_CUDA(cudaFuncSetAttribute(k_dct1_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fft_smem(FFT_MAX_P, FFT_MAX_P / 2 + 2)));
+        GD_CUDA(cudaFuncSetAttribute(k_dct_plan_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FFT_MAX_P * sizeof(double2))));
+        attr_set = true;
+    }
+    k_dct_plan_tables<<<blocks_for(P, 256), 256, 0, c->stream>>>(M, P, b.tw.as<double2>(), b.chirp.as<double2>(), b.wpost.as<double2>());
+    k_dct_plan_filter<<<1, FFT_THREADS, (size_t)P * sizeof(double2), c->stream>>>(M, P, logP, b.tw.as<double2>(), b.chirp.as<double2>(), b.bhat.as<double2>());
+    c->stats.kernel_launches += 2;
+    GD_CUDA(cudaGetLastError());
+    b.N = N; b.M = M; b.P = P; b.logP = logP;
+    return 0;
+}
+static DctPlan plan_of(const DctPlanBufs &b) {
+    DctPlan p; p.N = b.N; p.M = b.M; p.P = b.P; p.logP = b.logP;
+    p.tw = b.tw.as<double2>(); p.chirp = b.chirp.as<double2>(); p.bhat = b.bhat.as<double2>(); p.wpost = b.wpost.as<double2>();
+    return p;
+}
+
+// rhs -> rows (DCT-I along x) -> columns (DCT-I along y, spectral divide + DC, DCT-I along y) -> rows (DCT-I along x, scale,
+// RGB interleave): 1 + 3 launches, two planar work images, the column pass in place.
+static int poisson_device_fft(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out) {
+    PoissonCache &pc = c->pc;
+    const size_t plane3 = (size_t)w * h * 3 * sizeof(double);
+    if (int r = pc.work.ensure(plane3)) return r;
+    if (int r = pc.work2.ensure(plane3)) return r;
+    if (int r = pc.partial.ensure((size_t)SM_COUNT * 8 * 3 * sizeof(double))) return r;
+    if (int r = pc.dc.ensure(64)) return r;
+    if (int r = ensure_plan(c, pc.plan_w, w)) return r;
+    if (int r = ensure_plan(c, pc.plan_h, h)) return r;
+    cudaStream_t st = c->stream;
+    double *A = pc.work.as<double>(), *B = pc.work2.as<double>();
+    const int nb = SM_COUNT * 8;
+    k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, h, 0, h, d_u, d_gx, d_gy, alpha, A, pc.partial.as<double>());
+    k_dc_reduce<<<1, 32, 0, st>>>(nb, pc.partial.as<double>(), pc.dc.as<double>());
+    const DctPlan pw = plan_of(pc.plan_w), ph = plan_of(pc.plan_h);
+    DctArgs a; memset(&a, 0, sizeof(a));
+    a.plane_stride = (long long)w * h; a.img_w = w; a.img_h = h; a.alpha = alpha; a.dc = pc.dc.as<double>();
+    a.scale = 4.0 * (w - 1) * (h - 1); a.out = d_out;
+    // rows, forward
+    a.mode = DCT_STORE; a.count = 3 * h; a.per_plane = h; a.line_stride = w; a.elem_stride = 1;
+    k_dct1_fft<<<a.count, FFT_THREADS, fft_smem(pw.P, w), st>>>(pw, a, A, B);
+    // columns: forward, divide, inverse — in place
+    a.mode = DCT_COLUMNS; a.count = 3 * w; a.per_plane = w; a.line_stride = 1; a.elem_stride = w;
+    k_dct1_fft<<<a.count, FFT_THREADS, fft_smem(ph.P, h), st>>>(ph, a, B, B);
+    // rows, inverse + scale + interleave
+    a.mode = DCT_SCALE_INTERLEAVE; a.count = 3 * h; a.per_plane = h; a.line_stride = w; a.elem_stride = 1;
+    k_dct1_fft<<<a.count, FFT_THREADS, fft_smem(pw.P, w), st>>>(pw, a, B, nullptr);
+    c->stats.kernel_launches += 5;
+    GD_CUDA(cudaGetLastError());
+    return 0;
+}
+
 int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, const double *d_gy, double alpha, double *d_out) {
     if (w < 2 || h < 2) return fail(GDPT_ERR_ARG, "Poisson solve needs at least a 2x2 image");
+    if (c->poisson_fft && fft_eligible(w) && fft_eligible(h)) return poisson_device_fft(c, w, h, d_u, d_gx, d_gy, alpha, d_out);
     if (int r = ensure_poisson(c, w, h)) return r;
     PoissonCache &pc = c->pc;
     cudaStream_t st = c->stream;

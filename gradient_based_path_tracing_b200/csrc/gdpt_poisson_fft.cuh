@@ -1,0 +1,203 @@
+// DCT-I (FFTW's REDFT00, what fourierSolve executes twice per channel: /root/reference/src/render.cpp:190-192,227,242)
+// in O(N log N): the replacement for the dense-matrix form of gdpt_poisson.cuh on films of 16 pixels a side and more.
+//
+//   X_k = x_0 + (-1)^k x_M + 2 sum_{n=1}^{M-1} x_n cos(pi n k / M),   M = N - 1,  k = 0..M
+//
+// is the DFT of length 2M of the even extension y of x.  Because y is real, that DFT follows from ONE complex DFT of
+// length M of z_n = y_2n + i y_2n+1 (the usual even/odd split, stable in floating point).  2M has large prime factors at
+// every film size of interest (1919*2, 1079*2, 3839*2, 2159*2: SURVEY 7.2-4), so the length-M DFT is evaluated with
+// Bluestein's chirp-z identity  Z_k = conj(w_k) * sum_n (z_n conj(w_n)) w_(k-n),  w_n = exp(i pi n^2 / M),  as a circular
+// convolution of power-of-two length P >= 2M - 1:  IFFT_P( FFT_P(a) * FFT_P(b) ).
+//
+// One thread block owns one line (a row, or a column read with its stride): the line is staged in shared memory, both
+// power-of-two FFTs run there as radix-4 passes (decimation in frequency forward, the exact structural inverse —
+// decimation in time — backward, so no digit-reversal pass is ever needed: the filter's transform is produced by the same
+// forward routine and therefore in the same order), and the column pass keeps the line on chip across "forward DCT,
+// spectral divide (render.cpp:231-239), inverse DCT".  FP64 throughout; the chirp angles are reduced exactly in integers
+// (n^2 mod 2M) before cospi / sinpi.
+#pragma once
+#ifndef GDPT_FFT_HOST_TEST      // tests/host/fft_check.cpp compiles the device functions below for the host (one "thread")
+#include <cuda_runtime.h>
+#endif
+#include <math.h>
+
+namespace gdpt {
+
+struct DctPlan {
+    int N, M, P, logP;
+    const double2 *tw;      // [P]   exp(-2 pi i k / P)
+    const double2 *chirp;   // [M]   w_n = exp(i pi n^2 / M)
+    const double2 *bhat;    // [P]   FFT_P of the circular chirp filter, in the forward routine's output order, times 1/P
+    const double2 *wpost;   // [M]   exp(-i pi k / M)
+};
+
+constexpr int FFT_THREADS = 256;
+
+__device__ __forceinline__ double2 cmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__device__ __forceinline__ double2 cmulc(double2 a, double2 b) { return make_double2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y); }   // a * conj(b)
+__device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+
+// In-place forward FFT of s[0..P) (natural order in, digit-reversed out), all threads of the block.
+__device__ inline void fft_forward(double2 *s, int P, int logP, const double2 *__restrict__ tw) {
+    int n = P;
+    for (int stage = 0; stage < logP / 2; stage++, n >>= 2) {
+        const int q4 = n >> 2, ts = P / n;
+        for (int idx = threadIdx.x; idx < (P >> 2); idx += blockDim.x) {
+            const int blk = idx / q4, j = idx - blk * q4, base = blk * n + j;
+            const double2 a = s[base], b = s[base + q4], c = s[base + 2 * q4], d = s[base + 3 * q4];
+            const double2 t0 = cadd(a, c), t1 = csub(a, c), t2 = cadd(b, d), t3 = csub(b, d);
+            const double2 y1 = make_double2(t1.x + t3.y, t1.y - t3.x), y3 = make_double2(t1.x - t3.y, t1.y + t3.x);
+            s[base] = cadd(t0, t2);
+            if (j == 0) { s[base + q4] = y1; s[base + 2 * q4] = csub(t0, t2); s[base + 3 * q4] = y3; }
+            else {
+                s[base + q4] = cmul(y1, __ldg(tw + j * ts));
+                s[base + 2 * q4] = cmul(csub(t0, t2), __ldg(tw + 2 * j * ts));
+                s[base + 3 * q4] = cmul(y3, __ldg(tw + 3 * j * ts));
+            }
+        }
+        __syncthreads();
+    }
+    if (logP & 1) {
+        for (int idx = threadIdx.x; idx < (P >> 1); idx += blockDim.x) {
+            const double2 a = s[2 * idx], b = s[2 * idx + 1];
+            s[2 * idx] = cadd(a, b); s[2 * idx + 1] = csub(a, b);
+        }
+        __syncthreads();
+    }
+}
+
+// The structural inverse of fft_forward (digit-reversed in, natural out), unscaled: fft_inverse(fft_forward(x)) = P x.
+__device__ inline void fft_inverse(double2 *s, int P, int logP, const double2 *__restrict__ tw) {
+    if (logP & 1) {
+        for (int idx = threadIdx.x; idx < (P >> 1); idx += blockDim.x) {
+            const double2 a = s[2 * idx], b = s[2 * idx + 1];
+            s[2 * idx] = cadd(a, b); s[2 * idx + 1] = csub(a, b);
+        }
+        __syncthreads();
+    }
+    int n = (logP & 1) ? 8 : 4;
+    for (int stage = 0; stage < logP / 2; stage++, n <<= 2) {
+        const int q4 = n >> 2, ts = P / n;
+        for (int idx = threadIdx.x; idx < (P >> 2); idx += blockDim.x) {
+            const int blk = idx / q4, j = idx - blk * q4, base = blk * n + j;
+            double2 u0 = s[base], u1 = s[base + q4], u2 = s[base + 2 * q4], u3 = s[base + 3 * q4];
+            if (j != 0) { u1 = cmulc(u1, __ldg(tw + j * ts)); u2 = cmulc(u2, __ldg(tw + 2 * j * ts)); u3 = cmulc(u3, __ldg(tw + 3 * j * ts)); }
+            const double2 t0 = cadd(u0, u2), t1 = csub(u0, u2), t2 = cadd(u1, u3), t3 = csub(u1, u3);
+            s[base] = cadd(t0, t2);
+            s[base + q4] = make_double2(t1.x - t3.y, t1.y + t3.x);      // u0 + i u1 - u2 - i u3
+            s[base + 2 * q4] = csub(t0, t2);
+            s[base + 3 * q4] = make_double2(t1.x + t3.y, t1.y - t3.x);  // u0 - i u1 - u2 + i u3
+        }
+        __syncthreads();
+    }
+}
+
+// xs[0..N) (real, shared memory) -> its DCT-I in place.  s: P complex of shared memory.
+__device__ inline void dct1_line(const DctPlan &pl, double *xs, double2 *s) {
+    const int M = pl.M, P = pl.P;
+    for (int n = threadIdx.x; n < P; n += blockDim.x) {
+        double2 a = make_double2(0.0, 0.0);
+        if (n < M) {
+            const int e = 2 * n, o = 2 * n + 1;
+            const double re = xs[e <= M ? e : 2 * M - e], im = xs[o <= M ? o : 2 * M - o];
+            a = cmulc(make_double2(re, im), __ldg(pl.chirp + n));
+        }
+        s[n] = a;
+    }
+    __syncthreads();
+    fft_forward(s, P, pl.logP, pl.tw);
+    for (int i = threadIdx.x; i < P; i += blockDim.x) s[i] = cmul(s[i], __ldg(pl.bhat + i));
+    __syncthreads();
+    fft_inverse(s, P, pl.logP, pl.tw);
+    for (int k = threadIdx.x; k < M; k += blockDim.x) s[k] = cmulc(s[k], __ldg(pl.chirp + k));     // Z_k
+    __syncthreads();
+    for (int k = threadIdx.x; k < M; k += blockDim.x) {
+        const double2 zk = s[k], zm = s[k == 0 ? 0 : M - k], wp = __ldg(pl.wpost + k);
+        const double ex = 0.5 * (zk.x + zm.x), ey = 0.5 * (zk.y - zm.y);          // E = (Z_k + conj Z_(M-k)) / 2
+        const double ox = 0.5 * (zk.y + zm.y), oy = -0.5 * (zk.x - zm.x);         // O = (Z_k - conj Z_(M-k)) / (2i)
+        (void)ey;
+        xs[k] = ex + wp.x * ox - wp.y * oy;
+        if (k == 0) xs[M] = zk.x - zk.y;                                          // Y_M = E_0 - O_0
+    }
+    __syncthreads();
+}
+
+#ifndef GDPT_FFT_HOST_TEST
+enum { DCT_STORE = 0, DCT_COLUMNS = 1, DCT_SCALE_INTERLEAVE = 2 };
+struct DctArgs {
+    int mode;
+    int count;              // lines
+    int per_plane;          // lines per channel plane (rows: H, columns: W)
+    long long plane_stride; // elements between channel planes
+    long long line_stride;  // elements between consecutive lines of a plane (rows: W, columns: 1)
+    long long elem_stride;  // elements between consecutive samples of a line (rows: 1, columns: W)
+    // DCT_COLUMNS: spectral divide between the two transforms (render.cpp:229-239)
+    int img_w, img_h; double alpha; const double *dc;
+    // DCT_SCALE_INTERLEAVE: out[(y * img_w + x) * 3 + ch] = value / scale (render.cpp:243-247)
+    double scale; double *out;
+};
+
+static __global__ void __launch_bounds__(FFT_THREADS) k_dct1_fft(DctPlan pl, DctArgs a, const double *in, double *dst) {   // in == dst is allowed (a block reads its whole line before it writes it)
+    extern __shared__ double2 smem_fft[];
+    double2 *s = smem_fft;
+    double *xs = reinterpret_cast<double *>(smem_fft + pl.P);
+    const int N = pl.N;
+    for (int line = blockIdx.x; line < a.count; line += gridDim.x) {
+        const int ch = line / a.per_plane, l = line - ch * a.per_plane;
+        const long long base = ch * a.plane_stride + l * a.line_stride;
+        for (int n = threadIdx.x; n < N; n += blockDim.x) xs[n] = in[base + n * a.elem_stride];
+        __syncthreads();
+        dct1_line(pl, xs, s);
+        if (a.mode == DCT_COLUMNS) {
+            // l = image column x, sample index = frequency row y: F = H / (alpha - (float)(lapY + lapX)); F(0,0) = DC of the primal
+            const double lapx = 2.0 * cos(3.14159265358979323846 * l / (a.img_w - 1));
+            for (int y = threadIdx.x; y < N; y += blockDim.x) {
+                const double lapy = -4.0 + (2.0 * cos(3.14159265358979323846 * y / (a.img_h - 1)));
+                const float resp = (float)(lapy + lapx);
+                double v = xs[y] / (a.alpha - resp);
+                if (y == 0 && l == 0) v = a.dc[ch];
+                xs[y] = v;
+            }
+            __syncthreads();
+            dct1_line(pl, xs, s);
+        }
+        if (a.mode == DCT_SCALE_INTERLEAVE) {
+            for (int n = threadIdx.x; n < N; n += blockDim.x) a.out[((long long)l * a.img_w + n) * 3 + ch] = xs[n] / a.scale;
+        } else {
+            for (int n = threadIdx.x; n < N; n += blockDim.x) dst[base + n * a.elem_stride] = xs[n];
+        }
+        __syncthreads();
+    }
+}
+
+// Plan tables for one line length.  tw, chirp, wpost first (any grid), then the filter transform by ONE block.
+static __global__ void k_dct_plan_tables(int M, int P, double2 *tw, double2 *chirp, double2 *wpost) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P) { const double t = 2.0 * (double)i / (double)P; tw[i] = make_double2(cospi(t), -sinpi(t)); }
+    if (i < M) {
+        const long long q = ((long long)i * i) % (2LL * M);
+        const double t = (double)q / (double)M;
+        chirp[i] = make_double2(cospi(t), sinpi(t));
+        const double u = (double)i / (double)M;
+        wpost[i] = make_double2(cospi(u), -sinpi(u));
+    }
+}
+static __global__ void __launch_bounds__(FFT_THREADS) k_dct_plan_filter(int M, int P, int logP, const double2 *tw, const double2 *chirp, double2 *bhat) {
+    extern __shared__ double2 smem_fft[];
+    double2 *s = smem_fft;
+    for (int i = threadIdx.x; i < P; i += blockDim.x) {
+        double2 v = make_double2(0.0, 0.0);
+        if (i < M) v = chirp[i];
+        else if (P - i < M) v = chirp[P - i];       // b_(-m) = w_m
+        s[i] = v;
+    }
+    __syncthreads();
+    fft_forward(s, P, logP, tw);
+    const double inv = 1.0 / (double)P;
+    for (int i = threadIdx.x; i < P; i += blockDim.x) bhat[i] = make_double2(s[i].x * inv, s[i].y * inv);
+}
+
+#endif  // GDPT_FFT_HOST_TEST
+
+} // namespace gdpt

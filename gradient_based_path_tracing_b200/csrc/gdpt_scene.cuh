@@ -314,8 +314,10 @@ GD_D T mip_bilinear(const DImage &im, R u, R v, int level, F fetch) {
     int w = im.w[level], h = im.h[level];
     u = u * w - R(0.5);
     v = v * h - R(0.5);
-    int ufi = imodulo((int)u, w), vfi = imodulo((int)v, h);
-    int uci = imodulo(ufi + 1, w), vci = imodulo(vfi + 1, h);
+    // modulo(int(u), w) etc. of mipmap.h:52-55; the integer divisions are skipped where they cannot change the value
+    const int iu = (int)u, iv = (int)v;
+    const int ufi = (iu >= 0 && iu < w) ? iu : imodulo(iu, w), vfi = (iv >= 0 && iv < h) ? iv : imodulo(iv, h);
+    const int uci = ufi + 1 == w ? 0 : ufi + 1, vci = vfi + 1 == h ? 0 : vfi + 1;
     R uo = u - ufi, vo = v - vfi;
     long long base = im.off[level];
     T ff = fetch(base + (long long)vfi * w + ufi), fc = fetch(base + (long long)vci * w + ufi);

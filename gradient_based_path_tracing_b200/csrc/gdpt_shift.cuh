@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK) k_shift(DScene<R> sc, WaveParams 
         else {
             long long s = i / wp.npix_pad, p = i % wp.npix_pad;
             int tile = (int)(p >> 5), lane = (int)(p & 31);
-            px = (tile % wp.tiles_x) * 8 + (lane & 7); py = wp.y0 + (tile / wp.tiles_x) * 4 + (lane >> 3);
+            px = (tile % wp.tiles_x) * 8 + (lane & 7); py = wave_row(wp, tile / wp.tiles_x, lane);
             if (px >= wp.width || py >= wp.y1) break;
             stream = (unsigned long long)(wp.sample0 + s) * (unsigned long long)wp.width * wp.height + (unsigned long long)py * wp.width + px;
         }
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, MINB) k_shift_sm(DScene<R> sc, Wa
             else {
                 long long s = i / wp.npix_pad, p = i % wp.npix_pad;
                 int tile = (int)(p >> 5), lane = (int)(p & 31);
-                px = (tile % wp.tiles_x) * 8 + (lane & 7); py = wp.y0 + (tile / wp.tiles_x) * 4 + (lane >> 3);
+                px = (tile % wp.tiles_x) * 8 + (lane & 7); py = wave_row(wp, tile / wp.tiles_x, lane);
                 if (px >= wp.width || py >= wp.y1) continue;
                 stream = (unsigned long long)(wp.sample0 + s) * (unsigned long long)wp.width * wp.height + (unsigned long long)py * wp.width + px;
             }

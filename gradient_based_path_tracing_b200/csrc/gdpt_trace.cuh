@@ -40,13 +40,19 @@ struct TraceStackT {
 };
 using TraceStack = TraceStackT<STACK_SMEM>;
 
-template <bool EXACT, bool FLAT = false>
-GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3], float tnear, float &best, Hit &hit) {
+// r: the ray state (o, d, tnear, best = current tfar, hit; EXACT mode also best_d).  EXACT mode decides "closer" in DOUBLE like
+// the oracle's ray caster — accepted iff tnear < t <= best_d, an exactly equal depth goes to the smaller (shape, primitive) id —
+// so the hit does not depend on the order in which the tree presents the primitives; best (float, rounded from best_d) only
+// prunes boxes.  A sphere is tested by the reference's own callback against the FLOAT tfar of the Embree ray (sphere.inl:77-85),
+// and its hit distance travels on as that float (intersection.cpp:39-40): mirrored here.
+template <bool EXACT, bool FLAT = false, typename RS>
+GD_D void test_prim(const DBvh &bvh, int pi, RS &r) {
+    const float *o = r.o, *d = r.d; const float tnear = r.tnear; float &best = r.best; Hit &hit = r.hit;
     float4 a = __ldg(bvh.prims + 3 * pi), b = __ldg(bvh.prims + 3 * pi + 1), c = __ldg(bvh.prims + 3 * pi + 2);
     int prim_id = __float_as_int(a.w), shape_id = __float_as_int(b.w), kind = __float_as_int(c.w);
     if (kind == 1) {
         double t = sphere_hit_d(bvh.spheres + 4 * shape_id, o, d, tnear, best);
-        if (t >= 0.0) { best = (float)t; hit.t = best; hit.u = 0.f; hit.v = 0.f; hit.shape_id = shape_id; hit.prim_id = prim_id; }
+        if (t >= 0.0) { best = (float)t; r.best_d = (double)best; hit.t = best; hit.u = 0.f; hit.v = 0.f; hit.shape_id = shape_id; hit.prim_id = prim_id; }
         return;
     }
     float t, u, v;
@@ -81,10 +87,10 @@ GD_D void test_prim(const DBvh &bvh, int pi, const float o[3], const float d[3],
         double vd = (dx * qx + dy * qy + dz * qz) * inv;
         if (!(vd >= 0.0 && ud + vd <= 1.0)) return;
         double td = (e2x * qx + e2y * qy + e2z * qz) * inv;
-        if (!(td > (double)tnear && td <= (double)best)) return;
+        if (!(td > (double)tnear && td <= r.best_d)) return;
+        if (td == r.best_d && hit.shape_id >= 0 && !(shape_id < hit.shape_id || (shape_id == hit.shape_id && prim_id < hit.prim_id))) return;
+        r.best_d = td;
         t = (float)td; u = (float)ud; v = (float)vd;
-        // an earlier hit whose double t rounded to the same float: keep the ordering rule
-        if (t == best && hit.shape_id >= 0 && !(shape_id < hit.shape_id || (shape_id == hit.shape_id && prim_id < hit.prim_id))) return;
     } else {
         float e1x = b.x - a.x, e1y = b.y - a.y, e1z = b.z - a.z;
         float e2x = c.x - a.x, e2y = c.y - a.y, e2z = c.z - a.z;
@@ -112,12 +118,13 @@ constexpr int TRACE_POP = (int)0x80000001;    // "take the next stack entry" (lo
 struct RayState {
     float o[3], d[3], id[3];   // origin, direction, 1/direction
     float tnear, best;         // best = current tfar
+    double best_d;             // EXACT mode: the accepted hit distance in double (test_prim); unused otherwise
     float oid[3], slack;       // FMA slab form: o*id and the absolute rounding slack that keeps it conservative
     Hit hit;
     GD_D void init(const float4 &a, const float4 &b) {
         o[0] = a.x; o[1] = a.y; o[2] = a.z; d[0] = b.x; d[1] = b.y; d[2] = b.z;
         id[0] = 1.0f / b.x; id[1] = 1.0f / b.y; id[2] = 1.0f / b.z;
-        tnear = a.w; best = b.w;
+        tnear = a.w; best = b.w; best_d = (double)b.w;
         oid[0] = o[0] * id[0]; oid[1] = o[1] * id[1]; oid[2] = o[2] * id[2];
         slack = 2.4e-7f * fmaxf(fmaxf(fabsf(oid[0]), fabsf(oid[1])), fabsf(oid[2]));
         hit.t = b.w; hit.u = hit.v = 0.f; hit.shape_id = -1; hit.prim_id = -1;
@@ -135,8 +142,11 @@ GD_D int trace_pop(const ST &st, int &sp, float best) {
 }
 
 // Inner node: slab-test the 4 children, descend into the nearest, push the rest far-to-near.
-template <int SORT = 0, int FMA = 0, bool NOPOP = false, typename ST>
-GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, ST &st, int &sp) {
+// EAGER = 1 (EXACT_E selects the triangle arithmetic): children that are leaves and pass the slab test are tested right here,
+// in the node step, instead of being visited in a trip of their own — the leaf code then runs for every lane whose node has a
+// hit leaf child at this trip, not for the two or three lanes of a warp that happen to sit on a leaf.
+template <int SORT = 0, int FMA = 0, bool NOPOP = false, int EAGER = 0, bool EXACT_E = false, typename ST, typename RS>
+GD_D int trace_node(const DBvh &bvh, int cur, RS &r, ST &st, int &sp, unsigned *n_prims = nullptr) {
     const float4 *n = bvh.nodes + 8 * (size_t)cur;
     const float INF = __int_as_float(0x7f800000);
     float dist[4]; int cid[4];
@@ -181,6 +191,21 @@ GD_D int trace_node(const DBvh &bvh, int cur, const RayState &r, ST &st, int &sp
         dist[k] = (cid[k] != 0 && tmn <= tmx) ? tmn : INF;
     }
     }
+    if (EAGER) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (cid[k] < 0 && dist[k] < INF) {
+                if (dist[k] <= r.best) {
+                    const int enc = ~cid[k], first = enc >> 3, cnt = enc & 7;
+                    if (n_prims) *n_prims += cnt;
+                    for (int q = 0; q < cnt; q++) test_prim<EXACT_E, false>(bvh, first + q, r);
+                }
+                dist[k] = INF;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) if (dist[k] > r.best) dist[k] = INF;     // a hit found above may have closed the other children
+    }
 #define GD_CSWAP(i, j) if (dist[j] < dist[i]) { float td = dist[i]; dist[i] = dist[j]; dist[j] = td; int tc = cid[i]; cid[i] = cid[j]; cid[j] = tc; }
     if (SORT == 0) {   // sort the 4 candidates by distance (network), nearest first
         GD_CSWAP(0, 1) GD_CSWAP(2, 3) GD_CSWAP(0, 2) GD_CSWAP(1, 3) GD_CSWAP(1, 2)
@@ -202,7 +227,7 @@ GD_D int trace_leaf(const DBvh &bvh, int cur, RayState &r, const ST &st, int &sp
     int enc = ~cur;
     int first = enc >> 3, cnt = enc & 7;
     if (n_prims) *n_prims += cnt;
-    for (int i = 0; i < cnt; i++) test_prim<EXACT, FLAT>(bvh, first + i, r.o, r.d, r.tnear, r.best, r.hit);
+    for (int i = 0; i < cnt; i++) test_prim<EXACT, FLAT>(bvh, first + i, r);
     return trace_pop(st, sp, r.best);
 }
 

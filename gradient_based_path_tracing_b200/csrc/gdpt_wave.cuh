@@ -33,7 +33,7 @@ inline void launch_trace(gdpt_ctx *c, const RayF *rays, HitRec *hits, int n, con
     else if constexpr (EXACT) launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, st, rays, hits, n, order, count_ptr);
     else switch (c->trace_variant) {
 #define GD_V(v) case v: launch_trace_v<EXACT, false, v>(c, st, rays, hits, n, order, count_ptr); break;
-        GD_V(0) GD_V(10000) GD_V(20000) GD_V(40000)
+        GD_V(0) GD_V(10000) GD_V(40000) GD_V(120000)
 #undef GD_V
         default: launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, st, rays, hits, n, order, count_ptr);
     }
@@ -235,12 +235,14 @@ int run_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     WaveCalibration &cal = c->cal;
     const int prec = (int)sizeof(R);
     const bool same = cal.valid && cal.max_depth == sc.max_depth && cal.rr_depth == sc.rr_depth && cal.precision == prec && cal.width == wp.width &&
-                      cal.y0 == wp.y0 && cal.y1 == wp.y1 && cal.tail_paths == c->tail_paths && wp.n_paths <= cal.n_paths;
+                      cal.y0 == wp.y0 && cal.y1 == wp.y1 && cal.tail_paths == c->tail_paths && wp.n_paths <= cal.n_paths &&
+                      cal.strip_count == wp.strip_count && cal.strip_phase == wp.strip_phase;
     if (!same) {
         cal.valid = false;
         if (int r = run_wave_sync<R, MS>(c, sc, wp, &cal)) return r;
         cal.n_paths = wp.n_paths; cal.max_depth = sc.max_depth; cal.rr_depth = sc.rr_depth; cal.precision = prec; cal.width = wp.width;
-        cal.y0 = wp.y0; cal.y1 = wp.y1; cal.tail_paths = c->tail_paths; cal.valid = !cal.counts.empty();
+        cal.y0 = wp.y0; cal.y1 = wp.y1; cal.tail_paths = c->tail_paths; cal.strip_count = wp.strip_count; cal.strip_phase = wp.strip_phase;
+        cal.valid = !cal.counts.empty();
         return 0;
     }
     const int k = c->wave_index % std::max(1, c->wave_streams);

@@ -45,6 +45,7 @@ struct WaveParams {
     int width, height;       // full image
     int y0, y1;              // row band rendered by this context
     int tiles_x;             // ceil(width / 8)
+    int strip_count, strip_phase;   // of the 4-row strips of [y0, y1) this context renders those with index = phase (mod count); count <= 1: all
     int n_paths;             // padded path slots in the wave
     long long npix_pad;      // padded pixels per sample pass (tiles * 32)
     int sample0, n_samples;  // first sample index of the wave, samples in the wave
@@ -60,6 +61,12 @@ struct WaveParams {
     int sort_cell_bits, sort_dir_bits;
 };
 
+// row of lane `lane` of the 8x4 pixel tile in tile row `tile_row` of this context's share of the band
+GD_D int wave_row(const WaveParams &wp, int tile_row, int lane) {
+    const int strip = wp.strip_count > 1 ? wp.strip_phase + tile_row * wp.strip_count : tile_row;
+    return wp.y0 + strip * 4 + (lane >> 3);
+}
+
 // ---------------------------------------------------------------- ray sorting
 // Bounce rays are incoherent; before they are traced the queue is re-ordered by
 // key = (coarse origin cell, Morton) : (direction, 8x8 octahedral bins) : (fine cell bit per axis)
@@ -72,10 +79,10 @@ constexpr int SORT_CHUNK = 32768;                       // histogram bins scanne
 constexpr int SORT_MAX_KEY_BITS = 25;                   // 3*cell + 2*dir may not exceed this (1024 chunks)
 inline int sort_bins(int cell_bits, int dir_bits) { return 1 << (3 * cell_bits + 2 * dir_bits); }
 
-GD_D unsigned sort_spread(unsigned x, int bits) {   // abcd -> a00b00c00d
-    unsigned r = 0;
-    for (int b = 0; b < bits; b++) r |= ((x >> b) & 1u) << (3 * b);
-    return r;
+GD_D unsigned sort_spread(unsigned x, int bits) {   // abcd -> a00b00c00d (up to 10 bits)
+    x &= (1u << bits) - 1u;
+    x = (x | (x << 16)) & 0x030000ffu; x = (x | (x << 8)) & 0x0300f00fu; x = (x | (x << 4)) & 0x030c30c3u; x = (x | (x << 2)) & 0x09249249u;
+    return x;
 }
 // key = [coarse cell Morton : direction bin : lowest cell bit per axis] — a warp of the sorted queue shares a
 // 2^(CELL_BITS-1) cell and a ~22 degree direction bin and differs in the fine cell
@@ -206,7 +213,7 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
     } else {
         long long s = i / wp.npix_pad, p = i % wp.npix_pad;
         int tile = (int)(p >> 5), lane = (int)(p & 31);
-        int x = (tile % wp.tiles_x) * 8 + (lane & 7), y = wp.y0 + (tile / wp.tiles_x) * 4 + (lane >> 3);
+        int x = (tile % wp.tiles_x) * 8 + (lane & 7), y = wave_row(wp, tile / wp.tiles_x, lane);
         if (x < wp.width && y < wp.y1) {
             g.px = x; g.py = y; active = true;
             stream = (unsigned long long)(wp.sample0 + s) * (unsigned long long)wp.width * wp.height + (unsigned long long)y * wp.width + x;
@@ -244,7 +251,8 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 //   STACKSEL 0: 20, 1: 16, 2: 12, 3: 8 shared-memory stack entries per thread (rest spills)
 //   OCC  0: launch bound 8 blocks/SM (64 regs), 1: 7 (72), 2: 9 (56), 3: 10 (48)
 //   LOOP (x10000) bit 0: a node step that lands on a leaf tests it in the same trip; bit 1: triangle test without early exits;
-//        bit 2: one pop site per trip (node misses and finished leaves pop together at the top of the next trip)
+//        bit 2: one pop site per trip (node misses and finished leaves pop together at the top of the next trip);
+//        bit 3 (with bit 2): leaf children are tested inside their parent's node step (no leaf trips)
 // COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
 // (bench.py derives the algorithmic bytes per ray from them; never in timed runs).
 constexpr int trace_variant_depth(int v) { return ((v / 100) % 10) == 0 ? 20 : ((v / 100) % 10) == 1 ? 16 : ((v / 100) % 10) == 2 ? 12 : 8; }
@@ -272,11 +280,14 @@ __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(
             if (LOOP & 4) {   // one pop site at the top of the trip, shared by the lanes coming from a node miss and from a leaf
                 while (true) {
                     if (cur == TRACE_POP) { cur = trace_pop(st, sp, r.best); if (cur == TRACE_DONE) break; }
-                    if (cur >= 0) { if (COUNT) cn++; cur = trace_node<SORT, FMA, true>(bvh, cur, r, st, sp); }
-                    else {
+                    if (cur >= 0) {
+                        if (COUNT) cn++;
+                        cur = trace_node<SORT, FMA, true, (LOOP & 8) ? 1 : 0, EXACT>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
+                        if ((LOOP & 8) && ANY && r.hit.shape_id >= 0) break;
+                    } else {
                         int enc = ~cur, first = enc >> 3, cnt = enc & 7;
                         if (COUNT) cp += cnt;
-                        for (int q = 0; q < cnt; q++) test_prim<EXACT, false>(bvh, first + q, r.o, r.d, r.tnear, r.best, r.hit);
+                        for (int q = 0; q < cnt; q++) test_prim<EXACT, false>(bvh, first + q, r);
                         if (ANY && r.hit.shape_id >= 0) break;
                         cur = TRACE_POP;
                     }

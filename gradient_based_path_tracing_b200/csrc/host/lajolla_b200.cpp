@@ -57,11 +57,11 @@ static void describe_scene(const FlatScene &s) {
 
 int main(int argc, char *argv[]) {
     if (argc <= 1) {
-        std::cout << "[Usage] ./lajolla_b200 [-o output_file_name] [-overlay camera.gdpt] [-spp n] [-precision f32|f64] [-offsets reference|shift] [-device d] [-seed s] filename.gdpt[.z]" << std::endl;
+        std::cout << "[Usage] ./lajolla_b200 [-o output_file_name] [-overlay camera.gdpt] [-spp n] [-precision f32|f64] [-offsets reference|shift] [-device d] [-gpus n] [-seed s] filename.gdpt[.z]" << std::endl;
         return 0;
     }
     std::string outputfile, overlay, precision = "f32", offsets = "reference";
-    int spp = 0, device = 0; unsigned long long seed = 0;
+    int spp = 0, device = 0, gpus = 1; unsigned long long seed = 0;
     bool describe = false;
     int integrator_override = -1;   // Integrator enum value (src/scene.h:14-23): 5 Path, 7 GradPath
     std::vector<std::string> filenames;
@@ -75,6 +75,7 @@ int main(int argc, char *argv[]) {
         else if (a == "-precision") precision = value();
         else if (a == "-offsets") offsets = value();              // gradpath only: the shipped offset semantics, or shift-mapped offsets (gdpt.h)
         else if (a == "-device") device = std::stoi(value());
+        else if (a == "-gpus") gpus = std::stoi(value());         // gradpath over n GPUs of this box (gdpt_multi_*: one host thread per device)
         else if (a == "-seed") seed = std::stoull(value());
         else if (a == "-integrator") { std::string v = value(); const char *names[] = {"depth", "shadingNormal", "meanCurvature", "rayDifferential", "mipmapLevel", "path", "volpath", "gradpath"};   // parse_scene.cpp:520-566
             for (int k = 0; k < 8; k++) if (v == names[k]) integrator_override = k;
@@ -103,7 +104,10 @@ int main(int argc, char *argv[]) {
         }
         if (describe) { describe_scene(scene); continue; }
         gdpt_ctx *ctx = nullptr;
-        if (gdpt_create(&scene.desc, device, &ctx) != GDPT_OK) { std::cerr << gdpt_last_error() << std::endl; return 1; }
+        gdpt_multi *multi = nullptr;
+        const bool use_multi = gpus > 1 && scene.integrator == 7;
+        if (gpus > 1 && !use_multi) { std::cerr << "-gpus applies to the gradpath integrator" << std::endl; return 2; }
+        if ((use_multi ? gdpt_multi_create(&scene.desc, gpus, nullptr, &multi) : gdpt_create(&scene.desc, device, &ctx)) != GDPT_OK) { std::cerr << gdpt_last_error() << std::endl; return 1; }
         std::cout << "Done. Took " << seconds_since(timer) << " seconds." << std::endl;
 
         std::cout << "Rendering..." << std::endl;
@@ -116,10 +120,11 @@ int main(int argc, char *argv[]) {
         p.offset_mode = offsets == "shift" ? GDPT_OFFSETS_SHIFT : GDPT_OFFSETS_REFERENCE;
         gdpt_images img{primal.data(), dx.data(), dy.data(), out.data()};
         const bool path = scene.integrator == 5;          // Integrator::Path -> path_render (render.cpp:385-386): one image
-        int rc = aux ? gdpt_render_aux(ctx, scene.integrator, p.precision, out.data()) : path ? gdpt_render_path(ctx, &p, out.data()) : gdpt_render(ctx, &p, &img);
+        int rc = use_multi ? gdpt_multi_render(multi, &p, &img)
+                 : aux ? gdpt_render_aux(ctx, scene.integrator, p.precision, out.data()) : path ? gdpt_render_path(ctx, &p, out.data()) : gdpt_render(ctx, &p, &img);
         gdpt_stats st{};
-        gdpt_get_stats(ctx, &st);
-        gdpt_destroy(ctx);
+        if (use_multi) { gdpt_multi_get_stats(multi, &st); gdpt_multi_destroy(multi); }
+        else { gdpt_get_stats(ctx, &st); gdpt_destroy(ctx); }
         if (rc != GDPT_OK) { std::cerr << gdpt_last_error() << std::endl; return 1; }
         double took = seconds_since(timer);
         std::cout << "Done. Took " << took << " seconds." << std::endl;

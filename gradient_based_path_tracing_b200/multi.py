@@ -223,13 +223,22 @@ class DistributedRenderer:
         self.scene, self.device, self.dist, self.torch, self._capi = scene, device, dist, torch, _capi
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
         self.bands = partition_rows(scene.height, self.world)
+        # which builder: a rank's share of the planned work decides like gdpt_create does for the whole film (include/gdpt.h:
+        # the host's better tree pays from ~2e8 pixel-samples).  Device builds are per rank (9 ms, no host cores involved);
+        # a host build is done once on rank 0 and broadcast from 4 ranks up (N builds side by side share the box's cores).
+        share_of_work = scene.width * scene.height * max(1, scene.options.samples_per_pixel) / self.world
+        self.bvh_builder = "device" if share_of_work < 2e8 else "host"
         if share_bvh == "auto":
             share_bvh = self.world >= 4
-        if share_bvh and self.world > 1 and device not in scene._ctx:
-            self.ctx = scene.context(device, build_bvh=self.rank == 0)
+        if device in scene._ctx:
+            self.ctx = scene.context(device)
+        elif self.bvh_builder == "device":
+            self.ctx = scene.context(device, bvh="device")
+        elif share_bvh and self.world > 1:
+            self.ctx = scene.context(device, build_bvh=self.rank == 0, bvh="host")
             share_bvh_from_rank0(scene, device, dist, torch)
         else:
-            self.ctx = scene.context(device)
+            self.ctx = scene.context(device, bvh="host")
         n = scene.height * scene.width * 3
         dev = torch.device("cuda", device)
         self.acc = [torch.zeros(n, dtype=torch.float64, device=dev) for _ in range(5)]
@@ -241,6 +250,11 @@ class DistributedRenderer:
         if solver == "distributed" and (self.world == 1 or any(b[1] <= b[0] for b in self.bands)):
             solver = "gather"
         self.solver = solver
+        # gather solve: the film is shared as interleaved 4-row strips (strip i belongs to rank i mod N — what the reference's
+        # dynamic tile queue achieves, parallel.cpp:183-237): contiguous bands of Sponza differ by up to 8 % in cost (sky
+        # openings and arches against the floor), strips by well under 1 %.  The distributed solve needs contiguous row bands.
+        self.interleave = solver == "gather" and self.world > 1
+        self.last_ms = {}
         self.dsolve = None
         if solver == "distributed":
             self.dsolve = DistributedPoisson(scene.width, scene.height, self.bands, dist, torch, CudaStages(self.ctx, _capi), device=dev)
@@ -266,35 +280,60 @@ class DistributedRenderer:
             return img.cpu().numpy().reshape(self.scene.height, self.scene.width, 3)
         return None
 
+    def _to_host(self, named):
+        """Device images -> page-locked host arrays from the binding's pinned pool (_capi.pinned_empty: the blocks go back to
+        the pool when the arrays are collected), so the copy runs at PCIe speed."""
+        torch = self.torch
+        shape = (self.scene.height, self.scene.width, 3)
+        out = {}
+        for k, v in named:
+            a = self._capi.pinned_empty(shape)
+            torch.from_numpy(a.reshape(-1)).copy_(v, non_blocking=True)
+            out[k] = a
+        torch.cuda.current_stream().synchronize()
+        return out
+
     def render(self, spp, precision="f32", seed=0, data_cost=0.04, to_host=False, offsets="reference"):
+        """Times of the last call (CUDA events on this rank's stream, ms) are left in self.last_ms:
+        render (this rank's share of the samples), exchange (reduce / halo + transposes + gather), solve, copy."""
         from .render import _params
         lib, check = self._capi.lib(), self._capi.check
         torch = self.torch
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
         y0, y1 = self.bands[self.rank]
         for b in self.acc:
             b.zero_()
         torch.cuda.current_stream().synchronize()
-        if y1 > y0:
+        ev[0].record()
+        if self.interleave:
+            p = _params(self.scene, spp=spp, precision=precision, seed=seed, offsets=offsets, strips=(self.world, self.rank))
+        elif y1 > y0:
             p = _params(self.scene, spp=spp, precision=precision, seed=seed, rows=(y0, y1), offsets=offsets)
             if y0 == 0:
                 p.y0 = 0
+        else:
+            p = None
+        if p is not None:
             ptrs = [C.c_void_p(b.data_ptr()) for b in self.acc]
             check(lib.gdpt_render_accumulate_device(self.ctx, C.byref(p), *ptrs))
             check(lib.gdpt_synchronize(self.ctx))
+        ev[1].record()
         res = None
         if self.dsolve is not None:
             a = self.acc
             self.dsolve.solve(a[0], a[1], a[2], a[3], a[4], self.cx, self.cy, self.out, alpha=data_cost)
             self.dsolve.gather_rows([a[0], self.cx, self.cy, self.out] if to_host else [self.out], dst=0)
             torch.cuda.current_stream().synchronize()
+            ev[3].record()
             if self.rank == 0 and to_host:
-                shape = (self.scene.height, self.scene.width, 3)
-                res = {k: v.cpu().numpy().reshape(shape) for k, v in
-                       (("primal", a[0]), ("dx", self.cx), ("dy", self.cy), ("poisson", self.out))}
+                res = self._to_host((("primal", a[0]), ("dx", self.cx), ("dy", self.cy), ("poisson", self.out)))
+            ev[4].record(); ev[4].synchronize()
+            self.last_ms = {"render": ev[0].elapsed_time(ev[1]), "exchange+solve": ev[1].elapsed_time(ev[3]), "copy": ev[3].elapsed_time(ev[4])}
             return res
         if self.world > 1:
             reduce_bands(self.acc, self.dist, dst=0)
             torch.cuda.current_stream().synchronize()
+        ev[2].record()
         if self.rank == 0:
             w, h = self.scene.width, self.scene.height
             a = self.acc
@@ -304,8 +343,12 @@ class DistributedRenderer:
             check(lib.gdpt_poisson_device(self.ctx, w, h, C.c_void_p(a[0].data_ptr()), C.c_void_p(self.cx.data_ptr()),
                                           C.c_void_p(self.cy.data_ptr()), data_cost, C.c_void_p(self.out.data_ptr())))
             check(lib.gdpt_synchronize(self.ctx))
+            ev[3].record()
             if to_host:
-                shape = (h, w, 3)
-                res = {k: v.cpu().numpy().reshape(shape) for k, v in
-                       (("primal", a[0]), ("dx", self.cx), ("dy", self.cy), ("poisson", self.out))}
+                res = self._to_host((("primal", a[0]), ("dx", self.cx), ("dy", self.cy), ("poisson", self.out)))
+        else:
+            ev[3].record()
+        ev[4].record(); ev[4].synchronize()
+        self.last_ms = {"render": ev[0].elapsed_time(ev[1]), "exchange": ev[1].elapsed_time(ev[2]), "solve": ev[2].elapsed_time(ev[3]),
+                        "copy": ev[3].elapsed_time(ev[4])}
         return res

@@ -23,7 +23,7 @@ class RenderResult(dict):
 
 
 def _params(scene, spp=None, precision="f64", seed=0, sample0=0, max_depth=None, rr_depth=None, data_cost=0.04,
-            rows=None, wave_samples=0, offsets="reference"):
+            rows=None, wave_samples=0, offsets="reference", strips=None):
     p = _capi.GdptRenderParams()
     p.spp = int(spp if spp is not None else scene.options.samples_per_pixel)
     p.sample0 = int(sample0)
@@ -35,6 +35,7 @@ def _params(scene, spp=None, precision="f64", seed=0, sample0=0, max_depth=None,
     p.y0, p.y1 = (0, 0) if rows is None else (int(rows[0]), int(rows[1]))
     p.wave_samples = int(wave_samples)
     p.offset_mode = {"reference": _capi.OFFSETS_REFERENCE, "shift": _capi.OFFSETS_SHIFT}[offsets]
+    p.strip_count, p.strip_phase = (0, 0) if strips is None else (int(strips[0]), int(strips[1]))    # (count, phase): every count-th 4-row strip
     return p
 
 
@@ -44,18 +45,43 @@ def stats(scene, device=0):
     return {k: getattr(s, k) for k, _ in s._fields_}
 
 
-def gradient_path_render(scene, device=0, outputs=("primal", "dx", "dy", "poisson"), **kw):
-    """gradient_path_render (render.cpp:257-370) on the GPU; returns all four buffers."""
+def gradient_path_render(scene, device=0, outputs=("primal", "dx", "dy", "poisson"), pinned=True, **kw):
+    """gradient_path_render (render.cpp:257-370) on the GPU; returns all four buffers (page-locked host arrays by default)."""
     ctx = scene.context(device)
     p = _params(scene, **kw)
     imgs = _capi.GdptImages()
     res = RenderResult()
     for name in outputs:
-        a = np.zeros((scene.height, scene.width, 3), dtype=np.float64)
+        a = _capi.pinned_empty((scene.height, scene.width, 3)) if pinned else np.empty((scene.height, scene.width, 3), dtype=np.float64)
         res[name] = a
         setattr(imgs, name, _capi.as_dp(a))
     _capi.check(_capi.lib().gdpt_render(ctx, C.byref(p), C.byref(imgs)))
     res["stats"] = stats(scene, device)
+    return res
+
+
+def gradient_path_render_multi(scene, n_gpus, outputs=("primal", "dx", "dy", "poisson"), devices=None, **kw):
+    """gradient_path_render over `n_gpus` GPUs of this box inside this process (gdpt_multi_*: one host thread per device,
+    interleaved 4-row strips, NVLink peer copies to the first device, merge + solve there)."""
+    lib = _capi.lib()
+    h = C.c_void_p()
+    d = scene.desc()
+    dev = (C.c_int32 * n_gpus)(*devices) if devices is not None else None
+    _capi.check(lib.gdpt_multi_create(C.byref(d), n_gpus, dev, C.byref(h)))
+    try:
+        p = _params(scene, **kw)
+        imgs = _capi.GdptImages()
+        res = RenderResult()
+        for name in outputs:
+            a = _capi.pinned_empty((scene.height, scene.width, 3))
+            res[name] = a
+            setattr(imgs, name, _capi.as_dp(a))
+        _capi.check(lib.gdpt_multi_render(h, C.byref(p), C.byref(imgs)))
+        s = _capi.GdptStats()
+        _capi.check(lib.gdpt_multi_get_stats(h, C.byref(s)))
+        res["stats"] = {k: getattr(s, k) for k, _ in s._fields_}
+    finally:
+        lib.gdpt_multi_destroy(h)
     return res
 
 

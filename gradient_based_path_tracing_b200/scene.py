@@ -187,13 +187,15 @@ class Scene:
             d.envmap_to_local = _capi.as_dp(dbl("envmap.to_local", 4))
         return d
 
-    def context(self, device=0, build_bvh=True):
+    def context(self, device=0, build_bvh=True, bvh=None):
         """gdpt_create on `device` (once per scene and device).  build_bvh=False: gdpt_create_ex(GDPT_CREATE_NO_BVH) — the
         caller hands a tree over with adopt_bvh() before rendering (multi.DistributedRenderer broadcasts rank 0's)."""
         if device not in self._ctx:
             h = C.c_void_p()
             d = self.desc()
-            _capi.check(_capi.lib().gdpt_create_ex(C.byref(d), device, 0 if build_bvh else _capi.CREATE_NO_BVH, C.byref(h)))
+            flags = 0 if build_bvh else _capi.CREATE_NO_BVH      # bvh: None (chosen from the planned work) | "host" | "device"
+            flags |= {None: 0, "host": _capi.CREATE_BVH_HOST, "device": _capi.CREATE_BVH_DEVICE}[bvh]
+            _capi.check(_capi.lib().gdpt_create_ex(C.byref(d), device, flags, C.byref(h)))
             self._ctx[device] = h
         return self._ctx[device]
 

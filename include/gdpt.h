@@ -17,6 +17,7 @@
  */
 #ifndef GDPT_H
 #define GDPT_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -93,6 +94,9 @@ typedef struct {
     int32_t y0, y1;           /* row band [y0,y1) to render; y1 <= 0: whole image */
     int32_t wave_samples;     /* samples per pixel per wave; 0: auto */
     int32_t offset_mode;      /* GDPT_OFFSETS_*; 0 = the reference's semantics */
+    int32_t strip_count;      /* > 1: rows [y0,y1) are cut into 4-row strips and this call renders the strips whose index is */
+    int32_t strip_phase;      /*      strip_phase (mod strip_count) — interleaved sharing of one film between GPUs (the reference's
+                               *      dynamic tile queue, parallel.cpp:183-237, balances load the same way); <= 1: every row */
 } gdpt_render_params;
 
 /* Host output images; any pointer may be NULL.  primal/dx/dy/poisson = c/cx/cy/out of render.cpp:336-353. */
@@ -108,6 +112,9 @@ const char *gdpt_last_error(void);
 int gdpt_device_count(void);
 
 #define GDPT_CREATE_NO_BVH 1 /* gdpt_create_ex: everything but the BVH build */
+#define GDPT_CREATE_BVH_HOST 2   /* build the tree with the host's binned-SAH builder + triangle pre-splitting (best tree, ~45 ms for Sponza) */
+#define GDPT_CREATE_BVH_DEVICE 4 /* build it on the device (PLOC, ~9 ms, 5-6 % slower traversal); neither flag: chosen from the planned work
+                                  * width * height * samples_per_pixel (device build below 2e8 pixel-samples) */
 
 /* Upload the scene to `device`, rebuild mip chains, build the BVH (replaces Scene::Scene's
  * Embree registration/commit, scene.cpp:19-34). */
@@ -122,6 +129,10 @@ int gdpt_bvh_info(gdpt_ctx *ctx, int64_t *n_nodes, int64_t *n_prims, int32_t *de
 /* Copy a BVH (device or host pointers) into a context created with GDPT_CREATE_NO_BVH. */
 int gdpt_bvh_adopt(gdpt_ctx *ctx, const void *d_nodes, int64_t n_nodes, const void *d_prims, int64_t n_prims, int32_t depth);
 void gdpt_destroy(gdpt_ctx *ctx);
+/* Page-locked host memory for the caller's image buffers (cudaMallocHost / cudaFreeHost): gdpt_render copies its four images
+ * into pinned buffers at PCIe speed and into pageable ones (what `new[]` at render.cpp:336-338 gives) several times slower. */
+int gdpt_host_alloc(size_t bytes, void **out);
+void gdpt_host_free(void *p);
 /* scene bounds radius / centre as scene.cpp:30-34 derives them (for parity checks) */
 int gdpt_scene_bounds(gdpt_ctx *ctx, double *radius_center4);
 
@@ -179,12 +190,24 @@ int gdpt_poisson_dist_columns(gdpt_ctx *ctx, const gdpt_dist_geom *geom, double 
                               const double *d_recv, double *d_send_back);
 int gdpt_poisson_dist_rows_inverse(gdpt_ctx *ctx, const gdpt_dist_geom *geom, const double *d_recv_back, double *d_out);
 
+/* ---- several GPUs of one box behind the ABI: gradient_path_render with the tile loop of render.cpp:271-331 spread over
+ * n_devices GPUs inside this process (one host thread per device; scene replicated, BVH built once and copied device to
+ * device; film shared as interleaved 4-row strips; the strips gathered on the first device over NVLink peer copies; merge and
+ * solve there).  devices == NULL: 0 .. n_devices-1.  params: as gdpt_render, with y0 / y1 / strip_* left 0. ---- */
+typedef struct gdpt_multi gdpt_multi;
+int gdpt_multi_create(const gdpt_scene_desc *scene, int n_devices, const int *devices, gdpt_multi **out);
+int gdpt_multi_render(gdpt_multi *m, const gdpt_render_params *params, gdpt_images *out);
+int gdpt_multi_get_stats(gdpt_multi *m, gdpt_stats *out);      /* counters summed over the devices */
+int gdpt_multi_device_count(gdpt_multi *m);
+void gdpt_multi_destroy(gdpt_multi *m);
+
 int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out);
 /* Scheduling / tuning knobs of a context (no effect on results; no counterpart in the reference, whose only knob is -t threads,
  * src/main.cpp:20-23).  "async_waves" 1|0: launch the waves of a render from the first wave's measured path counts without
  * per-bounce host read-backs (default 1); "wave_streams" 1..4: waves in flight on separate streams (default 2); "time_kernels"
  * 1|0: keep the host-synchronised loop and fill gdpt_stats.ms_trace / ms_shade with per-kernel event times (default 0: those two
- * fields stay 0); "tail_paths" n; "sort_rays" 1|0; "trace_variant" v; "shade_variant" v. */
+ * fields stay 0); "poisson_fft" 1|0: the O(N log N) form of the DCT-I in fourierSolve's
+ * replacement or the dense-matrix form (default 1; films under 16 pixels a side always take the matrix form); "tail_paths" n; "sort_rays" 1|0; "trace_variant" v; "shade_variant" v. */
 int gdpt_set_option(gdpt_ctx *ctx, const char *name, int value);
 /* Run all of the context's work on the caller's CUDA stream (a cudaStream_t; NULL restores the context's own). */
 int gdpt_set_stream(gdpt_ctx *ctx, void *cuda_stream);

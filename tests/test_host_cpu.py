@@ -290,3 +290,19 @@ def test_cpp_host_exr_and_pfm_writers(tmp_path, w, h):
     head = ("PF\n%d %d\n-1\n" % (w, h)).encode()
     assert b.startswith(head)
     assert np.array_equal(np.frombuffer(b[len(head):], dtype=np.float32).reshape(h, w, 3), img.astype(np.float32))
+
+
+# ------------------------------------------------------------------ FFT form of the DCT-I (device functions compiled for the host)
+def test_fft_dct1_device_functions_on_the_host(tmp_path):
+    """csrc/gdpt_poisson_fft.cuh — the radix-4 forward / inverse FFT passes and the Bluestein DCT-I line transform the Poisson
+    kernels run in shared memory — compiled for the host with one emulated thread (tests/host/fft_check.cpp) against the
+    O(N^2) definition of FFTW's REDFT00, at the film sizes of the configs (incl. odd log2 P and the 4097 limit)."""
+    import json
+    import subprocess
+    exe = tmp_path / "fft_check"
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "gradient_based_path_tracing_b200", "csrc"),
+                           os.path.join(ROOT, "tests", "host", "fft_check.cpp"), "-o", str(exe)])
+    sizes = [16, 17, 33, 64, 90, 512, 575, 768, 1080, 1920, 2160, 3840, 4097]
+    r = json.loads(subprocess.check_output([str(exe)] + [str(n) for n in sizes], timeout=300))
+    for n in sizes:
+        assert r[str(n)]["roundtrip"] < 1e-14 and r[str(n)]["dct_rel_err"] < 1e-13, (n, r[str(n)])

@@ -77,3 +77,60 @@ def test_distributed_solve_equals_gather_solve_nccl(tmp_path, world):
     outs = [p.communicate(timeout=600)[0].decode() for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert "OK" in outs[0] and "PATH OK" in outs[0]
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_multi_gpu_behind_the_c_abi(g, tmp_path, n):
+    """gdpt_multi_* (one process, one host thread per device, interleaved strips, NVLink peer copies) equals one GPU:
+    through the Python binding and through `lajolla_b200 -gpus n`."""
+    import numpy as np
+    if _gpus() < n:
+        pytest.skip("needs %d GPUs" % n)
+    for name, prec in (("cbox_gdpt", "f64"), ("sponza_small", "f32")):
+        sc = g.Scene.named(name)
+        one = g.gradient_path_render(sc, spp=2, precision=prec)
+        many = g.gradient_path_render_multi(sc, n, spp=2, precision=prec)
+        for k in ("primal", "dx", "dy"):
+            assert np.allclose(getattr(one, k), getattr(many, k), rtol=1e-12, atol=1e-15), (name, k)
+        assert np.linalg.norm(one.poisson - many.poisson) <= 1e-10 * np.linalg.norm(one.poisson)
+        assert many.stats["paths"] >= sc.width * sc.height * 2
+        sc.close()
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "lajolla_b200")
+    out = tmp_path / "m.pfm"
+    r = subprocess.run([exe, "-gpus", str(n), "-o", str(out), "-spp", "2", "-precision", "f64", os.path.join(ROOT, "scenes", "cbox_gdpt.gdpt.z")], capture_output=True, timeout=600)
+    assert r.returncode == 0, r.stderr.decode()
+    from test_parity_gpu import _read_pfm
+    sc = g.Scene.named("cbox_gdpt")
+    want = g.gradient_path_render(sc, spp=2, precision="f64")
+    assert np.allclose(_read_pfm(str(out)), want.poisson.astype(np.float32), rtol=1e-6, atol=1e-9)
+
+
+def test_multi_gpu_abi_on_one_device_and_bad_arguments(g):
+    """n = 1 is the single-GPU render; more devices than present, or a band inside the parameters, are refused."""
+    import ctypes as C
+    import numpy as np
+    sc = g.Scene.named("cbox_gdpt_64")
+    one = g.gradient_path_render(sc, spp=3, precision="f64")
+    m = g.gradient_path_render_multi(sc, 1, spp=3, precision="f64")
+    assert np.allclose(one.primal, m.primal, rtol=1e-12, atol=1e-15) and np.allclose(one.poisson, m.poisson, rtol=1e-9, atol=1e-12)
+    with pytest.raises(g._capi.GdptError):
+        g.gradient_path_render_multi(sc, _gpus() + 1, spp=1)
+    with pytest.raises(g._capi.GdptError):
+        g.gradient_path_render_multi(sc, 1, spp=1, rows=(0, 16))
+
+
+def test_interleaved_strips_compose_to_the_full_image(g):
+    """gdpt_render_params.strip_count / strip_phase: the strips of all phases sum to the whole film (what the multi-GPU paths
+    rely on), also when the film height is not a multiple of the strip height times the count."""
+    import numpy as np
+    sc = g.Scene.named("sponza_small")          # 160 x 90: 23 strips, the last one 2 rows
+    full = g.gradient_path_render(sc, spp=2, precision="f64", outputs=("primal",)).primal
+    for n in (2, 3, 5):
+        acc = np.zeros_like(full)
+        for k in range(n):
+            part = g.gradient_path_render(sc, spp=2, precision="f64", outputs=("primal",), strips=(n, k)).primal
+            rows = np.abs(part).sum(axis=(1, 2)) > 0
+            owned = np.array([(y // 4) % n == k for y in range(sc.height)])
+            assert not (rows & ~owned).any()
+            acc += part
+        assert np.allclose(acc, full, rtol=1e-12, atol=1e-15), n

@@ -429,3 +429,34 @@ def test_bvh_can_be_built_once_and_adopted(g):
         assert np.allclose(getattr(ra, k), getattr(rb, k), rtol=1e-12, atol=1e-15), k
     assert np.array_equal(g.scene_bounds(a), g.scene_bounds(b))
     b.close()
+
+
+@pytest.mark.parametrize("name", ["sponza_small", "veach_mi_small", "cbox_gdpt_64"])
+def test_host_and_device_bvh_builders_agree(g, name):
+    """gdpt_create_ex(GDPT_CREATE_BVH_HOST) — binned SAH + pre-splitting on the host — and GDPT_CREATE_BVH_DEVICE — PLOC on the
+    GPU (csrc/gdpt_bvh_gpu.cu): different trees, the same closest hits (the hit rule does not depend on the traversal order
+    but for depth ties decided in float), both equal to the reference's ids; and the device build is reproducible."""
+    z = golden("intersect_%s.npz" % name)
+    out = {}
+    for builder in ("host", "device", "device2"):
+        sc = g.Scene.named(name)
+        sc.context(0, bvh=builder[:6])
+        nn, npr, depth, _, _ = sc.bvh_info(0)
+        ids, vtx = g.intersect(sc, z["rays"], z["rdiff"], precision="f64")
+        ids2, vtx2 = g.intersect(sc, z["rays2"], None, precision="f64")
+        img = g.gradient_path_render(sc, spp=2, precision="f64", outputs=("primal",)).primal
+        out[builder] = (ids, ids2, vtx, img, (nn, npr, depth), vtx2)
+        sc.close()
+    assert out["device"][4] == out["device2"][4] and np.array_equal(out["device"][3], out["device2"][3])
+    for k, kv in ((0, 2), (1, 5)):
+        # EXACT mode decides "closer" in double with the id tie rule, so the two trees must give the same hit but where the
+        # float box test lets one tree skip a primitive at the very same depth (a handful of rays at most)
+        diff = (out["host"][k] != out["device"][k]).any(axis=1)
+        tie = diff & (np.abs(out["host"][kv][:, 22] - out["device"][kv][:, 22]) <= 1e-6 * np.abs(out["host"][kv][:, 22]))
+        assert (diff & ~tie).sum() == 0 and diff.mean() <= 2e-3, (name, k, diff.sum(), (diff & ~tie).sum())
+        want = z["ids"] if k == 0 else z["ids2"]
+        assert ((out["device"][k] != want).any(axis=1)).mean() <= 2e-2
+    same = (out["host"][0] == out["device"][0]).all(axis=1) & (out["host"][0][:, 0] >= 0)
+    assert np.allclose(out["host"][2][same], out["device"][2][same], rtol=1e-12, atol=1e-12, equal_nan=True)
+    close = np.isclose(out["host"][3], out["device"][3], rtol=1e-9, atol=1e-12)
+    assert close.mean() > 0.999

@@ -25,6 +25,8 @@ if "sched" in what:
     for w in (1, 4):
         run("async, 3 streams, %d spp per wave" % w, {"async_waves": 1, "wave_streams": 3}, wave=w)
     run("async, 2 streams, trace variant 0 (two pop sites)", {"async_waves": 1, "wave_streams": 2, "trace_variant": 0})
+    run("async, 2 streams, trace variant 120000 (leaf children tested in the node step)", {"async_waves": 1, "wave_streams": 2, "trace_variant": 120000})
+    run("async, 2 streams, trace variant 40000 again", {"async_waves": 1, "wave_streams": 2, "trace_variant": 40000})
     run("async, 2 streams, f64", {"async_waves": 1, "wave_streams": 2}, prec="f64")
     run("async, 3 streams, f64", {"async_waves": 1, "wave_streams": 3}, prec="f64")
 if "records" in what:
@@ -50,3 +52,26 @@ if "e2e" in what:
         sc.close(); t5 = time.perf_counter()
         print("rep %d: Scene() %.3f  gdpt_create %.3f  first render(8spp) %.3f  second render %.3f  destroy %.3f   stats %s" % (
             rep, t1 - t0, t2 - t1, t3 - t2, t4 - t3, t5 - t4, {k: round(v, 1) for k, v in r.stats.items() if k.startswith("ms_")}), flush=True)
+if "bvh" in what:
+    import ctypes as C
+    from gradient_based_path_tracing_b200 import _capi
+    from gradient_based_path_tracing_b200.render import _params
+    base = g.Scene.named("sponza_1080p")
+    os.environ["GDPT_VERBOSE"] = "1"
+    for mode, split, radius, leaf in (("host", "2", 16, 4), ("gpu", "0", 8, 4), ("gpu", "2", 8, 4), ("gpu", "2", 16, 4), ("gpu", "1", 8, 4), ("gpu", "3", 8, 4), ("gpu", "2", 8, 2)):
+        os.environ["GDPT_BVH"] = mode; os.environ["GDPT_BVH_SPLIT"] = split; os.environ["GDPT_PLOC_RADIUS"] = str(radius); os.environ["GDPT_BVH_MAX_LEAF"] = str(leaf)
+        for rep in range(2):
+            sc = g.Scene(base.a)
+            t0 = time.perf_counter(); sc.context(0); t1 = time.perf_counter()
+        nn, npr, depth, _, _ = sc.bvh_info(0)
+        g.gradient_path_render(sc, spp=4, precision="f32", outputs=("primal",))
+        t2 = time.perf_counter()
+        r = g.gradient_path_render(sc, spp=32, precision="f32", outputs=("primal",))
+        dt = time.perf_counter() - t2
+        cnt = np.zeros(3)
+        p = _params(sc, spp=1, precision="f32")
+        _capi.check(_capi.lib().gdpt_traversal_counts(sc.context(0), C.byref(p), _capi.as_dp(cnt)))
+        print("BVH %-4s split %s radius %d leaf %d: create %.1f ms, %d nodes, %d prim records, depth %d; 32 spp %.1f ms (%.1f Mpaths/s), %.2f nodes + %.2f prims per ray, mean %.6f" % (
+            mode, split, radius, leaf, (t1 - t0) * 1e3, nn, npr, depth, dt * 1e3, 5 * 1920 * 1080 * 32 / dt / 1e6, cnt[0], cnt[1], r.primal.mean()), flush=True)
+        sc.close()
+    del os.environ["GDPT_BVH"], os.environ["GDPT_BVH_SPLIT"], os.environ["GDPT_VERBOSE"], os.environ["GDPT_PLOC_RADIUS"], os.environ["GDPT_BVH_MAX_LEAF"]
