@@ -414,6 +414,28 @@ def run_native(args):
                "e2e": {"value": paths / (float(fe.item()) * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": float(fe.item()), "steps": 1},
                "note": "same workload in GDPT_PRECISION_F64 (double traversal tests + shading, -fmad=false): the mode whose per-sample records equal the compiled reference's"}
 
+    # (every rank takes part: at N > 1 a render is a collective)
+    # kernel durations: a separate pass of the same workload at fewer spp with the host-synchronised wave loop and CUDA events
+    # around every k_trace / shade launch on the launching stream (in the timed region above two waves overlap on two
+    # streams without read-backs, where per-launch events would time the neighbour's kernels too)
+    check(lib.gdpt_set_option(R.ctx, b"time_kernels", 1))
+    roof_spp = min(spp, 32)
+    R.render(2, precision=args.precision, offsets=args.offsets)
+    barrier()
+    r0 = stats()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
+    R.render(roof_spp, precision=args.precision, offsets=args.offsets)
+    g1.record()
+    barrier()
+    r1 = stats()
+    check(lib.gdpt_set_option(R.ctx, b"time_kernels", 0))
+    ms_pass = g0.elapsed_time(g1)
+    rays = r1["rays_traced"] - r0["rays_traced"]
+    ms_trace = r1["ms_trace"] - r0["ms_trace"]
+    ms_shade = r1["ms_shade"] - r0["ms_shade"]
+    rays_step = (s1["rays_traced"] - s0["rays_traced"]) / args.steps
+
     if rank == 0:
         # ---- roofline of the traversal kernel (k_trace): algorithmic bytes per ray from a counting pass
         peaks, how = measured_peaks()
@@ -421,37 +443,17 @@ def run_native(args):
         cnt = np.zeros(3)
         check(lib.gdpt_traversal_counts(R.ctx, C.byref(p), _capi.as_dp(cnt)))
         bytes_per_ray = 32 + 20 + 128.0 * cnt[0] + 48.0 * cnt[1]
-        # kernel durations: a separate pass of the same workload at fewer spp with the host-synchronised wave loop and CUDA events
-        # around every k_trace / shade launch on the launching stream (in the timed region above two waves overlap on two
-        # streams without read-backs, where per-launch events would time the neighbour's kernels too)
-        check(lib.gdpt_set_option(R.ctx, b"time_kernels", 1))
-        roof_spp = min(spp, 32)
-        R.render(2, precision=args.precision, offsets=args.offsets)
-        barrier()
-        r0 = stats()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record()
-        R.render(roof_spp, precision=args.precision, offsets=args.offsets)
-        g1.record()
-        barrier()
-        r1 = stats()
-        check(lib.gdpt_set_option(R.ctx, b"time_kernels", 0))
-        ms_pass = g0.elapsed_time(g1)
-        rays = r1["rays_traced"] - r0["rays_traced"]
-        ms_trace = r1["ms_trace"] - r0["ms_trace"]
-        ms_shade = r1["ms_shade"] - r0["ms_shade"]
-        rays_step = (s1["rays_traced"] - s0["rays_traced"]) / args.steps
         achieved = rays * bytes_per_ray / (ms_trace * 1e-3) / 1e9 if ms_trace > 0 else None
         l2 = np.zeros(1)
         try:
             check(lib.gdpt_measure_l2_read(local, 48, 40, _capi.as_dp(l2)))     # 48 MB buffer, L2-resident
         except Exception:
             l2[0] = 0.0
-        # committed ncu evidence for the same kernel (profiles/r1_k_trace_*.json; one --set full capture per launch type)
+        # committed ncu evidence for the same kernel (profiles/r2_k_trace_*.json; one --set full capture per launch type)
         ncu = {}
         for tag in ("bounce", "primary"):
             try:
-                ncu[tag] = json.load(open(os.path.join(ROOT, "profiles", "r1_k_trace_%s.json" % tag)))
+                ncu[tag] = json.load(open(os.path.join(ROOT, "profiles", "r2_k_trace_%s.json" % tag)))
             except Exception:
                 pass
         nb = ncu.get("bounce")

@@ -128,7 +128,7 @@ struct gdpt_ctx {
     gdpt::WaveSlot slot[MAX_SLOTS];
     gdpt::WaveCalibration cal;
     bool async_waves = true;          // launch waves from the calibration without per-bounce host syncs (gdpt_set_option "async_waves")
-    int wave_streams = 2;             // waves in flight on separate streams (1..MAX_SLOTS; "wave_streams")
+    int wave_streams = 3;             // waves in flight on separate streams (1..MAX_SLOTS; "wave_streams"): 2 -> 3 is worth 1-2 %, 4 nothing more
     cudaEvent_t ev_fork = nullptr;
     unsigned forked = 0;              // bit k: slot k's stream has work of the current accumulation in flight
     int wave_index = 0;

@@ -35,7 +35,9 @@ static int ensure_poisson(gdpt_ctx *c, int w, int h) {
 
 // ---------------------------------------------------------------- FFT form (gdpt_poisson_fft.cuh)
 constexpr int FFT_MIN_N = 16, FFT_MAX_P = 8192;      // P complex + N real of shared memory per block: 160 KB at P = 8192 (N <= 4097)
-static size_t fft_smem(int P, int N) { return (size_t)P * sizeof(double2) + (size_t)((N + 1) & ~1) * sizeof(double); }
+static int ilog2(int P) { int l = 0; while ((1 << l) < P) l++; return l; }
+// P complex (the transform) + the pass twiddles + N real (the line) of shared memory per block
+static size_t fft_smem(int P, int N) { return ((size_t)P + fft_twiddle_count(P, ilog2(P))) * sizeof(double2) + (size_t)((N + 1) & ~1) * sizeof(double); }
 static bool fft_eligible(int N) {
     if (N < FFT_MIN_N) return false;
     int P = 16; while (P < 2 * (N - 1) - 1) P <<= 1;
@@ -45,7 +47,7 @@ static int ensure_plan(gdpt_ctx *c, DctPlanBufs &b, int N) {
     if (b.N == N) return 0;
     const int M = N - 1;
     int P = 16, logP = 4; while (P < 2 * M - 1) { P <<= 1; logP++; }
-    if (int r = b.tw.ensure((size_t)P * sizeof(double2))) return r;
+    if (int r = b.tw.ensure((size_t)std::max(1, fft_twiddle_count(P, logP)) * sizeof(double2))) return r;
     if (int r = b.chirp.ensure((size_t)M * sizeof(double2))) return r;
     if (int r = b.wpost.ensure((size_t)M * sizeof(double2))) return r;
     if (int r = b.bhat.ensure((size_t)P * sizeof(double2))) return r;
@@ -55,7 +57,7 @@ static int ensure_plan(gdpt_ctx *c, DctPlanBufs &b, int N) {
         GD_CUDA(cudaFuncSetAttribute(k_dct_plan_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FFT_MAX_P * sizeof(double2))));
         attr_set = true;
     }
-    k_dct_plan_tables<<<blocks_for(P, 256), 256, 0, c->stream>>>(M, P, b.tw.as<double2>(), b.chirp.as<double2>(), b.wpost.as<double2>());
+    k_dct_plan_tables<<<blocks_for(P, 256), 256, 0, c->stream>>>(M, P, logP, b.tw.as<double2>(), b.chirp.as<double2>(), b.wpost.as<double2>());
     k_dct_plan_filter<<<1, FFT_THREADS, (size_t)P * sizeof(double2), c->stream>>>(M, P, logP, b.tw.as<double2>(), b.chirp.as<double2>(), b.bhat.as<double2>());
     c->stats.kernel_launches += 2;
     GD_CUDA(cudaGetLastError());
@@ -83,20 +85,21 @@ static int poisson_device_fft(gdpt_ctx *c, int w, int h, const double *d_u, cons
     double *A = pc.work.as<double>(), *B = pc.work2.as<double>();
     const int nb = SM_COUNT * 8;
     k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, h, 0, h, d_u, d_gx, d_gy, alpha, A, pc.partial.as<double>());
-    k_dc_reduce<<<1, 32, 0, st>>>(nb, pc.partial.as<double>(), pc.dc.as<double>());
+    k_dc_reduce<<<1, 96, 0, st>>>(nb, pc.partial.as<double>(), pc.dc.as<double>());
     const DctPlan pw = plan_of(pc.plan_w), ph = plan_of(pc.plan_h);
     DctArgs a; memset(&a, 0, sizeof(a));
     a.plane_stride = (long long)w * h; a.img_w = w; a.img_h = h; a.alpha = alpha; a.dc = pc.dc.as<double>();
     a.scale = 4.0 * (w - 1) * (h - 1); a.out = d_out;
     // rows, forward
     a.mode = DCT_STORE; a.count = 3 * h; a.per_plane = h; a.line_stride = w; a.elem_stride = 1;
-    k_dct1_fft<<<a.count, FFT_THREADS, fft_smem(pw.P, w), st>>>(pw, a, A, B);
+    const int grid_cap = SM_COUNT * 2;      // persistent blocks: the pass twiddles are staged once per block, the lines are looped over
+    k_dct1_fft<<<std::min(a.count, grid_cap), FFT_THREADS, fft_smem(pw.P, w), st>>>(pw, a, A, B);
     // columns: forward, divide, inverse — in place
     a.mode = DCT_COLUMNS; a.count = 3 * w; a.per_plane = w; a.line_stride = 1; a.elem_stride = w;
-    k_dct1_fft<<<a.count, FFT_THREADS, fft_smem(ph.P, h), st>>>(ph, a, B, B);
+    k_dct1_fft<<<std::min(a.count, grid_cap), FFT_THREADS, fft_smem(ph.P, h), st>>>(ph, a, B, B);
     // rows, inverse + scale + interleave
     a.mode = DCT_SCALE_INTERLEAVE; a.count = 3 * h; a.per_plane = h; a.line_stride = w; a.elem_stride = 1;
-    k_dct1_fft<<<a.count, FFT_THREADS, fft_smem(pw.P, w), st>>>(pw, a, B, nullptr);
+    k_dct1_fft<<<std::min(a.count, grid_cap), FFT_THREADS, fft_smem(pw.P, w), st>>>(pw, a, B, nullptr);
     c->stats.kernel_launches += 5;
     GD_CUDA(cudaGetLastError());
     return 0;
@@ -111,7 +114,7 @@ int poisson_device(gdpt_ctx *c, int w, int h, const double *d_u, const double *d
     double *A = pc.work.as<double>(), *B = pc.work2.as<double>();
     const int nb = SM_COUNT * 8;
     k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, h, 0, h, d_u, d_gx, d_gy, alpha, A, pc.partial.as<double>());
-    k_dc_reduce<<<1, 32, 0, st>>>(nb, pc.partial.as<double>(), pc.dc.as<double>());
+    k_dc_reduce<<<1, 96, 0, st>>>(nb, pc.partial.as<double>(), pc.dc.as<double>());
     Epilogue ep; memset(&ep, 0, sizeof(ep));
     ep.img_w = w; ep.img_h = h; ep.alpha = alpha; ep.dc = pc.dc.as<double>(); ep.out = d_out;
     ep.scale = 4.0 * (w - 1) * (h - 1);
@@ -159,7 +162,7 @@ int poisson_dist_rows_forward(gdpt_ctx *c, const gdpt_dist_geom *g, const double
     const int w = g->w, rows = g->y1 - g->y0, nb = SM_COUNT * 8;
     if (int r = pc.work.ensure(std::max<size_t>((size_t)w * rows * 3 * sizeof(double), 16))) return r;
     k_poisson_rhs<<<nb, RHS_BLOCK, 0, st>>>(w, g->h, g->y0, g->y1, d_u, d_gx, d_gy, alpha, pc.work.as<double>(), pc.partial.as<double>());
-    k_dc_reduce<<<1, 32, 0, st>>>(nb, pc.partial.as<double>(), d_dc_partial);
+    k_dc_reduce<<<1, 96, 0, st>>>(nb, pc.partial.as<double>(), d_dc_partial);
     c->stats.kernel_launches += 2;
     if (rows > 0) {
         Epilogue ep; memset(&ep, 0, sizeof(ep));

@@ -67,12 +67,15 @@ static __global__ void __launch_bounds__(RHS_BLOCK) k_poisson_rhs(int w, int h, 
     if (threadIdx.x == 0) for (int c = 0; c < 3; c++) partial[blockIdx.x * 3 + c] = red[c][0];
 }
 
+// one warp per channel (launch with >= 96 threads): lane l adds partials l, l+32, ... in that order, then a shuffle tree —
+// a fixed order, so the DC sums are the same on every run
 static __global__ void k_dc_reduce(int nblocks, const double *partial, double *dc) {
-    if (threadIdx.x < 3) {
-        double s = 0;
-        for (int b = 0; b < nblocks; b++) s += partial[b * 3 + threadIdx.x];
-        dc[threadIdx.x] = s;
-    }
+    const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (c >= 3) return;
+    double s = 0;
+    for (int b = lane; b < nblocks; b += 32) s += partial[b * 3 + c];
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+    if (lane == 0) dc[c] = s;
 }
 
 // D[n][k] (transpose=0) or D[k][n] (transpose=1) = w_n cos(pi n k/(N-1))

@@ -25,13 +25,16 @@ namespace gdpt {
 
 struct DctPlan {
     int N, M, P, logP;
-    const double2 *tw;      // [P]   exp(-2 pi i k / P)
+    const double2 *tw;      // [T]   per radix-4 pass, contiguous: exp(-2 pi i j / n) for j < n/4, n = P, P/4, ... (T = fft_twiddle_count(P))
     const double2 *chirp;   // [M]   w_n = exp(i pi n^2 / M)
     const double2 *bhat;    // [P]   FFT_P of the circular chirp filter, in the forward routine's output order, times 1/P
     const double2 *wpost;   // [M]   exp(-i pi k / M)
 };
 
-constexpr int FFT_THREADS = 256;
+// twiddles of all radix-4 passes of a length-P transform, pass after pass (forward order): sum of n/4 over n = P, P/4, ...
+__host__ __device__ inline int fft_twiddle_count(int P, int logP) { int t = 0; for (int s = 0, n = P; s < logP / 2; s++, n >>= 2) t += n >> 2; return t; }
+
+constexpr int FFT_THREADS = 512;      // 16 warps per block, two blocks per SM at 1080p (80 KB each): the passes are latency / barrier bound
 
 __device__ __forceinline__ double2 cmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 __device__ __forceinline__ double2 cmulc(double2 a, double2 b) { return make_double2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y); }   // a * conj(b)
@@ -39,21 +42,24 @@ __device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_doub
 __device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
 
 // In-place forward FFT of s[0..P) (natural order in, digit-reversed out), all threads of the block.
+// tw: the per-pass twiddle table (DctPlan::tw), staged in shared memory by the kernels: only w^j is read, w^2j and w^3j are
+// formed in registers — the FP64 pipe idles while the shared-memory / L1 pipe is the busy one (ncu: l1tex 94 %).
 __device__ inline void fft_forward(double2 *s, int P, int logP, const double2 *__restrict__ tw) {
-    int n = P;
-    for (int stage = 0; stage < logP / 2; stage++, n >>= 2) {
-        const int q4 = n >> 2, ts = P / n;
+    int n = P, ln = logP, off = 0;        // block length of the pass, its log2, start of the pass's twiddles
+    for (int stage = 0; stage < logP / 2; stage++, off += n >> 2, n >>= 2, ln -= 2) {
+        const int q4 = n >> 2, lq = ln - 2;
         for (int idx = threadIdx.x; idx < (P >> 2); idx += blockDim.x) {
-            const int blk = idx / q4, j = idx - blk * q4, base = blk * n + j;
+            const int blk = idx >> lq, j = idx & (q4 - 1), base = (blk << ln) + j;
             const double2 a = s[base], b = s[base + q4], c = s[base + 2 * q4], d = s[base + 3 * q4];
             const double2 t0 = cadd(a, c), t1 = csub(a, c), t2 = cadd(b, d), t3 = csub(b, d);
             const double2 y1 = make_double2(t1.x + t3.y, t1.y - t3.x), y3 = make_double2(t1.x - t3.y, t1.y + t3.x);
             s[base] = cadd(t0, t2);
             if (j == 0) { s[base + q4] = y1; s[base + 2 * q4] = csub(t0, t2); s[base + 3 * q4] = y3; }
             else {
-                s[base + q4] = cmul(y1, __ldg(tw + j * ts));
-                s[base + 2 * q4] = cmul(csub(t0, t2), __ldg(tw + 2 * j * ts));
-                s[base + 3 * q4] = cmul(y3, __ldg(tw + 3 * j * ts));
+                const double2 w1 = tw[off + j], w2 = cmul(w1, w1), w3 = cmul(w2, w1);
+                s[base + q4] = cmul(y1, w1);
+                s[base + 2 * q4] = cmul(csub(t0, t2), w2);
+                s[base + 3 * q4] = cmul(y3, w3);
             }
         }
         __syncthreads();
@@ -76,13 +82,14 @@ __device__ inline void fft_inverse(double2 *s, int P, int logP, const double2 *_
         }
         __syncthreads();
     }
-    int n = (logP & 1) ? 8 : 4;
-    for (int stage = 0; stage < logP / 2; stage++, n <<= 2) {
-        const int q4 = n >> 2, ts = P / n;
+    int n = (logP & 1) ? 8 : 4, ln = (logP & 1) ? 3 : 2, off = fft_twiddle_count(P, logP);
+    for (int stage = 0; stage < logP / 2; stage++, n <<= 2, ln += 2) {
+        const int q4 = n >> 2, lq = ln - 2;
+        off -= q4;
         for (int idx = threadIdx.x; idx < (P >> 2); idx += blockDim.x) {
-            const int blk = idx / q4, j = idx - blk * q4, base = blk * n + j;
+            const int blk = idx >> lq, j = idx & (q4 - 1), base = (blk << ln) + j;
             double2 u0 = s[base], u1 = s[base + q4], u2 = s[base + 2 * q4], u3 = s[base + 3 * q4];
-            if (j != 0) { u1 = cmulc(u1, __ldg(tw + j * ts)); u2 = cmulc(u2, __ldg(tw + 2 * j * ts)); u3 = cmulc(u3, __ldg(tw + 3 * j * ts)); }
+            if (j != 0) { const double2 w1 = tw[off + j], w2 = cmul(w1, w1), w3 = cmul(w2, w1); u1 = cmulc(u1, w1); u2 = cmulc(u2, w2); u3 = cmulc(u3, w3); }
             const double2 t0 = cadd(u0, u2), t1 = csub(u0, u2), t2 = cadd(u1, u3), t3 = csub(u1, u3);
             s[base] = cadd(t0, t2);
             s[base + q4] = make_double2(t1.x - t3.y, t1.y + t3.x);      // u0 + i u1 - u2 - i u3
@@ -94,7 +101,7 @@ __device__ inline void fft_inverse(double2 *s, int P, int logP, const double2 *_
 }
 
 // xs[0..N) (real, shared memory) -> its DCT-I in place.  s: P complex of shared memory.
-__device__ inline void dct1_line(const DctPlan &pl, double *xs, double2 *s) {
+__device__ inline void dct1_line(const DctPlan &pl, double *xs, double2 *s, const double2 *tw) {
     const int M = pl.M, P = pl.P;
     for (int n = threadIdx.x; n < P; n += blockDim.x) {
         double2 a = make_double2(0.0, 0.0);
@@ -106,10 +113,10 @@ __device__ inline void dct1_line(const DctPlan &pl, double *xs, double2 *s) {
         s[n] = a;
     }
     __syncthreads();
-    fft_forward(s, P, pl.logP, pl.tw);
+    fft_forward(s, P, pl.logP, tw);
     for (int i = threadIdx.x; i < P; i += blockDim.x) s[i] = cmul(s[i], __ldg(pl.bhat + i));
     __syncthreads();
-    fft_inverse(s, P, pl.logP, pl.tw);
+    fft_inverse(s, P, pl.logP, tw);
     for (int k = threadIdx.x; k < M; k += blockDim.x) s[k] = cmulc(s[k], __ldg(pl.chirp + k));     // Z_k
     __syncthreads();
     for (int k = threadIdx.x; k < M; k += blockDim.x) {
@@ -138,17 +145,20 @@ struct DctArgs {
     double scale; double *out;
 };
 
-static __global__ void __launch_bounds__(FFT_THREADS) k_dct1_fft(DctPlan pl, DctArgs a, const double *in, double *dst) {   // in == dst is allowed (a block reads its whole line before it writes it)
+static __global__ void __launch_bounds__(FFT_THREADS, 2) k_dct1_fft(DctPlan pl, DctArgs a, const double *in, double *dst) {   // in == dst is allowed (a block reads its whole line before it writes it)
     extern __shared__ double2 smem_fft[];
     double2 *s = smem_fft;
-    double *xs = reinterpret_cast<double *>(smem_fft + pl.P);
-    const int N = pl.N;
+    const int N = pl.N, T = fft_twiddle_count(pl.P, pl.logP);
+    double2 *twsm = smem_fft + pl.P;                                       // the pass twiddles, staged once per block
+    double *xs = reinterpret_cast<double *>(smem_fft + pl.P + T);
+    for (int i = threadIdx.x; i < T; i += blockDim.x) twsm[i] = pl.tw[i];
+    __syncthreads();
     for (int line = blockIdx.x; line < a.count; line += gridDim.x) {
         const int ch = line / a.per_plane, l = line - ch * a.per_plane;
         const long long base = ch * a.plane_stride + l * a.line_stride;
         for (int n = threadIdx.x; n < N; n += blockDim.x) xs[n] = in[base + n * a.elem_stride];
         __syncthreads();
-        dct1_line(pl, xs, s);
+        dct1_line(pl, xs, s, twsm);
         if (a.mode == DCT_COLUMNS) {
             // l = image column x, sample index = frequency row y: F = H / (alpha - (float)(lapY + lapX)); F(0,0) = DC of the primal
             const double lapx = 2.0 * cos(3.14159265358979323846 * l / (a.img_w - 1));
@@ -160,7 +170,7 @@ static __global__ void __launch_bounds__(FFT_THREADS) k_dct1_fft(DctPlan pl, Dct
                 xs[y] = v;
             }
             __syncthreads();
-            dct1_line(pl, xs, s);
+            dct1_line(pl, xs, s, twsm);
         }
         if (a.mode == DCT_SCALE_INTERLEAVE) {
             for (int n = threadIdx.x; n < N; n += blockDim.x) a.out[((long long)l * a.img_w + n) * 3 + ch] = xs[n] / a.scale;
@@ -172,9 +182,14 @@ static __global__ void __launch_bounds__(FFT_THREADS) k_dct1_fft(DctPlan pl, Dct
 }
 
 // Plan tables for one line length.  tw, chirp, wpost first (any grid), then the filter transform by ONE block.
-static __global__ void k_dct_plan_tables(int M, int P, double2 *tw, double2 *chirp, double2 *wpost) {
+static __global__ void k_dct_plan_tables(int M, int P, int logP, double2 *tw, double2 *chirp, double2 *wpost) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < P) { const double t = 2.0 * (double)i / (double)P; tw[i] = make_double2(cospi(t), -sinpi(t)); }
+    if (i < fft_twiddle_count(P, logP)) {        // entry i belongs to the pass with block length n: exp(-2 pi i j / n)
+        int off = 0, n = P;
+        while (i >= off + (n >> 2)) { off += n >> 2; n >>= 2; }
+        const double t = 2.0 * (double)(i - off) / (double)n;
+        tw[i] = make_double2(cospi(t), -sinpi(t));
+    }
     if (i < M) {
         const long long q = ((long long)i * i) % (2LL * M);
         const double t = (double)q / (double)M;
@@ -186,7 +201,7 @@ static __global__ void k_dct_plan_tables(int M, int P, double2 *tw, double2 *chi
 static __global__ void __launch_bounds__(FFT_THREADS) k_dct_plan_filter(int M, int P, int logP, const double2 *tw, const double2 *chirp, double2 *bhat) {
     extern __shared__ double2 smem_fft[];
     double2 *s = smem_fft;
-    for (int i = threadIdx.x; i < P; i += blockDim.x) {
+    for (int i = threadIdx.x; i < P; i += blockDim.x) {        // (the twiddles are read from global memory here: once per size)
         double2 v = make_double2(0.0, 0.0);
         if (i < M) v = chirp[i];
         else if (P - i < M) v = chirp[P - i];       // b_(-m) = w_m

@@ -59,7 +59,7 @@ extern "C" int gdpt_poisson_device_noalloc(int device, int w, int h, const doubl
     k_dct_matrix<<<148 * 4, 256, 0, st>>>(w, 0, Dw);
     k_dct_matrix<<<148 * 4, 256, 0, st>>>(h, 1, DhT);
     k_poisson_rhs<<<NB, RHS_BLOCK, 0, st>>>(w, h, 0, h, d_u, d_gx, d_gy, alpha, A, partial);
-    k_dc_reduce<<<1, 32, 0, st>>>(NB, partial, dc);
+    k_dc_reduce<<<1, 96, 0, st>>>(NB, partial, dc);
     Epilogue ep; memset(&ep, 0, sizeof(ep));
     ep.img_w = w; ep.img_h = h; ep.alpha = alpha; ep.dc = dc; ep.out = d_out;
     ep.scale = 4.0 * (w - 1) * (h - 1);

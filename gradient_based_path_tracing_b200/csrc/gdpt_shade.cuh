@@ -175,13 +175,16 @@ GD_D bool bounce_step(const DScene<R> &sc, const WaveParams &wp, PathRec<R> &pr,
     return start_iteration<R, MS>(sc, nv, dir_view, pr, ray);
 }
 
-template <typename R, int MS, int MINB = 1>
+// One thread per path of [start, n).  LOOP = false: the launch covers the range (thread i handles path start + i); this is
+// the kernel of every ordinary launch — a loop around the body costs it 38 registers (114 -> 152) and a block per SM.
+// LOOP = true: grid-stride from `start`; launched after a launch that was sized by an ESTIMATE of n (waves scheduled without
+// host read-backs) to take whatever lies beyond the estimate — normally nothing.
+template <typename R, int MS, int MINB = 1, bool LOOP = false>
 __global__ void __launch_bounds__(128, MINB) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
                                                 const HitRec *hits, const int *in_count, int in_max,
-                                                PathRec<R> *out, RayF *rays_out, int *out_count) {
+                                                PathRec<R> *out, RayF *rays_out, int *out_count, int start = 0) {
     const int n = min(*in_count, in_max);
-    // grid-stride over whole warps: the launch may be sized by an estimate of n (no host read-back of the count)
-    for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+    for (int base = start + blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
         const int i = base + threadIdx.x;
         bool alive = false;
         PathRec<R> pr; RayF ray;
@@ -194,6 +197,7 @@ __global__ void __launch_bounds__(128, MINB) k_bounce(DScene<R> sc, WaveParams w
         }
         int slot = warp_slot(alive, out_count);
         if (alive) { store_soa(out, slot, wp.n_paths, pr); store_rec(rays_out + slot, ray); sort_emit(wp, slot, ray); }
+        if (!LOOP) break;
     }
 }
 

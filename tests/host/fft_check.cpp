@@ -13,6 +13,7 @@ static Dim threadIdx{0}, blockDim{1};
 #define __device__
 #define __forceinline__ inline
 #define __restrict__
+#define __host__
 static inline void __syncthreads() {}
 template <typename T> static inline T __ldg(const T *p) { return *p; }
 static inline double cospi(double x) { return cos(M_PI * x); }
@@ -27,8 +28,13 @@ int main(int argc, char **argv) {
     for (int a = 1; a < argc; a++) {
         const int N = atoi(argv[a]), M = N - 1;
         int P = 16, logP = 4; while (P < 2 * M - 1) { P <<= 1; logP++; }
-        std::vector<double2> tw(P), chirp(M), wpost(M), bhat(P), s(P);
-        for (int i = 0; i < P; i++) { double t = 2.0 * i / P; tw[i] = make_double2(cospi(t), -sinpi(t)); }
+        const int T = fft_twiddle_count(P, logP);
+        std::vector<double2> tw(T), chirp(M), wpost(M), bhat(P), s(P);
+        for (int i = 0; i < T; i++) {
+            int off = 0, n = P;
+            while (i >= off + (n >> 2)) { off += n >> 2; n >>= 2; }
+            double t = 2.0 * (i - off) / n; tw[i] = make_double2(cospi(t), -sinpi(t));
+        }
         for (int i = 0; i < M; i++) {
             long long q = ((long long)i * i) % (2LL * M);
             chirp[i] = make_double2(cospi((double)q / M), sinpi((double)q / M));
@@ -52,7 +58,7 @@ int main(int argc, char **argv) {
             for (int n = 1; n < M; n++) acc += 2.0L * x[n] * cosl(M_PIl * (long double)(((long long)n * k) % (2LL * M)) / M);
             want[k] = (double)acc;
         }
-        dct1_line(pl, x.data(), s.data());
+        dct1_line(pl, x.data(), s.data(), tw.data());
         double err = 0, scale = 0;
         for (int k = 0; k < N; k++) { err = fmax(err, fabs(x[k] - want[k])); scale = fmax(scale, fabs(want[k])); }
         printf("%s\"%d\": {\"P\": %d, \"roundtrip\": %.3e, \"dct_rel_err\": %.3e}", first ? "" : ", ", N, P, rt, err / scale);
