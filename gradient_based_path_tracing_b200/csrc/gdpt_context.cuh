@@ -89,9 +89,11 @@ namespace gdpt {
 // shift-mapped mode); slot 1 lets the next wave run on a second stream while the late, small bounces of the previous one
 // leave most SMs idle.
 struct WaveSlot {
-    DevBuf *gen, *rays, *hits, *rec_a, *rec_b, *off, *counters, *sort_keys, *sort_order, *sort_hist;
+    DevBuf *gen, *rays, *hits, *rec_a, *rec_b, *off, *counters, *sort_keys, *sort_order, *sort_hist, *res;
     cudaStream_t stream = nullptr;     // slot 0: the context's stream
-    cudaEvent_t done = nullptr;
+    cudaEvent_t done = nullptr;        // the slot's last wave has been queued up to here
+    cudaEvent_t reduced = nullptr;     // ... and its per-path results have been added to the images (the slot's buffers are free again)
+    bool busy = false;                 // a wave of the current accumulation used the slot
 };
 // What the first (host-synchronised) wave of a configuration measured: live paths after the primary stage and after
 // every bounce.  Later waves of the same configuration are launched from these numbers without reading anything back.
@@ -124,7 +126,12 @@ struct gdpt_ctx {
     // wavefront queues
     gdpt::DevBuf gen, rays, hits, rec_a, rec_b, off, counters, recout, xs, ys, streams;
     static constexpr int MAX_SLOTS = 4;
-    gdpt::DevBuf xbuf[MAX_SLOTS - 1][10];   // queue buffers of the wave slots beyond the first
+    gdpt::DevBuf res0;                      // per-path result records of slot 0 (deterministic accumulation)
+    gdpt::DevBuf xbuf[MAX_SLOTS - 1][11];   // queue buffers of the wave slots beyond the first
+    cudaStream_t reduce_stream = nullptr;   // k_wave_reduce of every wave, in wave order
+    cudaEvent_t ev_reduce_join = nullptr;
+    bool reduce_forked = false;             // reduce_stream has joined the context's stream for the current accumulation
+    bool deterministic = true;              // per-path result records + ordered reduction instead of atomicAdd(double) ("deterministic")
     gdpt::WaveSlot slot[MAX_SLOTS];
     gdpt::WaveCalibration cal;
     bool async_waves = true;          // launch waves from the calibration without per-bounce host syncs (gdpt_set_option "async_waves")
@@ -201,13 +208,16 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     for (auto &e : c->ev) GD_CUDA(cudaEventCreate(&e));
     GD_CUDA(cudaMallocHost((void **)&c->h_counts, 64));
     GD_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
-    c->slot[0] = gdpt::WaveSlot{&c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters, &c->sort_keys, &c->sort_order, &c->sort_hist};
+    c->slot[0] = gdpt::WaveSlot{&c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->res0};
+    GD_CUDA(cudaStreamCreateWithFlags(&c->reduce_stream, cudaStreamNonBlocking));
+    GD_CUDA(cudaEventCreateWithFlags(&c->ev_reduce_join, cudaEventDisableTiming));
+    if (const char *e = getenv("GDPT_DETERMINISTIC")) c->deterministic = atoi(e) != 0;
     for (int k = 1; k < gdpt_ctx::MAX_SLOTS; k++) {
         gdpt::DevBuf *b = c->xbuf[k - 1];
-        c->slot[k] = gdpt::WaveSlot{b, b + 1, b + 2, b + 3, b + 4, b + 5, b + 6, b + 7, b + 8, b + 9};
+        c->slot[k] = gdpt::WaveSlot{b, b + 1, b + 2, b + 3, b + 4, b + 5, b + 6, b + 7, b + 8, b + 9, b + 10};
         GD_CUDA(cudaStreamCreateWithFlags(&c->slot[k].stream, cudaStreamNonBlocking));
     }
-    for (auto &sl : c->slot) GD_CUDA(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    for (auto &sl : c->slot) { GD_CUDA(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming)); GD_CUDA(cudaEventCreateWithFlags(&sl.reduced, cudaEventDisableTiming)); }
     if (int r = c->dev_stats.ensure(64)) return r;
     GD_CUDA(cudaMemset(c->dev_stats.p, 0, 64));
     if (const char *e = getenv("GDPT_ASYNC_WAVES")) c->async_waves = atoi(e) != 0;
@@ -501,6 +511,12 @@ inline int join_wave_streams(gdpt_ctx *c) {
         GD_CUDA(cudaStreamWaitEvent(c->stream, c->slot[k].done, 0));
     }
     c->forked = 0;
+    if (c->reduce_forked) {
+        GD_CUDA(cudaEventRecord(c->ev_reduce_join, c->reduce_stream));
+        GD_CUDA(cudaStreamWaitEvent(c->stream, c->ev_reduce_join, 0));
+        c->reduce_forked = false;
+    }
+    for (auto &sl : c->slot) sl.busy = false;
     c->wave_index = 0;
     return 0;
 }
@@ -511,13 +527,15 @@ inline void destroy_context(gdpt_ctx *c) {
     gdpt::DevBuf *all[] = {&c->shapes, &c->spheres, &c->indices, &c->materials, &c->img3, &c->img1, &c->pos_d, &c->nrm_d, &c->uv_d, &c->tex_d,
                            &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tex_f, &c->texels3_f, &c->texels1_f,
                            &c->light_f, &c->lcdf_d, &c->lcdf_f, &c->lpmf_d, &c->lpmf_f, &c->tcdf_d, &c->tcdf_f, &c->area_d, &c->area_f, &c->lshape, &c->ecr_d, &c->ecr_f, &c->epr_d, &c->epr_f, &c->ecm_d, &c->ecm_f, &c->epm_d, &c->epm_f, &c->shadow_rays, &c->shadow_hits, &c->prec_a, &c->prec_b, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
-                           &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->dev_stats, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
+                           &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->dev_stats, &c->res0, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
     for (auto *b : all) b->release();
     for (auto &row : c->xbuf) for (auto &b : row) b.release();
     c->pc.release();
     if (c->h_counts) cudaFreeHost(c->h_counts);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    for (auto &sl : c->slot) if (sl.done) cudaEventDestroy(sl.done);
+    for (auto &sl : c->slot) { if (sl.done) cudaEventDestroy(sl.done); if (sl.reduced) cudaEventDestroy(sl.reduced); }
+    if (c->ev_reduce_join) cudaEventDestroy(c->ev_reduce_join);
+    if (c->reduce_stream) cudaStreamDestroy(c->reduce_stream);
     for (int k = 1; k < gdpt_ctx::MAX_SLOTS; k++) if (c->slot[k].stream) cudaStreamDestroy(c->slot[k].stream);
     for (auto &e : c->ev) if (e) cudaEventDestroy(e);
     if (c->stream && c->own_stream) cudaStreamDestroy(c->stream);

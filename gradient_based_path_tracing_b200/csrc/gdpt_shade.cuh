@@ -26,6 +26,14 @@ GD_D void finish_path(const WaveParams &wp, int px, int py, int id, const V3<R> 
     double rd[3] = {(double)rad.x, (double)rad.y, (double)rad.z};
     double *bufs[4] = {wp.cx0, wp.cy0, wp.cx1, wp.cy1};
     const double sign[4] = {1.0, 1.0, -1.0, -1.0};  // X0,Y0: contrib - contribS ; X1,Y1: contribS - contrib
+    if (wp.res) {                                    // one contiguous 120-byte record per path; summed in sample order by k_wave_reduce
+        double *o = wp.res + (size_t)id * 15;
+        for (int c = 0; c < 3; c++) {
+            o[c] = rd[c] * inv_spp;
+            for (int k = 0; k < 4; k++) o[3 + 3 * k + c] = sign[k] * (contrib[c] - cS[k][c]) * (wS[k] / (prob * spp));
+        }
+        return;
+    }
     for (int c = 0; c < 3; c++) {
         if (rd[c] != 0.0) atomicAdd(wp.img + p + c, rd[c] * inv_spp);
         for (int k = 0; k < 4; k++) {
@@ -54,6 +62,30 @@ GD_D void finish_with_offsets(const WaveParams &wp, const PathRec<R> &pr, const 
         }
     }
     finish_path<R>(wp, pr.px, pr.py, pr.id, pr.rad, pr.contrib, pr.prob, cS, wS);
+}
+
+// The accumulation of render.cpp:311-327 without atomics: thread per pixel slot of the wave (the 8x4-tile enumeration of
+// k_generate), the samples of the wave added one after the other — in sample order, onto the running image value — so the
+// five images are bit-reproducible and carry the summation order of the reference's own per-pixel loop.  Waves are reduced in
+// wave order (one stream), pixels are disjoint between threads, strips between GPUs.
+static __global__ void __launch_bounds__(256) k_wave_reduce(WaveParams wp, const double *res, double *img, double *cx0, double *cy0, double *cx1, double *cy1) {
+    const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (p >= wp.npix_pad) return;
+    const int tile = (int)(p >> 5), lane = (int)(p & 31);
+    const int x = (tile % wp.tiles_x) * 8 + (lane & 7), y = wave_row(wp, tile / wp.tiles_x, lane);
+    if (x >= wp.width || y >= wp.y1) return;
+    const size_t pix = ((size_t)y * wp.width + x) * 3;
+    double *bufs[5] = {img, cx0, cy0, cx1, cy1};
+    double acc[15];
+#pragma unroll
+    for (int k = 0; k < 15; k++) acc[k] = bufs[k / 3][pix + k % 3];
+    for (int s = 0; s < wp.n_samples; s++) {
+        const double *r = res + ((size_t)s * wp.npix_pad + p) * 15;
+#pragma unroll
+        for (int k = 0; k < 15; k++) acc[k] += r[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 15; k++) bufs[k / 3][pix + k % 3] = acc[k];
 }
 
 // Start of a loop iteration at `vtx` (path_tracing.h:528-564 + eval/pdf of :762-763, which

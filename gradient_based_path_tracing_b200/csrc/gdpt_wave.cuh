@@ -85,6 +85,11 @@ int prepare_slot(gdpt_ctx *c, WaveSlot &sl, WaveParams &wp, bool &sorting) {
     if (int r = sl.rec_b->ensure((size_t)N * sizeof(PathRec<R>))) return r;
     if (int r = sl.off->ensure((size_t)N * sizeof(OffRec<R>))) return r;
     if (int r = sl.counters->ensure(64)) return r;
+    wp.res = nullptr;
+    if (c->deterministic && !wp.rec_out && wp.img) {
+        if (int r = sl.res->ensure((size_t)N * 15 * sizeof(double))) return r;
+        wp.res = sl.res->as<double>();
+    }
     sorting = c->sort_rays && N >= SORT_MIN_RAYS;
     if (sorting) {
         if (int r = sl.sort_keys->ensure((size_t)N * sizeof(int))) return r;
@@ -122,6 +127,7 @@ int run_wave_sync(gdpt_ctx *c, DScene<R> sc, WaveParams wp, WaveCalibration *cal
     float ms;
 
     GD_CUDA(cudaMemsetAsync(cnt, 0, 64, st));
+    if (wp.res) GD_CUDA(cudaMemsetAsync(wp.res, 0, (size_t)N * 15 * sizeof(double), st));
     k_generate<R><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, rays);
     c->stats.kernel_launches++;
     GD_CUDA(cudaEventRecord(e0, st));
@@ -172,6 +178,10 @@ int run_wave_sync(gdpt_ctx *c, DScene<R> sc, WaveParams wp, WaveCalibration *cal
         if (cal) cal->counts.push_back(count);
         std::swap(cur, nxt); which ^= 1; first = false;
     }
+    if (wp.res) {
+        k_wave_reduce<<<blocks_for(wp.npix_pad, 256), 256, 0, st>>>(wp, wp.res, wp.img, wp.cx0, wp.cy0, wp.cx1, wp.cy1);
+        c->stats.kernel_launches++;
+    }
     GD_CUDA(cudaGetLastError());
     return 0;
 }
@@ -197,6 +207,10 @@ int run_wave_async(gdpt_ctx *c, DScene<R> sc, WaveParams wp, const WaveCalibrati
         double b = (stage < (int)cal.counts.size() ? cal.counts[stage] : cal.counts.back()) * scale;
         return (int)std::min<double>(N, b * 1.06 + 16384.0);
     };
+    if (wp.res) {
+        if (sl.busy) GD_CUDA(cudaStreamWaitEvent(st, sl.reduced, 0));      // the slot's previous wave must have been added to the images
+        GD_CUDA(cudaMemsetAsync(wp.res, 0, (size_t)N * 15 * sizeof(double), st));
+    }
     GD_CUDA(cudaMemsetAsync(cnt, 0, 64, st));
     k_generate<R><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, gen, rays);
     c->stats.kernel_launches++;
@@ -228,6 +242,19 @@ int run_wave_async(gdpt_ctx *c, DScene<R> sc, WaveParams wp, const WaveCalibrati
         launch_bounce<R, MS>(c, st, ub, true, sc, wp, cur, first ? off : nullptr, hits, cin, N, nxt, rays, cout);
         std::swap(cur, nxt); which ^= 1; first = false;
     }
+    if (wp.res) {     // the reduction of this wave: on the reduce stream, i.e. after the reductions of all earlier waves
+        if (!c->reduce_forked) {      // (joins what is already queued on the context's stream: image clears, the calibration wave)
+            GD_CUDA(cudaEventRecord(c->ev_fork, c->stream));
+            GD_CUDA(cudaStreamWaitEvent(c->reduce_stream, c->ev_fork, 0));
+            c->reduce_forked = true;
+        }
+        GD_CUDA(cudaEventRecord(sl.done, st));
+        GD_CUDA(cudaStreamWaitEvent(c->reduce_stream, sl.done, 0));
+        k_wave_reduce<<<blocks_for(wp.npix_pad, 256), 256, 0, c->reduce_stream>>>(wp, wp.res, wp.img, wp.cx0, wp.cy0, wp.cx1, wp.cy1);
+        GD_CUDA(cudaEventRecord(sl.reduced, c->reduce_stream));
+        c->stats.kernel_launches++;
+    }
+    sl.busy = true;
     GD_CUDA(cudaGetLastError());
     return 0;
 }

@@ -55,6 +55,10 @@ struct WaveParams {
     const int *xs, *ys; const unsigned long long *streams; double *rec_out;
     // image mode: five accumulation images, W*H*3 doubles each, row-major, y down
     double *img, *cx0, *cy0, *cx1, *cy1;
+    // deterministic accumulation (gradpath, reference offsets): every finished path writes its 15 contributions (radiance3,
+    // then X0, Y0, X1, Y1 gradients x 3) to res[id * 15 ..] instead of adding them to the images with atomics; k_wave_reduce then
+    // adds them pixel by pixel in sample order.  nullptr: atomicAdd(double) straight into the images.
+    double *res;
     // ray sorting (set by run_wave when enabled): per-slot key + histogram, origin grid over the scene box
     int *sort_keys, *sort_hist;
     float sort_lo[3], sort_scale[3];

@@ -206,7 +206,9 @@ int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out);
  * src/main.cpp:20-23).  "async_waves" 1|0: launch the waves of a render from the first wave's measured path counts without
  * per-bounce host read-backs (default 1); "wave_streams" 1..4: waves in flight on separate streams (default 3); "time_kernels"
  * 1|0: keep the host-synchronised loop and fill gdpt_stats.ms_trace / ms_shade with per-kernel event times (default 0: those two
- * fields stay 0); "poisson_fft" 1|0: the O(N log N) form of the DCT-I in fourierSolve's
+ * fields stay 0); "deterministic" 1|0: gradpath accumulates through per-path
+ * result records that are added to the images in sample order (bit-reproducible images, the summation order of render.cpp:303-327;
+ * default 1) or with atomicAdd(double) straight into the images; "poisson_fft" 1|0: the O(N log N) form of the DCT-I in fourierSolve's
  * replacement or the dense-matrix form (default 1; films under 16 pixels a side always take the matrix form); "tail_paths" n; "sort_rays" 1|0; "trace_variant" v; "shade_variant" v. */
 int gdpt_set_option(gdpt_ctx *ctx, const char *name, int value);
 /* Run all of the context's work on the caller's CUDA stream (a cudaStream_t; NULL restores the context's own). */

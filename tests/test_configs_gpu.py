@@ -223,3 +223,21 @@ def test_waves_launched_without_host_syncs_give_the_same_images(g):
             for f in ("primal", "dx", "dy"):
                 assert np.allclose(getattr(a, f), getattr(b, f), rtol=1e-9, atol=1e-12), (tag, f)
             assert np.linalg.norm(a.poisson - b.poisson) <= 1e-9 * np.linalg.norm(a.poisson)
+
+
+def test_images_are_bit_reproducible(g):
+    """Deterministic accumulation (per-path result records added in sample order, waves reduced in wave order): two renders
+    give the same bits — also across wave schedules and wave sizes — and the atomicAdd(double) path agrees to rounding."""
+    imgs = {}
+    for tag, opts, wave in (("a", {}, 2), ("b", {}, 2), ("sync", {"async_waves": 0}, 2), ("one_stream", {"wave_streams": 1}, 2), ("waves_of_3", {}, 3),
+                            ("atomics", {"deterministic": 0}, 2)):
+        sc = g.Scene.named("cbox_gdpt")
+        for k, v in opts.items():
+            sc.set_option(k, v)
+        imgs[tag] = g.gradient_path_render(sc, spp=9, precision="f32", wave_samples=wave)
+        sc.close()
+    for tag in ("b", "sync", "one_stream", "waves_of_3"):
+        for f in ("primal", "dx", "dy", "poisson"):
+            assert np.array_equal(getattr(imgs["a"], f), getattr(imgs[tag], f)), (tag, f)
+    for f in ("primal", "dx", "dy"):
+        assert np.allclose(getattr(imgs["a"], f), getattr(imgs["atomics"], f), rtol=1e-9, atol=1e-12), f

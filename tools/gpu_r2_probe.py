@@ -20,15 +20,12 @@ if "sched" in what:
         print("%-44s %7.1f ms  %7.1f Mpaths/s   mean %.6f  launches %d" % (tag, dt * 1e3, 5 * 1920 * 1080 * spp / dt / 1e6, r.primal.mean(), r.stats["kernel_launches"]), flush=True)
         sc.close()
     run("sync (host read-back per bounce)", {"async_waves": 0})
-    for ns in (1, 2, 3, 4):
-        run("async, %d stream(s)" % ns, {"async_waves": 1, "wave_streams": ns})
-    for w in (1, 4):
-        run("async, 3 streams, %d spp per wave" % w, {"async_waves": 1, "wave_streams": 3}, wave=w)
-    run("async, 2 streams, trace variant 0 (two pop sites)", {"async_waves": 1, "wave_streams": 2, "trace_variant": 0})
-    run("async, 2 streams, trace variant 120000 (leaf children tested in the node step)", {"async_waves": 1, "wave_streams": 2, "trace_variant": 120000})
-    run("async, 2 streams, trace variant 40000 again", {"async_waves": 1, "wave_streams": 2, "trace_variant": 40000})
-    run("async, 2 streams, f64", {"async_waves": 1, "wave_streams": 2}, prec="f64")
-    run("async, 3 streams, f64", {"async_waves": 1, "wave_streams": 3}, prec="f64")
+    run("default (async, 3 streams, deterministic accumulation)", {})
+    run("atomicAdd accumulation", {"deterministic": 0})
+    run("default again", {})
+    run("atomicAdd accumulation again", {"deterministic": 0})
+    run("default, f64", {}, prec="f64")
+    run("atomicAdd accumulation, f64", {"deterministic": 0}, prec="f64")
 if "records" in what:
     for name in ["cbox_gdpt_64", "cbox_gdpt_d2", "veach_mi_small", "sponza_small", "disney_small"]:
         z = np.load("tests/golden/records_%s.npz" % name)
