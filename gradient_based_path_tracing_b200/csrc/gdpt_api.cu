@@ -281,6 +281,7 @@ int gdpt_set_option(gdpt_ctx *ctx, const char *name, int value) {
     else if (n == "tail_paths") ctx->tail_paths = value;
     else if (n == "poisson_fft") ctx->poisson_fft = value != 0;
     else if (n == "deterministic") ctx->deterministic = value != 0;
+    else if (n == "shade_sorted") ctx->shade_sorted = value != 0;
     else if (n == "sort_rays") ctx->sort_rays = value != 0;
     else if (n == "trace_variant") ctx->trace_variant = value;
     else if (n == "shade_variant") ctx->shade_variant = value;

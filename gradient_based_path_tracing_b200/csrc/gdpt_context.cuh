@@ -139,6 +139,7 @@ struct gdpt_ctx {
     cudaEvent_t ev_fork = nullptr;
     unsigned forked = 0;              // bit k: slot k's stream has work of the current accumulation in flight
     int wave_index = 0;
+    bool shade_sorted = false;        // k_bounce walks the queue in the traced (sorted) order instead of queue order ("shade_sorted")
     bool poisson_fft = true;          // the FFT form of the DCT-I (gdpt_poisson_fft.cuh); 0: the dense-matrix form ("poisson_fft")
     bool time_kernels = false;        // keep the host-synchronised wave loop with per-kernel event timing ("time_kernels"; bench.py's roofline pass)
     gdpt::DevBuf dev_stats;           // [0] rays traced by launches sized on the device (folded into stats.rays_traced by gdpt_get_stats)
@@ -263,10 +264,11 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     // Two builders (Embree's build-quality levels, scene.cpp:22, in this library's terms): the host's binned SAH with triangle
     // pre-splitting (gdpt_bvh.cpp: ~45 ms for Sponza, the better tree: 17.4 nodes + 2.8 primitives per ray) and the device's PLOC
     // (gdpt_bvh_gpu.cu: ~9 ms, 18.1 nodes + 4.7 primitives per ray, 5-6 % slower rendering).  Without a flag the planned work
-    // decides: the host build pays for itself from about 2e8 pixel-samples (Sponza 1080p at ~100 spp on one GPU).
+    // decides: the host build pays for itself from about 1e8 pixel-samples (Sponza 1080p at ~50 spp on one GPU:
+    // 5.5 % of the render time against ~35 ms of build time).
     const char *bvh_mode = getenv("GDPT_BVH");
     const double planned = (double)d->width * d->height * std::max(1, d->samples_per_pixel);
-    bool device_bvh = (flags & GDPT_CREATE_BVH_DEVICE) ? true : (flags & GDPT_CREATE_BVH_HOST) ? false : planned < 2e8;
+    bool device_bvh = (flags & GDPT_CREATE_BVH_DEVICE) ? true : (flags & GDPT_CREATE_BVH_HOST) ? false : planned < 1e8;
     if (bvh_mode) device_bvh = std::string(bvh_mode) != "host";
     if (no_bvh) device_bvh = false;
     std::thread bvh_thread([&] { if (no_bvh || device_bvh) scene_bounds(hs, bvh.lo, bvh.hi); else build_bvh(hs, bvh); });
@@ -310,6 +312,12 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     if (const char *sv = getenv("GDPT_SHADE_VARIANT")) c->shade_variant = atoi(sv);
     c->lambertian_only = !mats.empty();
     for (const DMaterial &m : mats) if (m.type != MAT_LAMBERTIAN) c->lambertian_only = false;
+    // Scenes with more than diffuse surfaces shade in the TRACED order (the ray sort's permutation: origin cell + direction
+    // bin): neighbouring hits share meshes, textures and mostly the material, so a warp runs one arm of the nine-way BSDF
+    // dispatch instead of several — the north star's material-sorted queue, obtained from the spatial sort that exists anyway.
+    // B200: Disney config 528 -> 881 Mpaths/s; all-Lambertian Sponza loses 8 % to the gathered record loads, so it keeps queue order.
+    c->shade_sorted = !c->lambertian_only;
+    if (const char *e = getenv("GDPT_SHADE_SORTED")) c->shade_sorted = atoi(e) != 0;
     if (int r = upload(c->materials, mats)) return r;
     std::vector<DTexture<double>> td(d->n_textures); std::vector<DTexture<float>> tf(d->n_textures);
     for (int i = 0; i < d->n_textures; i++) {

@@ -214,13 +214,16 @@ GD_D bool bounce_step(const DScene<R> &sc, const WaveParams &wp, PathRec<R> &pr,
 template <typename R, int MS, int MINB = 1, bool LOOP = false>
 __global__ void __launch_bounds__(128, MINB) k_bounce(DScene<R> sc, WaveParams wp, const PathRec<R> *in, const OffRec<R> *off_in,
                                                 const HitRec *hits, const int *in_count, int in_max,
-                                                PathRec<R> *out, RayF *rays_out, int *out_count, int start = 0) {
+                                                PathRec<R> *out, RayF *rays_out, int *out_count, int start = 0, const int *order = nullptr) {
     const int n = min(*in_count, in_max);
     for (int base = start + blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
-        const int i = base + threadIdx.x;
+        const int j = base + threadIdx.x;
         bool alive = false;
         PathRec<R> pr; RayF ray;
-        if (i < n) {
+        if (j < n) {
+            // order: the permutation the rays were traced in (origin cell + direction bin): a warp then shades neighbouring
+            // hits — the same meshes, textures and, in mixed scenes, mostly the same material
+            const int i = order ? __ldg(order + j) : j;
             load_soa(pr, in, i, wp.n_paths);
             const bool first = off_in != nullptr;          // iteration with num_vertices == 3
             OffRec<R> off; if (first) load_soa(off, off_in, i, wp.n_paths);

@@ -57,8 +57,9 @@ inline void launch_primary(gdpt_ctx *c, cudaStream_t st, int n, A... a) {
 
 // overflow: the launch was sized by an estimate of the live count; a small grid-stride launch takes the paths beyond it
 template <typename R, int MS, typename... A>
-inline void launch_bounce(gdpt_ctx *c, cudaStream_t st, int n, bool overflow, A... a) {
-    auto go = [&](auto kern) { kern<<<blocks_for(n, 128), 128, 0, st>>>(a..., 0); };
+inline void launch_bounce(gdpt_ctx *c, cudaStream_t st, int n, bool overflow, const int *order, A... a) {
+    if (!c->shade_sorted) order = nullptr;
+    auto go = [&](auto kern) { kern<<<blocks_for(n, 128), 128, 0, st>>>(a..., 0, order); };
     if constexpr (MS == MS_LAMBERTIAN && sizeof(R) == 4) {
         switch (c->shade_variant % 10) {
             case 1: go(k_bounce<R, MS, 5>); break;
@@ -69,7 +70,7 @@ inline void launch_bounce(gdpt_ctx *c, cudaStream_t st, int n, bool overflow, A.
     } else go(k_bounce<R, MS, 1>);
     c->stats.kernel_launches++; c->stats.bounce_iterations++;
     if (overflow) {
-        k_bounce<R, MS, 1, true><<<SM_COUNT, 128, 0, st>>>(a..., blocks_for(n, 128) * 128);
+        k_bounce<R, MS, 1, true><<<SM_COUNT, 128, 0, st>>>(a..., blocks_for(n, 128) * 128, order);
         c->stats.kernel_launches++;
     }
 }
@@ -168,7 +169,7 @@ int run_wave_sync(gdpt_ctx *c, DScene<R> sc, WaveParams wp, WaveCalibration *cal
         if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)n_bins * sizeof(int), st));
         int *cin = cnt + which, *cout = cnt + (which ^ 1);
         GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
-        launch_bounce<R, MS>(c, st, count, false, sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout);
+        launch_bounce<R, MS>(c, st, count, false, order, sc, wp, cur, first ? off : nullptr, hits, cin, count, nxt, rays, cout);
         GD_CUDA(cudaEventRecord(e2, st));
         GD_CUDA(cudaMemcpyAsync(c->h_counts, cout, sizeof(int), cudaMemcpyDeviceToHost, st));
         GD_CUDA(cudaStreamSynchronize(st));
@@ -239,7 +240,7 @@ int run_wave_async(gdpt_ctx *c, DScene<R> sc, WaveParams wp, const WaveCalibrati
         launch_trace<ModeSel<R>::exact>(c, rays, hits, N, order, st, cin);
         if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)n_bins * sizeof(int), st));
         GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
-        launch_bounce<R, MS>(c, st, ub, true, sc, wp, cur, first ? off : nullptr, hits, cin, N, nxt, rays, cout);
+        launch_bounce<R, MS>(c, st, ub, true, order, sc, wp, cur, first ? off : nullptr, hits, cin, N, nxt, rays, cout);
         std::swap(cur, nxt); which ^= 1; first = false;
     }
     if (wp.res) {     // the reduction of this wave: on the reduce stream, i.e. after the reductions of all earlier waves

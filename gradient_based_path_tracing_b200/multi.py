@@ -224,10 +224,10 @@ class DistributedRenderer:
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
         self.bands = partition_rows(scene.height, self.world)
         # which builder: a rank's share of the planned work decides like gdpt_create does for the whole film (include/gdpt.h:
-        # the host's better tree pays from ~2e8 pixel-samples).  Device builds are per rank (9 ms, no host cores involved);
+        # the host's better tree pays from ~1e8 pixel-samples).  Device builds are per rank (9 ms, no host cores involved);
         # a host build is done once on rank 0 and broadcast from 4 ranks up (N builds side by side share the box's cores).
         share_of_work = scene.width * scene.height * max(1, scene.options.samples_per_pixel) / self.world
-        self.bvh_builder = "device" if share_of_work < 2e8 else "host"
+        self.bvh_builder = "device" if share_of_work < 1e8 else "host"
         if share_bvh == "auto":
             share_bvh = self.world >= 4
         if device in scene._ctx:

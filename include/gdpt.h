@@ -114,7 +114,7 @@ int gdpt_device_count(void);
 #define GDPT_CREATE_NO_BVH 1 /* gdpt_create_ex: everything but the BVH build */
 #define GDPT_CREATE_BVH_HOST 2   /* build the tree with the host's binned-SAH builder + triangle pre-splitting (best tree, ~45 ms for Sponza) */
 #define GDPT_CREATE_BVH_DEVICE 4 /* build it on the device (PLOC, ~9 ms, 5-6 % slower traversal); neither flag: chosen from the planned work
-                                  * width * height * samples_per_pixel (device build below 2e8 pixel-samples) */
+                                  * width * height * samples_per_pixel (device build below 1e8 pixel-samples) */
 
 /* Upload the scene to `device`, rebuild mip chains, build the BVH (replaces Scene::Scene's
  * Embree registration/commit, scene.cpp:19-34). */
