@@ -67,8 +67,10 @@ if "bvh" in what:
     from gradient_based_path_tracing_b200.render import _params
     base = g.Scene.named("sponza_1080p")
     os.environ["GDPT_VERBOSE"] = "1"
-    for mode, split, radius, leaf in (("host", "2", 16, 4), ("gpu", "0", 8, 4), ("gpu", "2", 8, 4), ("gpu", "2", 16, 4), ("gpu", "1", 8, 4), ("gpu", "3", 8, 4), ("gpu", "2", 8, 2)):
-        os.environ["GDPT_BVH"] = mode; os.environ["GDPT_BVH_SPLIT"] = split; os.environ["GDPT_PLOC_RADIUS"] = str(radius); os.environ["GDPT_BVH_MAX_LEAF"] = str(leaf)
+    for mode, split, radius, leaf, noself in (("host", "2", 8, 4, 1), ("host", "2", 8, 4, 1), ("host", "3", 8, 4, 1), ("host", "4", 8, 4, 1), ("host", "6", 8, 4, 1), ("host", "2", 8, 4, 1), ("host", "3", 8, 4, 1),
+                                              ("host", "4", 8, 4, 1), ("gpu", "0", 8, 4, 1)):
+        os.environ["GDPT_BVH"] = mode; os.environ["GDPT_BVH_SPLIT"] = split; os.environ["GDPT_BVH_SPLIT_DEVICE"] = split if mode == "gpu" else "0"
+        os.environ["GDPT_PLOC_RADIUS"] = str(radius); os.environ["GDPT_BVH_MAX_LEAF"] = str(leaf); os.environ["GDPT_PLOC_NOSELF"] = str(noself)
         for rep in range(2):
             sc = g.Scene(base.a)
             t0 = time.perf_counter(); sc.context(0); t1 = time.perf_counter()
@@ -80,7 +82,7 @@ if "bvh" in what:
         cnt = np.zeros(3)
         p = _params(sc, spp=1, precision="f32")
         _capi.check(_capi.lib().gdpt_traversal_counts(sc.context(0), C.byref(p), _capi.as_dp(cnt)))
-        print("BVH %-4s split %s radius %d leaf %d: create %.1f ms, %d nodes, %d prim records, depth %d; 32 spp %.1f ms (%.1f Mpaths/s), %.2f nodes + %.2f prims per ray, mean %.6f" % (
-            mode, split, radius, leaf, (t1 - t0) * 1e3, nn, npr, depth, dt * 1e3, 5 * 1920 * 1080 * 32 / dt / 1e6, cnt[0], cnt[1], r.primal.mean()), flush=True)
+        print("BVH %-4s split %s radius %d leaf %d noself %d: create %.1f ms, %d nodes, %d prim records, depth %d; 32 spp %.1f ms (%.1f Mpaths/s), %.2f nodes + %.2f prims per ray, mean %.6f" % (
+            mode, split, radius, leaf, noself, (t1 - t0) * 1e3, nn, npr, depth, dt * 1e3, 5 * 1920 * 1080 * 32 / dt / 1e6, cnt[0], cnt[1], r.primal.mean()), flush=True)
         sc.close()
-    del os.environ["GDPT_BVH"], os.environ["GDPT_BVH_SPLIT"], os.environ["GDPT_VERBOSE"], os.environ["GDPT_PLOC_RADIUS"], os.environ["GDPT_BVH_MAX_LEAF"]
+    del os.environ["GDPT_BVH"], os.environ["GDPT_BVH_SPLIT"], os.environ["GDPT_VERBOSE"], os.environ["GDPT_PLOC_RADIUS"], os.environ["GDPT_BVH_MAX_LEAF"], os.environ["GDPT_PLOC_NOSELF"], os.environ["GDPT_BVH_SPLIT_DEVICE"]
