@@ -212,7 +212,7 @@ def _as_u8(torch, ptr, nbytes, dev):
 class DistributedRenderer:
     """render() across the ranks of an initialised torch.distributed process group."""
 
-    def __init__(self, scene, device, dist, torch, solver="auto", share_bvh="auto"):
+    def __init__(self, scene, device, dist, torch, solver="auto", share_bvh="auto", bvh=None):
         """solver: "gather" (sum the bands onto rank 0 and solve there), "distributed" (all-to-all transposed
         solve on all ranks) or "auto" (distributed from 3840x2160 pixels up when every rank has rows).
         share_bvh: rank 0 builds the BVH, the others create their context without one and receive rank 0's through a
@@ -227,7 +227,7 @@ class DistributedRenderer:
         # the host's better tree pays from ~1e8 pixel-samples).  Device builds are per rank (9 ms, no host cores involved);
         # a host build is done once on rank 0 and broadcast from 4 ranks up (N builds side by side share the box's cores).
         share_of_work = scene.width * scene.height * max(1, scene.options.samples_per_pixel) / self.world
-        self.bvh_builder = "device" if share_of_work < 1e8 else "host"
+        self.bvh_builder = bvh or ("device" if share_of_work < 1e8 else "host")      # bvh: "host" | "device" forces one
         if share_bvh == "auto":
             share_bvh = self.world >= 4
         if device in scene._ctx:

@@ -47,11 +47,13 @@ if rank == 0:
     print("PATH OK")
 # the BVH built on rank 0 only and broadcast (gdpt_create_ex + gdpt_bvh_adopt)
 sc2 = g.Scene(sc.a)
-r = DistributedRenderer(sc2, rank, dist, torch, solver="gather", share_bvh=True)
-assert sc2.bvh_info(rank)[:3] == sc.bvh_info(rank)[:3]
+r = DistributedRenderer(sc2, rank, dist, torch, solver="gather", share_bvh=True, bvh="host")
+ref = g.Scene(sc.a); ref.context(rank, bvh="host")
+assert sc2.bvh_info(rank)[:3] == ref.bvh_info(rank)[:3]
 shared = r.render(spp=2, precision="f64", to_host=True)
 if rank == 0:
-    assert np.array_equal(shared["primal"], res["gather"]["primal"]) and np.array_equal(shared["poisson"], res["gather"]["poisson"])
+    assert np.allclose(shared["primal"], res["gather"]["primal"], rtol=1e-12, atol=1e-15)       # another tree (host-built), the same hits
+    assert np.linalg.norm(shared["poisson"] - res["gather"]["poisson"]) <= 1e-9 * np.linalg.norm(shared["poisson"])
     print("SHARED BVH OK")
 dist.barrier()
 dist.destroy_process_group()
