@@ -306,3 +306,34 @@ def test_fft_dct1_device_functions_on_the_host(tmp_path):
     r = json.loads(subprocess.check_output([str(exe)] + [str(n) for n in sizes], timeout=300))
     for n in sizes:
         assert r[str(n)]["roundtrip"] < 1e-14 and r[str(n)]["dct_rel_err"] < 1e-13, (n, r[str(n)])
+
+
+# ------------------------------------------------------------------ bench.py: the reference arm and the helpers that need no GPU
+def test_bench_reference_arm_line_and_affine_cost_model():
+    """`bench.py --impl reference` on a small film: one JSON line with the contract's keys, the affine cost model
+    (fixed_s + spp * per_spp_s reproduces ms_per_step), the share of the stand-in ray caster, and the workload string the
+    native arm prints for the same configuration."""
+    import json
+    import subprocess
+    import sys
+    from oracle import ref
+    if not ref.scenes_available():
+        pytest.skip("oracle/_ref not built")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--scene", "cbox_gdpt_64", "--steps", "2", "--warmup", "1",
+                          "--ref-total-seconds", "3", "--cpu-seconds", "1"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype", "data", "config", "impl", "cpu_baseline", "e2e"):
+        assert k in d, k
+    assert d["impl"] == "reference" and d["dtype"] == "f64" and d["vs_baseline"] is None and d["e2e"]["value"] == d["value"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "reference" and cb["cores"] >= 1 and 0.0 <= cb["rtc_fraction"] <= 1.0
+    assert abs((cb["fixed_s"] + 4 * cb["per_spp_s"]) * 1e3 - d["ms_per_step"]) < 1e-6 * d["ms_per_step"] + 1e-9        # cbox_gdpt_64: 4 spp
+    assert cb["value_if_ray_casting_were_free"] >= cb["value"]
+    sys.path.insert(0, ROOT)
+    import bench
+    assert d["config"]["workload"] == bench.workload_name("cbox_gdpt_64", 64, 64, 4)
+    m = bench.synthetic_camera(1)
+    assert np.allclose(m[:3, :3].T @ m[:3, :3], np.eye(3), atol=1e-12) and np.allclose(m[3], [0, 0, 0, 1])
