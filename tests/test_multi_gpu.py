@@ -52,8 +52,11 @@ ref = g.Scene(sc.a); ref.context(rank, bvh="host")
 assert sc2.bvh_info(rank)[:3] == ref.bvh_info(rank)[:3]
 shared = r.render(spp=2, precision="f64", to_host=True)
 if rank == 0:
-    assert np.allclose(shared["primal"], res["gather"]["primal"], rtol=1e-12, atol=1e-15)       # another tree (host-built), the same hits
-    assert np.linalg.norm(shared["poisson"] - res["gather"]["poisson"]) <= 1e-9 * np.linalg.norm(shared["poisson"])
+    one = g.gradient_path_render(ref, spp=2, precision="f64")          # the same (host-built) tree on one GPU
+    assert np.allclose(shared["primal"], one.primal, rtol=1e-12, atol=1e-15)
+    assert np.linalg.norm(shared["poisson"] - one.poisson) <= 1e-9 * np.linalg.norm(one.poisson)
+    # against the device-built tree of the runs above: the same hits but for depth ties decided by a float box test
+    assert np.isclose(shared["primal"], res["gather"]["primal"], rtol=1e-9, atol=1e-12).mean() > 0.999
     print("SHARED BVH OK")
 dist.barrier()
 dist.destroy_process_group()
@@ -76,8 +79,18 @@ def test_distributed_solve_equals_gather_solve_nccl(tmp_path, world):
     for r in range(world):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), GDPT_PORT=port, GDPT_ROOT=ROOT, MASTER_ADDR="127.0.0.1")
         procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
-    outs = [p.communicate(timeout=600)[0].decode() for p in procs]
-    assert all(p.returncode == 0 for p in procs), outs
+    import time
+    t0 = time.time()
+    while any(p.poll() is None for p in procs):
+        if any(p.poll() not in (None, 0) for p in procs) or time.time() - t0 > 420:      # one rank failed (or the run hangs): stop the rest
+            time.sleep(2)
+            for p in procs:
+                if p.poll() is None:
+                    p.kill()
+            break
+        time.sleep(0.5)
+    outs = [p.communicate()[0].decode() for p in procs]
+    assert all(p.returncode == 0 for p in procs), [o[-3000:] for o in outs]
     assert "OK" in outs[0] and "PATH OK" in outs[0]
 
 
