@@ -188,12 +188,15 @@ __global__ void __launch_bounds__(128) k_path_generate(DScene<R> sc, WaveParams 
 template <typename R, int MS, bool FIRST>
 __global__ void __launch_bounds__(128) k_path_shade(DScene<R> sc, WaveParams wp, const PathState<R> *in, const HitRec *hits, const RayF *shadow_in,
                                                     const HitRec *shadow_hits, const int *in_count, int in_max,
-                                                    PathState<R> *out, RayF *rays_out, RayF *shadow_out, int *out_count) {
+                                                    PathState<R> *out, RayF *rays_out, RayF *shadow_out, int *out_count, const int *order = nullptr) {
     int n = FIRST ? in_max : min(*in_count, in_max);
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    // order: the permutation the rays were traced in — generic-material scenes shade in that order so that a warp meets one
+    // material (gdpt_ctx::shade_sorted, as in k_bounce)
+    const int i = (order && j < n) ? __ldg(order + j) : j;
     bool alive = false;
     PathState<R> ps; RayF ray, shadow;
-    if (i < n) {
+    if (j < n) {
         load_soa(ps, in, i, wp.n_paths);
         Hit h = load_hit(hits + i);
         if (FIRST) {

@@ -95,7 +95,8 @@ int run_path_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
         if (sorting) GD_CUDA(cudaMemsetAsync(wp.sort_hist, 0, (size_t)n_bins * sizeof(int), st));
         int *cin = cnt + which, *cout = cnt + (which ^ 1);
         GD_CUDA(cudaMemsetAsync(cout, 0, sizeof(int), st));
-        k_path_shade<R, MS, false><<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, hits, shadow, shadow_hits, cin, count, nxt, rays, shadow_next, cout);
+        k_path_shade<R, MS, false><<<blocks_for(count, 128), 128, 0, st>>>(sc, wp, cur, hits, shadow, shadow_hits, cin, count, nxt, rays, shadow_next, cout,
+                                                                           c->shade_sorted ? order : nullptr);
         c->stats.kernel_launches++; c->stats.bounce_iterations++;
         GD_CUDA(cudaEventRecord(e2, st));
         GD_CUDA(cudaMemcpyAsync(c->h_counts, cout, sizeof(int), cudaMemcpyDeviceToHost, st));
