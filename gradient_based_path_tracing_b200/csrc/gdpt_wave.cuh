@@ -33,7 +33,7 @@ inline void launch_trace(gdpt_ctx *c, const RayF *rays, HitRec *hits, int n, con
     else if constexpr (EXACT) launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, st, rays, hits, n, order, count_ptr);
     else switch (c->trace_variant) {
 #define GD_V(v) case v: launch_trace_v<EXACT, false, v>(c, st, rays, hits, n, order, count_ptr); break;
-        GD_V(0) GD_V(10000) GD_V(40000) GD_V(120000)
+        GD_V(0) GD_V(40000) GD_V(120000) GD_V(200000)
 #undef GD_V
         default: launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, st, rays, hits, n, order, count_ptr);
     }

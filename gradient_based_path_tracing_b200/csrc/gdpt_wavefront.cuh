@@ -256,7 +256,8 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 //   OCC  0: launch bound 8 blocks/SM (64 regs), 1: 7 (72), 2: 9 (56), 3: 10 (48)
 //   LOOP (x10000) bit 0: a node step that lands on a leaf tests it in the same trip; bit 1: triangle test without early exits;
 //        bit 2: one pop site per trip (node misses and finished leaves pop together at the top of the next trip);
-//        bit 3 (with bit 2): leaf children are tested inside their parent's node step (no leaf trips)
+//        bit 3 (with bit 2): leaf children are tested inside their parent's node step (no leaf trips);
+//        bit 4: streaming (evict-first) loads of rays / permutation and stores of hits
 // COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
 // (bench.py derives the algorithmic bytes per ray from them; never in timed runs).
 constexpr int trace_variant_depth(int v) { return ((v / 100) % 10) == 0 ? 20 : ((v / 100) % 10) == 1 ? 16 : ((v / 100) % 10) == 2 ? 12 : 8; }
@@ -274,9 +275,11 @@ __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(
     TraceStackT<DEPTH> st; st.smem = stack;
     unsigned long long tn = 0, tp = 0;
     for (int j = blockIdx.x * TRACE_BLOCK + threadIdx.x; j < n; j += gridDim.x * TRACE_BLOCK) {
-        const int i = order ? __ldg(order + j) : j;   // sorted launch: follow the permutation, rays stay where they are
+        const int i = order ? ((LOOP & 16) ? __ldcs(order + j) : __ldg(order + j)) : j;   // sorted launch: follow the permutation, rays stay where they are
         const float4 *rp = (const float4 *)(rays + i);
-        float4 a = __ldg(rp), b = __ldg(rp + 1);
+        // LOOP bit 4: the ray / permutation / hit streams are touched once — streaming loads and stores keep them from
+        // displacing the tree in L1 / L2
+        float4 a = (LOOP & 16) ? __ldcs(rp) : __ldg(rp), b = (LOOP & 16) ? __ldcs(rp + 1) : __ldg(rp + 1);
         RayState r; r.init(a, b);
         unsigned cn = 0, cp = 0;
         if (!(b.w < a.w) && bvh.n_nodes != 0) {   // tfar < tnear: never hits
@@ -303,7 +306,11 @@ __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(
                 if (ANY && r.hit.shape_id >= 0) break;
             }
         }
-        store_hit(hits + i, r.hit);
+        if (LOOP & 16) {
+            int4 *d = reinterpret_cast<int4 *>(hits + i);
+            __stcs(d, make_int4(__float_as_int(r.hit.t), __float_as_int(r.hit.u), __float_as_int(r.hit.v), r.hit.shape_id));
+            __stcs(d + 1, make_int4(r.hit.prim_id, 0, 0, 0));
+        } else store_hit(hits + i, r.hit);
         if (COUNT) { tn += cn; tp += cp; }
     }
     if (COUNT) {

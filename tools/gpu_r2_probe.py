@@ -20,24 +20,9 @@ if "sched" in what:
         print("%-44s %7.1f ms  %7.1f Mpaths/s   mean %.6f  launches %d" % (tag, dt * 1e3, 5 * 1920 * 1080 * spp / dt / 1e6, r.primal.mean(), r.stats["kernel_launches"]), flush=True)
         sc.close()
     run("default", {})
-    run("k_bounce in traced order (shade_sorted)", {"shade_sorted": 1})
+    run("trace variant 200000 (streaming ray / hit accesses)", {"trace_variant": 200000})
     run("default again", {})
-    run("shade_sorted again", {"shade_sorted": 1})
-    base = g.Scene.named("disney_gradpath")
-    def run_d(tag, opts):
-        sc = g.Scene(base.a)
-        for k, v in opts.items():
-            sc.set_option(k, v)
-        g.gradient_path_render(sc, spp=8, precision="f32", outputs=("primal",))
-        t0 = time.perf_counter()
-        r = g.gradient_path_render(sc, spp=128, precision="f32", outputs=("primal",))
-        dt = time.perf_counter() - t0
-        print("disney %-40s %7.1f ms  %7.1f Mpaths/s" % (tag, dt * 1e3, 5 * sc.width * sc.height * 128 / dt / 1e6), flush=True)
-        sc.close()
-    run_d("default", {})
-    run_d("shade_sorted", {"shade_sorted": 1})
-    run_d("default again", {})
-    run_d("shade_sorted again", {"shade_sorted": 1})
+    run("trace variant 200000 again", {"trace_variant": 200000})
 if "records" in what:
     for name in ["cbox_gdpt_64", "cbox_gdpt_d2", "veach_mi_small", "sponza_small", "disney_small"]:
         z = np.load("tests/golden/records_%s.npz" % name)
