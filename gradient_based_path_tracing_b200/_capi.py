@@ -70,7 +70,8 @@ EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_create_e
            "gdpt_render_path", "gdpt_render_path_accumulate_device", "gdpt_path_samples", "gdpt_sample_light", "gdpt_occluded", "gdpt_render_aux",
            "gdpt_merge_rows_device", "gdpt_poisson_dist_rows_forward", "gdpt_poisson_dist_columns", "gdpt_poisson_dist_rows_inverse",
            "gdpt_poisson_device_noalloc", "gdpt_set_option", "gdpt_host_alloc", "gdpt_host_free",
-           "gdpt_multi_create", "gdpt_multi_render", "gdpt_multi_get_stats", "gdpt_multi_device_count", "gdpt_multi_destroy"]
+           "gdpt_multi_create", "gdpt_multi_render", "gdpt_multi_get_stats", "gdpt_multi_device_count", "gdpt_multi_destroy",
+           "gdpt_smallgdpt_render"]
 
 _lib = None
 
@@ -109,6 +110,7 @@ def lib():
         L.gdpt_multi_device_count.argtypes = [vp]
         L.gdpt_multi_destroy.argtypes = [vp]
         L.gdpt_multi_destroy.restype = None
+        L.gdpt_smallgdpt_render.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(GdptImages), dp]
         L.gdpt_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
         L.gdpt_host_free.argtypes = [vp]
         L.gdpt_host_free.restype = None

@@ -201,6 +201,20 @@ int gdpt_multi_get_stats(gdpt_multi *m, gdpt_stats *out);      /* counters summe
 int gdpt_multi_device_count(gdpt_multi *m);
 void gdpt_multi_destroy(gdpt_multi *m);
 
+/* ---- the reference's second program, small_gdpt.cpp: main() (:439-563) on its built-in scene of eight
+ * spheres (:60-69, camera :55-57) — generatePath (:153-197), shiftPath (:200-285: random-number replay, reconnection at the
+ * first diffuse-diffuse edge), pathContrib / pathProb (:288-352), the balance-heuristic weights and the five running sums
+ * (:470-527), then the merge (:530-539) and fourierSolve(.., 0.04, ..) (:541) by the product's own kernels.  It needs no
+ * context and no scene description.  out: host images, height*width*3 doubles each, rows as the program stores them (top row
+ * first); dx / dy are the SIGNED merged gradients (the program writes their absolute values to image_dx.pfm / image_dy.pfm,
+ * :549-550); any pointer may be NULL.  rng_mode GDPT_SMALLGDPT_ROWS keeps the program's erand48 streams (one per film row,
+ * :462): the images equal the compiled program's up to the device libm's last bit in sin / cos; GDPT_SMALLGDPT_PIXELS gives
+ * every pixel a stream and a thread (the same estimator on other random numbers).  render_ms (may be NULL): device time of the
+ * sampling kernel. ---- */
+#define GDPT_SMALLGDPT_ROWS 0
+#define GDPT_SMALLGDPT_PIXELS 1
+int gdpt_smallgdpt_render(int device, int width, int height, int spp, int rng_mode, gdpt_images *out, double *render_ms);
+
 int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out);
 /* Scheduling / tuning knobs of a context (no effect on results; no counterpart in the reference, whose only knob is -t threads,
  * src/main.cpp:20-23).  "async_waves" 1|0: launch the waves of a render from the first wave's measured path counts without
