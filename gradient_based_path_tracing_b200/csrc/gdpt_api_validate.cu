@@ -29,7 +29,7 @@ struct Scratch {   // device scratch that frees itself
     }
     template <typename T> int put(T **out, const T *host, size_t n) {
         if (int r = alloc(out, n)) return r;
-        if (host && n) GD_CUDA(cudaMemcpy(*out, host, n * sizeof(T), cudaMemcpyHostToDevice));
+        if (host && n) { GD_CUDA(cudaMemcpy(*out, host, n * sizeof(T), cudaMemcpyHostToDevice)); GD_CUDA(cudaStreamSynchronize((cudaStream_t)0)); }
         return 0;
     }
 };

@@ -66,7 +66,10 @@ struct DevBuf {
 
 template <typename T> int upload(DevBuf &b, const std::vector<T> &v) {
     if (int r = b.ensure(std::max<size_t>(v.size() * sizeof(T), 16))) return r;
-    if (!v.empty()) GD_CUDA(cudaMemcpy(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    if (!v.empty()) {
+        GD_CUDA(cudaMemcpy(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        GD_CUDA(cudaStreamSynchronize((cudaStream_t)0));   // pageable source: the call may return before the DMA lands, and the readers run on non-blocking streams
+    }
     return 0;
 }
 
