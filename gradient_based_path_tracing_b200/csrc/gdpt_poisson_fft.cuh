@@ -41,46 +41,61 @@ __device__ __forceinline__ double2 cmulc(double2 a, double2 b) { return make_dou
 __device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
 
+// Where element e of the line lives in shared memory.  An element is 16 bytes, so a warp's access is served a quarter-warp
+// (8 lanes, 8 sixteen-byte banks) at a time.  In the natural layout the passes with butterfly stride 4, 2 and 1 (and the final
+// radix-2 pass of an odd log2 P) put 2 to 4 lanes of a quarter-warp on one bank: 34 % of the kernel's shared-memory wavefronts
+// were replays (ncu, l1tex__data_bank_conflicts_pipe_lsu_mem_shared, profiles/r2_k_dct_cols_final.txt).  XOR-ing the low three
+// index bits with (x ^ x<<1), x = bits 3..4, is the cheapest linear map that makes EVERY access pattern of both FFT directions
+// at P = 2048 / 4096 / 8192 and the contiguous sweeps conflict-free (exhaustive search over the 3-bit XOR masks of bits 3..6).
+__host__ __device__ __forceinline__ int fft_sw(int e) { const int x = (e >> 3) & 3; return e ^ (x ^ (x << 1)); }
+
 // In-place forward FFT of s[0..P) (natural order in, digit-reversed out), all threads of the block.
 // tw: the per-pass twiddle table (DctPlan::tw), staged in shared memory by the kernels: only w^j is read, w^2j and w^3j are
 // formed in registers — the FP64 pipe idles while the shared-memory / L1 pipe is the busy one (ncu: l1tex 94 %).
-__device__ inline void fft_forward(double2 *s, int P, int logP, const double2 *__restrict__ tw) {
+// first_stage = 1: the first radix-4 pass has already been done (dct1_line forms it straight from the real line).
+__device__ inline void fft_forward(double2 *s, int P, int logP, const double2 *__restrict__ tw, int first_stage = 0) {
     int n = P, ln = logP, off = 0;        // block length of the pass, its log2, start of the pass's twiddles
-    for (int stage = 0; stage < logP / 2; stage++, off += n >> 2, n >>= 2, ln -= 2) {
+    if (first_stage) { off = n >> 2; n >>= 2; ln -= 2; }
+    for (int stage = first_stage; stage < logP / 2; stage++, off += n >> 2, n >>= 2, ln -= 2) {
         const int q4 = n >> 2, lq = ln - 2;
         for (int idx = threadIdx.x; idx < (P >> 2); idx += blockDim.x) {
             const int blk = idx >> lq, j = idx & (q4 - 1), base = (blk << ln) + j;
-            const double2 a = s[base], b = s[base + q4], c = s[base + 2 * q4], d = s[base + 3 * q4];
+            const double2 a = s[fft_sw(base)], b = s[fft_sw(base + q4)], c = s[fft_sw(base + 2 * q4)], d = s[fft_sw(base + 3 * q4)];
             const double2 t0 = cadd(a, c), t1 = csub(a, c), t2 = cadd(b, d), t3 = csub(b, d);
             const double2 y1 = make_double2(t1.x + t3.y, t1.y - t3.x), y3 = make_double2(t1.x - t3.y, t1.y + t3.x);
-            s[base] = cadd(t0, t2);
-            if (j == 0) { s[base + q4] = y1; s[base + 2 * q4] = csub(t0, t2); s[base + 3 * q4] = y3; }
+            s[fft_sw(base)] = cadd(t0, t2);
+            if (j == 0) { s[fft_sw(base + q4)] = y1; s[fft_sw(base + 2 * q4)] = csub(t0, t2); s[fft_sw(base + 3 * q4)] = y3; }
             else {
                 const double2 w1 = tw[off + j], w2 = cmul(w1, w1), w3 = cmul(w2, w1);
-                s[base + q4] = cmul(y1, w1);
-                s[base + 2 * q4] = cmul(csub(t0, t2), w2);
-                s[base + 3 * q4] = cmul(y3, w3);
+                s[fft_sw(base + q4)] = cmul(y1, w1);
+                s[fft_sw(base + 2 * q4)] = cmul(csub(t0, t2), w2);
+                s[fft_sw(base + 3 * q4)] = cmul(y3, w3);
             }
         }
         __syncthreads();
     }
     if (logP & 1) {
         for (int idx = threadIdx.x; idx < (P >> 1); idx += blockDim.x) {
-            const double2 a = s[2 * idx], b = s[2 * idx + 1];
-            s[2 * idx] = cadd(a, b); s[2 * idx + 1] = csub(a, b);
+            const double2 a = s[fft_sw(2 * idx)], b = s[fft_sw(2 * idx + 1)];
+            s[fft_sw(2 * idx)] = cadd(a, b); s[fft_sw(2 * idx + 1)] = csub(a, b);
         }
         __syncthreads();
     }
 }
 
 // The structural inverse of fft_forward (digit-reversed in, natural out), unscaled: fft_inverse(fft_forward(x)) = P x.
-__device__ inline void fft_inverse(double2 *s, int P, int logP, const double2 *__restrict__ tw) {
+// keep: only outputs with index < keep are needed (the last pass does not store the others);
+// pre (may be null): element e is multiplied by pre[e] as the first stage loads it — the filter product of the circular
+// convolution rides on the first pass instead of being a shared-memory pass (and a barrier) of its own.
+__device__ inline void fft_inverse(double2 *s, int P, int logP, const double2 *__restrict__ tw, const double2 *__restrict__ pre = nullptr, int keep = 0x7fffffff) {
     if (logP & 1) {
         for (int idx = threadIdx.x; idx < (P >> 1); idx += blockDim.x) {
-            const double2 a = s[2 * idx], b = s[2 * idx + 1];
-            s[2 * idx] = cadd(a, b); s[2 * idx + 1] = csub(a, b);
+            double2 a = s[fft_sw(2 * idx)], b = s[fft_sw(2 * idx + 1)];
+            if (pre) { a = cmul(a, __ldg(pre + 2 * idx)); b = cmul(b, __ldg(pre + 2 * idx + 1)); }
+            s[fft_sw(2 * idx)] = cadd(a, b); s[fft_sw(2 * idx + 1)] = csub(a, b);
         }
         __syncthreads();
+        pre = nullptr;
     }
     int n = (logP & 1) ? 8 : 4, ln = (logP & 1) ? 3 : 2, off = fft_twiddle_count(P, logP);
     for (int stage = 0; stage < logP / 2; stage++, n <<= 2, ln += 2) {
@@ -88,13 +103,16 @@ __device__ inline void fft_inverse(double2 *s, int P, int logP, const double2 *_
         off -= q4;
         for (int idx = threadIdx.x; idx < (P >> 2); idx += blockDim.x) {
             const int blk = idx >> lq, j = idx & (q4 - 1), base = (blk << ln) + j;
-            double2 u0 = s[base], u1 = s[base + q4], u2 = s[base + 2 * q4], u3 = s[base + 3 * q4];
+            double2 u0 = s[fft_sw(base)], u1 = s[fft_sw(base + q4)], u2 = s[fft_sw(base + 2 * q4)], u3 = s[fft_sw(base + 3 * q4)];
+            if (stage == 0 && pre) { u0 = cmul(u0, __ldg(pre + base)); u1 = cmul(u1, __ldg(pre + base + q4)); u2 = cmul(u2, __ldg(pre + base + 2 * q4)); u3 = cmul(u3, __ldg(pre + base + 3 * q4)); }
             if (j != 0) { const double2 w1 = tw[off + j], w2 = cmul(w1, w1), w3 = cmul(w2, w1); u1 = cmulc(u1, w1); u2 = cmulc(u2, w2); u3 = cmulc(u3, w3); }
             const double2 t0 = cadd(u0, u2), t1 = csub(u0, u2), t2 = cadd(u1, u3), t3 = csub(u1, u3);
-            s[base] = cadd(t0, t2);
-            s[base + q4] = make_double2(t1.x - t3.y, t1.y + t3.x);      // u0 + i u1 - u2 - i u3
-            s[base + 2 * q4] = csub(t0, t2);
-            s[base + 3 * q4] = make_double2(t1.x + t3.y, t1.y - t3.x);  // u0 - i u1 - u2 + i u3
+            s[fft_sw(base)] = cadd(t0, t2);
+            if (n < P || base + q4 < keep) s[fft_sw(base + q4)] = make_double2(t1.x - t3.y, t1.y + t3.x);      // u0 + i u1 - u2 - i u3
+            if (n < P || base + 2 * q4 < keep) {
+                s[fft_sw(base + 2 * q4)] = csub(t0, t2);
+                s[fft_sw(base + 3 * q4)] = make_double2(t1.x + t3.y, t1.y - t3.x);  // u0 - i u1 - u2 + i u3
+            }
         }
         __syncthreads();
     }
@@ -103,24 +121,33 @@ __device__ inline void fft_inverse(double2 *s, int P, int logP, const double2 *_
 // xs[0..N) (real, shared memory) -> its DCT-I in place.  s: P complex of shared memory.
 __device__ inline void dct1_line(const DctPlan &pl, double *xs, double2 *s, const double2 *tw) {
     const int M = pl.M, P = pl.P;
-    for (int n = threadIdx.x; n < P; n += blockDim.x) {
-        double2 a = make_double2(0.0, 0.0);
-        if (n < M) {
-            const int e = 2 * n, o = 2 * n + 1;
-            const double re = xs[e <= M ? e : 2 * M - e], im = xs[o <= M ? o : 2 * M - o];
-            a = cmulc(make_double2(re, im), __ldg(pl.chirp + n));
+    // z_n = (y_2n + i y_2n+1) conj(w_n) for n < M, zero up to P — and since M <= P/2 the upper half of the padded line is all
+    // zeros, so the first radix-4 pass (block length P: inputs j, j + P/4, j + P/2, j + 3P/4) has c = d = 0 and is formed here
+    // from the real line directly: no store of the padded line, no pass over it
+    auto z = [&](int n) {
+        if (n >= M) return make_double2(0.0, 0.0);
+        const int e = 2 * n, o = 2 * n + 1;
+        return cmulc(make_double2(xs[e <= M ? e : 2 * M - e], xs[o <= M ? o : 2 * M - o]), __ldg(pl.chirp + n));
+    };
+    const int q4 = P >> 2;
+    for (int j = threadIdx.x; j < q4; j += blockDim.x) {
+        const double2 a = z(j), b = z(j + q4);
+        const double2 y1 = make_double2(a.x + b.y, a.y - b.x), y3 = make_double2(a.x - b.y, a.y + b.x), y2 = csub(a, b);
+        s[fft_sw(j)] = cadd(a, b);
+        if (j == 0) { s[fft_sw(q4)] = y1; s[fft_sw(2 * q4)] = y2; s[fft_sw(3 * q4)] = y3; }
+        else {
+            const double2 w1 = tw[j], w2 = cmul(w1, w1), w3 = cmul(w2, w1);
+            s[fft_sw(j + q4)] = cmul(y1, w1);
+            s[fft_sw(j + 2 * q4)] = cmul(y2, w2);
+            s[fft_sw(j + 3 * q4)] = cmul(y3, w3);
         }
-        s[n] = a;
     }
     __syncthreads();
-    fft_forward(s, P, pl.logP, tw);
-    for (int i = threadIdx.x; i < P; i += blockDim.x) s[i] = cmul(s[i], __ldg(pl.bhat + i));
-    __syncthreads();
-    fft_inverse(s, P, pl.logP, tw);
-    for (int k = threadIdx.x; k < M; k += blockDim.x) s[k] = cmulc(s[k], __ldg(pl.chirp + k));     // Z_k
-    __syncthreads();
+    fft_forward(s, P, pl.logP, tw, 1);
+    fft_inverse(s, P, pl.logP, tw, pl.bhat, M);
     for (int k = threadIdx.x; k < M; k += blockDim.x) {
-        const double2 zk = s[k], zm = s[k == 0 ? 0 : M - k], wp = __ldg(pl.wpost + k);
+        const int km = k == 0 ? 0 : M - k;                                        // Z_k = s_k conj(w_k), formed where it is used
+        const double2 zk = cmulc(s[fft_sw(k)], __ldg(pl.chirp + k)), zm = cmulc(s[fft_sw(km)], __ldg(pl.chirp + km)), wp = __ldg(pl.wpost + k);
         const double ex = 0.5 * (zk.x + zm.x), ey = 0.5 * (zk.y - zm.y);          // E = (Z_k + conj Z_(M-k)) / 2
         const double ox = 0.5 * (zk.y + zm.y), oy = -0.5 * (zk.x - zm.x);         // O = (Z_k - conj Z_(M-k)) / (2i)
         (void)ey;
@@ -205,12 +232,12 @@ static __global__ void __launch_bounds__(FFT_THREADS) k_dct_plan_filter(int M, i
         double2 v = make_double2(0.0, 0.0);
         if (i < M) v = chirp[i];
         else if (P - i < M) v = chirp[P - i];       // b_(-m) = w_m
-        s[i] = v;
+        s[fft_sw(i)] = v;
     }
     __syncthreads();
     fft_forward(s, P, logP, tw);
     const double inv = 1.0 / (double)P;
-    for (int i = threadIdx.x; i < P; i += blockDim.x) bhat[i] = make_double2(s[i].x * inv, s[i].y * inv);
+    for (int i = threadIdx.x; i < P; i += blockDim.x) { const double2 v = s[fft_sw(i)]; bhat[i] = make_double2(v.x * inv, v.y * inv); }
 }
 
 #endif  // GDPT_FFT_HOST_TEST

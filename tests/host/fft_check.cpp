@@ -40,9 +40,9 @@ int main(int argc, char **argv) {
             chirp[i] = make_double2(cospi((double)q / M), sinpi((double)q / M));
             wpost[i] = make_double2(cospi((double)i / M), -sinpi((double)i / M));
         }
-        for (int i = 0; i < P; i++) { double2 v = make_double2(0, 0); if (i < M) v = chirp[i]; else if (P - i < M) v = chirp[P - i]; s[i] = v; }
+        for (int i = 0; i < P; i++) { double2 v = make_double2(0, 0); if (i < M) v = chirp[i]; else if (P - i < M) v = chirp[P - i]; s[fft_sw(i)] = v; }   // the line buffer's layout: fft_sw
         fft_forward(s.data(), P, logP, tw.data());
-        for (int i = 0; i < P; i++) bhat[i] = make_double2(s[i].x / P, s[i].y / P);
+        for (int i = 0; i < P; i++) bhat[i] = make_double2(s[fft_sw(i)].x / P, s[fft_sw(i)].y / P);
         // round trip of the two FFT routines
         std::vector<double2> r(P);
         srand(N);
