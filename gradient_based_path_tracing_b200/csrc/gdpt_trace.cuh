@@ -5,7 +5,7 @@
 //  * one thread per ray; the ray is the FLOAT ray Embree would be handed;
 //  * "while-while" traversal: all lanes of a warp walk inner nodes until each holds a leaf
 //    (or is done), then all test leaves — the two phases never interleave inside a warp;
-//  * node = one 128-byte line fetched as 8 x 16-byte __ldg loads, 4 slab tests;
+//  * node = one 128-byte line: six box planes fetched as 3 x 32-byte loads (LDG.E.ENL2.256) + the child ids, 4 slab tests;
 //  * children visited front to back; the traversal stack lives in shared memory
 //    ([level][thread] -> bank-conflict free) with a small local-memory spill;
 //  * hit rule: tnear < t <= tfar, closest t, ties -> smaller shape id, then smaller
@@ -145,7 +145,13 @@ GD_D int trace_pop(const ST &st, int &sp, float best) {
 // EAGER = 1 (EXACT_E selects the triangle arithmetic): children that are leaves and pass the slab test are tested right here,
 // in the node step, instead of being visited in a trip of their own — the leaf code then runs for every lane whose node has a
 // hit leaf child at this trip, not for the two or three lanes of a warp that happen to sit on a leaf.
-template <int SORT = 0, int FMA = 0, bool NOPOP = false, int EAGER = 0, bool EXACT_E = false, typename ST, typename RS>
+// 256-bit global load (sm_100: LDG.E.ENL2.256): two of the node's float4 planes per instruction and per L1 wavefront.
+GD_D void ld256(const float4 *p, float4 &a, float4 &b) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
+// WIDE: the node's six planes are fetched with three 256-bit loads instead of six 128-bit ones.
+template <int SORT = 0, int FMA = 0, bool NOPOP = false, int EAGER = 0, bool EXACT_E = false, bool WIDE = false, typename ST, typename RS>
 GD_D int trace_node(const DBvh &bvh, int cur, RS &r, ST &st, int &sp, unsigned *n_prims = nullptr) {
     const float4 *n = bvh.nodes + 8 * (size_t)cur;
     const float INF = __int_as_float(0x7f800000);
@@ -167,7 +173,9 @@ GD_D int trace_node(const DBvh &bvh, int cur, RS &r, ST &st, int &sp, unsigned *
             dist[k] = (cid[k] != 0 && tmn <= tmx) ? tmn : INF;
         }
     } else {
-    float4 lox = __ldg(n), loy = __ldg(n + 1), loz = __ldg(n + 2), hix = __ldg(n + 3), hiy = __ldg(n + 4), hiz = __ldg(n + 5);
+    float4 lox, loy, loz, hix, hiy, hiz;
+    if (WIDE) { ld256(n, lox, loy); ld256(n + 2, loz, hix); ld256(n + 4, hiy, hiz); }
+    else { lox = __ldg(n); loy = __ldg(n + 1); loz = __ldg(n + 2); hix = __ldg(n + 3); hiy = __ldg(n + 4); hiz = __ldg(n + 5); }
     int4 ch = __ldg((const int4 *)(n + 6));
     cid[0] = ch.x; cid[1] = ch.y; cid[2] = ch.z; cid[3] = ch.w;
     const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
@@ -240,7 +248,7 @@ GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], floa
     TraceStack st; st.smem = smem_stack;
     int sp = 0, cur = 0;
     while (cur != TRACE_DONE) {
-        while (cur >= 0) { if (COUNT) (*n_nodes)++; cur = trace_node<0, 0>(bvh, cur, r, st, sp); }
+        while (cur >= 0) { if (COUNT) (*n_nodes)++; cur = trace_node<0, 0, false, 0, false, true>(bvh, cur, r, st, sp); }
         if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? n_prims : nullptr);
     }
     return r.hit;
@@ -254,7 +262,7 @@ GD_D bool trace_occluded(const DBvh &bvh, const float o[3], const float d[3], fl
     TraceStack st; st.smem = smem_stack;
     int sp = 0, cur = 0;
     while (cur != TRACE_DONE) {
-        while (cur >= 0) cur = trace_node<0, 0>(bvh, cur, r, st, sp);
+        while (cur >= 0) cur = trace_node<0, 0, false, 0, false, true>(bvh, cur, r, st, sp);
         if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, nullptr);
         if (r.hit.shape_id >= 0) return true;
     }
