@@ -48,6 +48,11 @@ class GdptRenderParams(C.Structure):
                 ("strip_count", C.c_int32), ("strip_phase", C.c_int32)]
 
 
+class GdptL1Params(C.Structure):
+    _fields_ = [("irls_iterations", C.c_int32), ("cg_iterations", C.c_int32), ("start", C.c_int32), ("reweight_primal", C.c_int32),
+                ("alpha", C.c_double), ("epsilon", C.c_double), ("cg_tolerance", C.c_double)]
+
+
 class GdptImages(C.Structure):
     _fields_ = [("primal", dp), ("dx", dp), ("dy", dp), ("poisson", dp)]
 
@@ -64,6 +69,8 @@ class GdptDistGeom(C.Structure):
 
 
 # every symbol include/gdpt.h declares
+L1_START_FOURIER, L1_START_PRIMAL, L1_START_OUT = 0, 1, 2
+
 EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_create_ex", "gdpt_bvh_info", "gdpt_bvh_adopt", "gdpt_destroy", "gdpt_scene_bounds", "gdpt_render",
            "gdpt_render_accumulate_device", "gdpt_merge_device", "gdpt_poisson", "gdpt_poisson_device", "gdpt_get_stats",
            "gdpt_synchronize", "gdpt_set_stream", "gdpt_traversal_counts", "gdpt_measure_l2_read", "gdpt_sample_primary", "gdpt_intersect", "gdpt_bsdf", "gdpt_grad_samples", "gdpt_pcg_fill",
@@ -71,7 +78,7 @@ EXPORTS = ["gdpt_last_error", "gdpt_device_count", "gdpt_create", "gdpt_create_e
            "gdpt_merge_rows_device", "gdpt_poisson_dist_rows_forward", "gdpt_poisson_dist_columns", "gdpt_poisson_dist_rows_inverse",
            "gdpt_poisson_device_noalloc", "gdpt_set_option", "gdpt_host_alloc", "gdpt_host_free",
            "gdpt_multi_create", "gdpt_multi_render", "gdpt_multi_get_stats", "gdpt_multi_device_count", "gdpt_multi_destroy",
-           "gdpt_smallgdpt_render"]
+           "gdpt_smallgdpt_render", "gdpt_poisson_l1", "gdpt_poisson_l1_device"]
 
 _lib = None
 
@@ -111,6 +118,8 @@ def lib():
         L.gdpt_multi_destroy.argtypes = [vp]
         L.gdpt_multi_destroy.restype = None
         L.gdpt_smallgdpt_render.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(GdptImages), dp]
+        L.gdpt_poisson_l1.argtypes = [C.c_int, C.c_int, C.c_int, dp, dp, dp, C.POINTER(GdptL1Params), dp, dp]
+        L.gdpt_poisson_l1_device.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.POINTER(GdptL1Params), vp, dp]
         L.gdpt_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
         L.gdpt_host_free.argtypes = [vp]
         L.gdpt_host_free.restype = None

@@ -8,7 +8,7 @@ B="$HERE/../_build"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 --expt-relaxed-constexpr --extended-lambda -Xcompiler -fPIC -Xcompiler -O3 ${GDPT_NVCC_EXTRA:-}"
 mkdir -p "$B"
-SRCS="gdpt_api.cu gdpt_api_validate.cu gdpt_wave_f64.cu gdpt_wave_f32.cu gdpt_path_f64.cu gdpt_path_f32.cu gdpt_validate_f64.cu gdpt_validate_f32.cu gdpt_poisson.cu gdpt_poisson_noalloc.cu gdpt_multi.cu gdpt_bvh_gpu.cu gdpt_textures.cu gdpt_shift_f64.cu gdpt_shift_f32.cu gdpt_smallgdpt_f64.cu"
+SRCS="gdpt_api.cu gdpt_api_validate.cu gdpt_wave_f64.cu gdpt_wave_f32.cu gdpt_path_f64.cu gdpt_path_f32.cu gdpt_validate_f64.cu gdpt_validate_f32.cu gdpt_poisson.cu gdpt_poisson_l1.cu gdpt_poisson_noalloc.cu gdpt_multi.cu gdpt_bvh_gpu.cu gdpt_textures.cu gdpt_shift_f64.cu gdpt_shift_f32.cu gdpt_smallgdpt_f64.cu"
 pids=(); OBJS=()
 newest_hdr=$(ls -t "$HERE"/*.cuh "$HERE"/*.h "$HERE/../../include/gdpt.h" | head -1)
 for f in $SRCS; do

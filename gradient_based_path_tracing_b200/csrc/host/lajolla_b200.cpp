@@ -57,10 +57,10 @@ static void describe_scene(const FlatScene &s) {
 
 int main(int argc, char *argv[]) {
     if (argc <= 1) {
-        std::cout << "[Usage] ./lajolla_b200 [-o output_file_name] [-overlay camera.gdpt] [-spp n] [-precision f32|f64] [-offsets reference|shift] [-device d] [-gpus n] [-seed s] filename.gdpt[.z]" << std::endl;
+        std::cout << "[Usage] ./lajolla_b200 [-o output_file_name] [-overlay camera.gdpt] [-spp n] [-precision f32|f64] [-offsets reference|shift] [-reconstruct l2|l1] [-device d] [-gpus n] [-seed s] filename.gdpt[.z]" << std::endl;
         return 0;
     }
-    std::string outputfile, overlay, precision = "f32", offsets = "reference";
+    std::string outputfile, overlay, precision = "f32", offsets = "reference", reconstruct = "l2";
     int spp = 0, device = 0, gpus = 1; unsigned long long seed = 0;
     bool describe = false;
     int integrator_override = -1;   // Integrator enum value (src/scene.h:14-23): 5 Path, 7 GradPath
@@ -74,6 +74,7 @@ int main(int argc, char *argv[]) {
         else if (a == "-spp") spp = std::stoi(value());
         else if (a == "-precision") precision = value();
         else if (a == "-offsets") offsets = value();              // gradpath only: the shipped offset semantics, or shift-mapped offsets (gdpt.h)
+        else if (a == "-reconstruct") reconstruct = value();      // gradpath only: l2 = fourierSolve (render.cpp:353), l1 = IRLS (gdpt_poisson_l1) written beside it as *_l1
         else if (a == "-device") device = std::stoi(value());
         else if (a == "-gpus") gpus = std::stoi(value());         // gradpath over n GPUs of this box (gdpt_multi_*: one host thread per device)
         else if (a == "-seed") seed = std::stoull(value());
@@ -85,6 +86,7 @@ int main(int argc, char *argv[]) {
     }
     if (precision != "f32" && precision != "f64") { std::cerr << "-precision must be f32 or f64" << std::endl; return 2; }
     if (offsets != "reference" && offsets != "shift") { std::cerr << "-offsets must be reference or shift" << std::endl; return 2; }
+    if (reconstruct != "l2" && reconstruct != "l1") { std::cerr << "-reconstruct must be l2 or l1" << std::endl; return 2; }
     if (!describe && gdpt_device_count() < 1) { std::cerr << "no CUDA device: lajolla_b200 has no CPU fallback" << std::endl; return 1; }
 
     for (const std::string &filename : filenames) {
@@ -144,6 +146,15 @@ int main(int argc, char *argv[]) {
             if ((path || aux) && f.second != out.data()) continue;
             err = write_image(f.first, w, h, f.second);
             if (!err.empty()) { std::cerr << err << std::endl; return 1; }
+        }
+        if (reconstruct == "l1" && !path && !aux) {
+            std::vector<double> l1(primal.size());
+            gdpt_l1_params lp{}; lp.irls_iterations = 10; lp.cg_iterations = 100; lp.start = GDPT_L1_START_FOURIER;
+            double info[4] = {0, 0, 0, 0};
+            if (gdpt_poisson_l1(device, w, h, primal.data(), dx.data(), dy.data(), &lp, l1.data(), info) != GDPT_OK) { std::cerr << gdpt_last_error() << std::endl; return 1; }
+            err = write_image(stem + "_l1" + ext, w, h, l1.data());
+            if (!err.empty()) { std::cerr << err << std::endl; return 1; }
+            std::printf("L1 reconstruction: %d reweightings, %d conjugate-gradient steps, %.1f ms on the device -> %s\n", lp.irls_iterations, (int)info[1], info[2], (stem + "_l1" + ext).c_str());
         }
         std::cout << "Image written to " << of << std::endl;
     }

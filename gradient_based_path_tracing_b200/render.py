@@ -133,6 +133,34 @@ def fourier_solve(u, gx, gy, data_cost=0.04, device=0):
     return out
 
 
+def reconstruct_l1(u, gx, gy, data_cost=0.04, irls_iterations=10, cg_iterations=50, epsilon=0.05, cg_tolerance=1e-6, start="fourier", reweight_primal=False, device=0, return_info=False):
+    """L1 reconstruction by iteratively reweighted least squares (gdpt_poisson_l1; no counterpart in the reference's code, whose
+    only reconstruction is fourierSolve).  start: "fourier" (fourierSolve's image), "primal" (u) or an (H, W, 3) array.
+    irls_iterations=0 solves the L2 problem (all weights 1) by conjugate gradients.  reweight_primal=False keeps the primal term
+    quadratic (the image keeps the primal's mean); True is the all-L1 energy."""
+    u, gx, gy = (_capi.f64(a) for a in (u, gx, gy))
+    if u.ndim != 3 or u.shape[2] != 3 or gx.shape != u.shape or gy.shape != u.shape:
+        raise ValueError("expected three (H, W, 3) arrays")
+    h, w, _ = u.shape
+    out = np.zeros_like(u)
+    if isinstance(start, str):
+        if start not in ("fourier", "primal"):
+            raise ValueError("start must be 'fourier', 'primal' or an image")
+        mode = _capi.L1_START_FOURIER if start == "fourier" else _capi.L1_START_PRIMAL
+    else:
+        s0 = _capi.f64(start)
+        if s0.shape != u.shape:
+            raise ValueError("the starting image must have the shape of u")
+        out[...] = s0
+        mode = _capi.L1_START_OUT
+    prm = _capi.GdptL1Params(int(irls_iterations), int(cg_iterations), mode, 1 if reweight_primal else 0, float(data_cost), float(epsilon), float(cg_tolerance))
+    info = np.zeros(4)
+    _capi.check(_capi.lib().gdpt_poisson_l1(device, w, h, _capi.as_dp(u), _capi.as_dp(gx), _capi.as_dp(gy), C.byref(prm), _capi.as_dp(out), _capi.as_dp(info)))
+    if return_info:
+        return out, {"relative_residual": float(info[0]), "cg_steps": int(info[1]), "ms": float(info[2]), "eps": float(info[3])}
+    return out
+
+
 # ---- validation entry points (same device functions as the renderer) ----
 def _prec(precision):
     return {"f64": _capi.PRECISION_F64, "f32": _capi.PRECISION_F32}[precision]

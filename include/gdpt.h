@@ -201,6 +201,33 @@ int gdpt_multi_get_stats(gdpt_multi *m, gdpt_stats *out);      /* counters summe
 int gdpt_multi_device_count(gdpt_multi *m);
 void gdpt_multi_destroy(gdpt_multi *m);
 
+/* ---- L1 reconstruction.  No counterpart in the reference's code: fourierSolve (render.cpp:172-254,
+ * small_gdpt.cpp:355-436) is the L2 screened-Poisson solve and the only reconstruction either program has; this is the robust
+ * alternative of the paper its handout cites (Kettunen et al. 2015, section 5.2; handouts/final_project.tex:109-111) by
+ * iteratively reweighted least squares:
+ *   E(I) = alpha sum wU |I - u|^2 + sum_{x>=1} wX |I(x,y) - I(x-1,y) - gx(x,y)|^2 + sum_{y>=1} wY |I(x,y) - I(x,y-1) - gy(x,y)|^2,
+ * wX, wY = 1 / (eps + L1 norm over the channels of the term's residual), eps = epsilon * mean|u|, each reweighting followed by a
+ * Jacobi-preconditioned conjugate-gradient solve started from the current image.  u, gx, gy as for gdpt_poisson (the merged
+ * gradients of render.cpp:340-350; column 0 of gx and row 0 of gy are not used).  info (may be NULL): [0] relative residual of
+ * the last solve, [1] conjugate-gradient steps taken in all solves, [2] device milliseconds, [3] eps. ---- */
+#define GDPT_L1_START_FOURIER 0   /* start from fourierSolve's image (gdpt_poisson_device) */
+#define GDPT_L1_START_PRIMAL 1    /* start from u */
+#define GDPT_L1_START_OUT 2       /* `out` holds the starting image */
+typedef struct {
+    int32_t irls_iterations;  /* reweightings; 0: the L2 problem (all weights 1) by conjugate gradients */
+    int32_t cg_iterations;    /* conjugate-gradient steps per reweighting (upper bound: a solve stops at cg_tolerance) */
+    int32_t start;            /* GDPT_L1_START_* */
+    int32_t reweight_primal;  /* 0: wU = 1, only the gradient terms are reweighted (the image keeps the primal's mean exactly);
+                               * 1: the primal term is reweighted too (the all-L1 energy of the paper; pulls towards medians) */
+    double alpha;             /* <= 0: 0.04 (render.cpp:353) */
+    double epsilon;           /* <= 0: 0.05 */
+    double cg_tolerance;      /* relative residual |r| / |b|; <= 0: 1e-6 */
+} gdpt_l1_params;
+int gdpt_poisson_l1(int device, int w, int h, const double *u, const double *gx, const double *gy, const gdpt_l1_params *params,
+                    double *out, double *info);
+int gdpt_poisson_l1_device(gdpt_ctx *ctx, int w, int h, const double *d_u, const double *d_gx, const double *d_gy,
+                           const gdpt_l1_params *params, double *d_out, double *info);
+
 /* ---- the reference's second program, small_gdpt.cpp: main() (:439-563) on its built-in scene of eight
  * spheres (:60-69, camera :55-57) — generatePath (:153-197), shiftPath (:200-285: random-number replay, reconnection at the
  * first diffuse-diffuse edge), pathContrib / pathProb (:288-352), the balance-heuristic weights and the five running sums

@@ -373,6 +373,25 @@ def test_cpp_host_cli_writes_the_same_images(g, scenes, tmp_path):
         assert np.allclose(got, img.astype(np.float32), rtol=1e-6, atol=1e-9), suffix
 
 
+def test_cpp_host_cli_l1_reconstruction(g, scenes, tmp_path):
+    """lajolla_b200 -reconstruct l1 writes the IRLS image beside fourierSolve's: equal to the Python host's reconstruct_l1 on the
+    same render with the CLI's settings (10 reweightings, at most 100 conjugate-gradient steps each, started from fourierSolve)."""
+    import os
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "lajolla_b200")
+    out = tmp_path / "cb.pfm"
+    r = subprocess.run([exe, "-o", str(out), "-spp", "4", "-offsets", "shift", "-reconstruct", "l1", "-precision", "f64",
+                        os.path.join(ROOT, "scenes", "cbox_gdpt_64.gdpt.z")], capture_output=True, timeout=600)
+    assert r.returncode == 0, r.stderr.decode()
+    assert "L1 reconstruction: 10 reweightings" in r.stdout.decode()
+    want = g.gradient_path_render(scenes("cbox_gdpt_64"), spp=4, precision="f64", offsets="shift")
+    l1 = g.reconstruct_l1(want.primal, want.dx, want.dy, 0.04, irls_iterations=10, cg_iterations=100)
+    got = _read_pfm(str(out)[:-4] + "_l1.pfm")
+    assert np.allclose(got, l1.astype(np.float32), rtol=1e-5, atol=1e-7)
+    assert np.allclose(_read_pfm(str(out)), want.poisson.astype(np.float32), rtol=1e-6, atol=1e-9)
+
+
 def test_cpp_host_cli_path_integrator(g, scenes, tmp_path):
     """`-integrator path` (Integrator::Path, render.cpp:385-386): one image, equal to path_render of the Python host."""
     import os
