@@ -43,7 +43,29 @@ GD_D void path_finish(const WaveParams &wp, const PathState<R> &ps) {
     // float mode: a sample whose products left the float range (near-specular chains) is dropped instead of poisoning the
     // pixel; the double mode keeps whatever the reference's arithmetic gives
     if (sizeof(R) == 4 && !(isfinite(rd[0]) && isfinite(rd[1]) && isfinite(rd[2]))) return;
+    if (wp.res) {                                    // one 24-byte record per path (zeroed per wave); summed in sample order by k_path_reduce
+        double *o = wp.res + (size_t)ps.id * 3;
+        for (int c = 0; c < 3; c++) o[c] = rd[c] * inv_spp;
+        return;
+    }
     for (int c = 0; c < 3; c++) if (rd[c] != 0.0) atomicAdd(wp.img + p + c, rd[c] * inv_spp);
+}
+
+// path_render's accumulation (render.cpp:98-113: the samples of a pixel added one after the other) without atomics: thread
+// per pixel slot of the wave, the wave's samples added in sample order onto the running image value — bit-reproducible.
+static __global__ void __launch_bounds__(256) k_path_reduce(WaveParams wp, const double *res, double *img) {
+    const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (p >= wp.npix_pad) return;
+    const int tile = (int)(p >> 5), lane = (int)(p & 31);
+    const int x = (tile % wp.tiles_x) * 8 + (lane & 7), y = wave_row(wp, tile / wp.tiles_x, lane);
+    if (x >= wp.width || y >= wp.y1) return;
+    const size_t pix = ((size_t)y * wp.width + x) * 3;
+    double a0 = img[pix], a1 = img[pix + 1], a2 = img[pix + 2];
+    for (int s = 0; s < wp.n_samples; s++) {
+        const double *r = res + ((size_t)s * wp.npix_pad + p) * 3;
+        a0 += r[0]; a1 += r[1]; a2 += r[2];
+    }
+    img[pix] = a0; img[pix + 1] = a1; img[pix + 2] = a2;
 }
 
 // power heuristic p_a^2 / (p_a^2 + p_b^2) (p_a > 0).  double: the reference's expression, literally; float: the same

@@ -47,6 +47,12 @@ int run_path_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     cudaEvent_t e0 = c->ev[4], e1 = c->ev[5], e2 = c->ev[6];
     float ms;
 
+    wp.res = nullptr;
+    if (c->deterministic && !wp.rec_out && !wp.xs) {      // image renders: per-path result records + ordered reduction (no atomics)
+        if (int r = c->res0.ensure((size_t)N * 3 * sizeof(double))) return r;
+        wp.res = c->res0.as<double>();
+        GD_CUDA(cudaMemsetAsync(wp.res, 0, (size_t)N * 3 * sizeof(double), st));
+    }
     GD_CUDA(cudaMemsetAsync(cnt, 0, 64, st));
     k_path_generate<R><<<blocks_for(N, 128), 128, 0, st>>>(sc, wp, cur, rays);
     c->stats.kernel_launches++;
@@ -106,6 +112,7 @@ int run_path_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
         count = c->h_counts[0];
         std::swap(cur, nxt); std::swap(shadow, shadow_next); which ^= 1;
     }
+    if (wp.res) { k_path_reduce<<<blocks_for(wp.npix_pad, 256), 256, 0, st>>>(wp, wp.res, wp.img); c->stats.kernel_launches++; }
     GD_CUDA(cudaGetLastError());
     return 0;
 }

@@ -61,6 +61,15 @@ GD_D void finish_shift(const WaveParams &wp, int px, int py, int id, const V3<R>
     const size_t p = ((size_t)py * wp.width + px) * 3, row = (size_t)wp.width * 3;
     const double spp = (double)wp.spp_total, inv_spp = 1.0 / spp;
     const double rd[3] = {(double)rad.x, (double)rad.y, (double)rad.z};
+    if (wp.res) {            // one 120-byte record per path (zeroed per wave): r, vx0, vy0, vx1, vy1; the border rule is k_shift_reduce's
+        double *o = wp.res + (size_t)id * 15;
+        for (int c = 0; c < 3; c++) {
+            o[c] = rd[c] * inv_spp;
+            o[3 + c] = (contrib[c] - cS[0][c]) * (wS[0] / (prob * spp)); o[6 + c] = (contrib[c] - cS[1][c]) * (wS[1] / (prob * spp));
+            o[9 + c] = (cS[2][c] - contrib[c]) * (wS[2] / (prob * spp)); o[12 + c] = (cS[3][c] - contrib[c]) * (wS[3] / (prob * spp));
+        }
+        return;
+    }
     for (int c = 0; c < 3; c++) {
         if (rd[c] != 0.0) atomicAdd(wp.img + p + c, rd[c] * inv_spp);
         const double vx0 = (contrib[c] - cS[0][c]) * (wS[0] / (prob * spp)), vy0 = (contrib[c] - cS[1][c]) * (wS[1] / (prob * spp));
@@ -70,6 +79,39 @@ GD_D void finish_shift(const WaveParams &wp, int px, int py, int id, const V3<R>
         if (px < wp.width - 1 && vx1 != 0.0) { atomicAdd(wp.cx1 + p + c, vx1); if (px == 0) atomicAdd(wp.cx0 + p + c, -vx1); }
         if (py < wp.height - 1 && vy1 != 0.0) { atomicAdd(wp.cy1 + p + c, vy1); if (py == 0) atomicAdd(wp.cy0 + p + c, -vy1); }
     }
+}
+
+// finish_shift's accumulation without atomics: thread per pixel slot of the wave, the wave's samples in sample order.  A pixel of
+// column 0 / row 0 also takes, sample by sample after its own terms, minus the X0 / Y0 estimate of its neighbour in column 1 /
+// row 1 (the border rule above): that neighbour lies in the same 8x4 tile, one lane / one tile row further.
+static __global__ void __launch_bounds__(256) k_shift_reduce(WaveParams wp, const double *res, double *img, double *cx0, double *cy0, double *cx1, double *cy1) {
+    const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (p >= wp.npix_pad) return;
+    const int tile = (int)(p >> 5), lane = (int)(p & 31);
+    const int x = (tile % wp.tiles_x) * 8 + (lane & 7), y = wave_row(wp, tile / wp.tiles_x, lane);
+    if (x >= wp.width || y >= wp.y1) return;
+    const size_t pix = ((size_t)y * wp.width + x) * 3;
+    const bool has_l = x > 0, has_u = y > 0, has_r = x < wp.width - 1, has_d = y < wp.height - 1;
+    const bool nb_x = x == 0 && wp.width > 1, nb_y = y == 0 && wp.height > 1 && wp.y1 > 1;      // the neighbour's record exists in this wave
+    double a[15];
+    double *bufs[5] = {img, cx0, cy0, cx1, cy1};
+#pragma unroll
+    for (int k = 0; k < 15; k++) a[k] = bufs[k / 3][pix + k % 3];
+    for (int s = 0; s < wp.n_samples; s++) {
+        const double *r = res + ((size_t)s * wp.npix_pad + p) * 15;
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            a[c] += r[c];
+            if (has_l) a[3 + c] += r[3 + c];
+            if (has_u) a[6 + c] += r[6 + c];
+            if (has_r) { a[9 + c] += r[9 + c]; if (x == 0) a[3 + c] += -r[9 + c]; }
+            if (has_d) { a[12 + c] += r[12 + c]; if (y == 0) a[6 + c] += -r[12 + c]; }
+            if (nb_x) a[3 + c] += -r[15 + 3 + c];               // pixel (1, y): next lane of the tile
+            if (nb_y) a[6 + c] += -r[15 * 8 + 6 + c];           // pixel (x, 1): next row of the tile
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 15; k++) bufs[k / 3][pix + k % 3] = a[k];
 }
 
 template <typename R, int MS, bool EXACT>
@@ -438,6 +480,12 @@ int run_shift_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     cudaStream_t st = c->stream;
     cudaEvent_t e0 = c->ev[4], e1 = c->ev[5];
     GD_CUDA(cudaMemsetAsync(cnt, 0, 2 * sizeof(unsigned long long), st));      // rays traced; next sample (k_shift_sm)
+    wp.res = nullptr;
+    if (c->deterministic && !wp.rec_out && !wp.xs) {      // image renders: per-path result records + ordered reduction (no atomics)
+        if (int r = c->res0.ensure((size_t)N * 15 * sizeof(double))) return r;
+        wp.res = c->res0.as<double>();
+        GD_CUDA(cudaMemsetAsync(wp.res, 0, (size_t)N * 15 * sizeof(double), st));
+    }
     GD_CUDA(cudaEventRecord(e0, st));
     // default: the state machine at 8 blocks per SM (64 registers; B200, Sponza 1080p, 8 spp: 87 ms — 5 blocks 100 ms, 3 blocks
     // 117 ms; k_shift 116 ms, 103 ms at 8 blocks per SM).  GDPT_SHIFT_KERNEL=0 runs k_shift (A/B, bit-identity test).
@@ -445,6 +493,7 @@ int run_shift_wave_ms(gdpt_ctx *c, DScene<R> sc, WaveParams wp) {
     const int nb = blocks_for(N, TRACE_BLOCK);
     if (straight) k_shift<R, MS, ModeSel<R>::exact><<<nb, TRACE_BLOCK, 0, st>>>(sc, wp, c->bvh, cnt);
     else k_shift_sm<R, MS, ModeSel<R>::exact, 8><<<std::min(nb, SM_COUNT * 8), TRACE_BLOCK, 0, st>>>(sc, wp, c->bvh, cnt, reinterpret_cast<int *>(cnt + 1));
+    if (wp.res) { k_shift_reduce<<<blocks_for(wp.npix_pad, 256), 256, 0, st>>>(wp, wp.res, wp.img, wp.cx0, wp.cy0, wp.cx1, wp.cy1); c->stats.kernel_launches++; }
     GD_CUDA(cudaEventRecord(e1, st));
     unsigned long long h = 0;
     GD_CUDA(cudaMemcpyAsync(&h, cnt, sizeof(h), cudaMemcpyDeviceToHost, st));

@@ -241,3 +241,24 @@ def test_images_are_bit_reproducible(g):
             assert np.array_equal(getattr(imgs["a"], f), getattr(imgs[tag], f)), (tag, f)
     for f in ("primal", "dx", "dy"):
         assert np.allclose(getattr(imgs["a"], f), getattr(imgs["atomics"], f), rtol=1e-9, atol=1e-12), f
+
+
+def test_path_and_shift_mode_images_are_bit_reproducible_and_equal_the_atomic_accumulation(g):
+    """The `path` integrator and the shift-mapped gradpath mode accumulate through per-path result records and an ordered
+    reduction (as the reference mode does): two renders give the same bits, several waves included, and the images equal the
+    atomicAdd accumulation (`deterministic` = 0) up to its summation order.  Row bands compose (border rule of the shift mode
+    at row 0 / column 0 included)."""
+    sc = g.Scene.named("cbox_gdpt_64")
+    for kw in (dict(spp=6, precision="f32", seed=5), dict(spp=5, precision="f64", seed=2, wave_samples=2)):
+        a = g.path_render(sc, **kw); b = g.path_render(sc, **kw)
+        assert np.array_equal(a, b)
+        s1 = g.gradient_path_render(sc, offsets="shift", **kw); s2 = g.gradient_path_render(sc, offsets="shift", **kw)
+        for n in ("primal", "dx", "dy", "poisson"):
+            assert np.array_equal(s1[n], s2[n]), n
+        sc.set_option("deterministic", 0)
+        pa = g.path_render(sc, **kw); sa = g.gradient_path_render(sc, offsets="shift", **kw)
+        sc.set_option("deterministic", 1)
+        assert np.allclose(a, pa, rtol=1e-12, atol=1e-15)
+        for n in ("primal", "dx", "dy"):
+            assert np.allclose(s1[n], sa[n], rtol=1e-11, atol=1e-14), n
+    sc.close()
