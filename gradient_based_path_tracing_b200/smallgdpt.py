@@ -23,10 +23,12 @@ def render(width=1024, height=768, spp=100, rng="rows", device=0):
         raise ValueError("rng must be 'rows' or 'pixels'")
     L = _capi.lib()
     w, h = int(width), int(height)
-    shape = (max(h, 0), max(w, 0), 3)
-    imgs = [_capi.pinned_empty(shape) for _ in range(4)] if 0 < w <= 16384 and 0 < h <= 16384 else [np.empty((1, 1, 3)) for _ in range(4)]
-    out = _capi.GdptImages(*[a.ctypes.data_as(_capi.dp) for a in imgs])
     ms = C.c_double(0.0)
+    if not (2 <= w <= 16384 and 2 <= h <= 16384):        # no images to allocate: let the library state its limits
+        _capi.check(L.gdpt_smallgdpt_render(int(device), w, h, int(spp), _MODES[rng], None, C.byref(ms)))
+        raise ValueError("film size out of range")
+    imgs = [_capi.pinned_empty((h, w, 3)) for _ in range(4)]
+    out = _capi.GdptImages(*[a.ctypes.data_as(_capi.dp) for a in imgs])
     _capi.check(L.gdpt_smallgdpt_render(int(device), w, h, int(spp), _MODES[rng], C.byref(out), C.byref(ms)))
     return {"primal": imgs[0], "dx": imgs[1], "dy": imgs[2], "poisson": imgs[3], "render_ms": ms.value}
 
