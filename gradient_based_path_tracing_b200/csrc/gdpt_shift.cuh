@@ -275,7 +275,7 @@ GD_D Hit shift_trace(const DBvh &bvh, const float o[3], const float d[3], float 
     TraceStack st; st.smem = smem_stack;
     int sp = 0, cur = 0;
     while (cur != TRACE_DONE) {
-        while (cur >= 0) cur = trace_node<0, 0, false, 0, false, true>(bvh, cur, r, st, sp);
+        while (cur >= 0) cur = trace_node<0, 0, false, 0, false, 1>(bvh, cur, r, st, sp);
         if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, nullptr);
         if (any && r.hit.shape_id >= 0) break;
     }

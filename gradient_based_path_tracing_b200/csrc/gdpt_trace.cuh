@@ -150,8 +150,18 @@ GD_D void ld256(const float4 *p, float4 &a, float4 &b) {
     asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
 }
-// WIDE: the node's six planes are fetched with three 256-bit loads instead of six 128-bit ones.
-template <int SORT = 0, int FMA = 0, bool NOPOP = false, int EAGER = 0, bool EXACT_E = false, bool WIDE = false, typename ST, typename RS>
+// the same with the L1 eviction priority "evict last": node lines are the re-used data of the walk, rays / hits / primitives are not
+GD_D void ld256_keep(const float4 *p, float4 &a, float4 &b) {
+    asm volatile("ld.global.nc.L1::evict_last.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
+GD_D int4 ld128_keep(const int4 *p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::evict_last.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// WIDE: the node's six planes are fetched with three 256-bit loads instead of six 128-bit ones; WIDE = 2: with evict-last priority.
+template <int SORT = 0, int FMA = 0, bool NOPOP = false, int EAGER = 0, bool EXACT_E = false, int WIDE = 0, typename ST, typename RS>
 GD_D int trace_node(const DBvh &bvh, int cur, RS &r, ST &st, int &sp, unsigned *n_prims = nullptr) {
     const float4 *n = bvh.nodes + 8 * (size_t)cur;
     const float INF = __int_as_float(0x7f800000);
@@ -174,9 +184,10 @@ GD_D int trace_node(const DBvh &bvh, int cur, RS &r, ST &st, int &sp, unsigned *
         }
     } else {
     float4 lox, loy, loz, hix, hiy, hiz;
-    if (WIDE) { ld256(n, lox, loy); ld256(n + 2, loz, hix); ld256(n + 4, hiy, hiz); }
+    if (WIDE == 2) { ld256_keep(n, lox, loy); ld256_keep(n + 2, loz, hix); ld256_keep(n + 4, hiy, hiz); }
+    else if (WIDE) { ld256(n, lox, loy); ld256(n + 2, loz, hix); ld256(n + 4, hiy, hiz); }
     else { lox = __ldg(n); loy = __ldg(n + 1); loz = __ldg(n + 2); hix = __ldg(n + 3); hiy = __ldg(n + 4); hiz = __ldg(n + 5); }
-    int4 ch = __ldg((const int4 *)(n + 6));
+    int4 ch = WIDE == 2 ? ld128_keep((const int4 *)(n + 6)) : __ldg((const int4 *)(n + 6));
     cid[0] = ch.x; cid[1] = ch.y; cid[2] = ch.z; cid[3] = ch.w;
     const float lx[4] = {lox.x, lox.y, lox.z, lox.w}, ly[4] = {loy.x, loy.y, loy.z, loy.w}, lz[4] = {loz.x, loz.y, loz.z, loz.w};
     const float hx[4] = {hix.x, hix.y, hix.z, hix.w}, hy[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, hz[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
@@ -248,7 +259,7 @@ GD_D Hit trace_closest(const DBvh &bvh, const float o[3], const float d[3], floa
     TraceStack st; st.smem = smem_stack;
     int sp = 0, cur = 0;
     while (cur != TRACE_DONE) {
-        while (cur >= 0) { if (COUNT) (*n_nodes)++; cur = trace_node<0, 0, false, 0, false, true>(bvh, cur, r, st, sp); }
+        while (cur >= 0) { if (COUNT) (*n_nodes)++; cur = trace_node<0, 0, false, 0, false, 1>(bvh, cur, r, st, sp); }
         if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, COUNT ? n_prims : nullptr);
     }
     return r.hit;
@@ -262,7 +273,7 @@ GD_D bool trace_occluded(const DBvh &bvh, const float o[3], const float d[3], fl
     TraceStack st; st.smem = smem_stack;
     int sp = 0, cur = 0;
     while (cur != TRACE_DONE) {
-        while (cur >= 0) cur = trace_node<0, 0, false, 0, false, true>(bvh, cur, r, st, sp);
+        while (cur >= 0) cur = trace_node<0, 0, false, 0, false, 1>(bvh, cur, r, st, sp);
         if (cur != TRACE_DONE) cur = trace_leaf<EXACT>(bvh, cur, r, st, sp, nullptr);
         if (r.hit.shape_id >= 0) return true;
     }

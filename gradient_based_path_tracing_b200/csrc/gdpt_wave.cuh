@@ -14,7 +14,7 @@ template <typename R> struct ModeSel;
 template <> struct ModeSel<double> { static constexpr bool exact = true; };
 template <> struct ModeSel<float> { static constexpr bool exact = false; };
 
-constexpr int TRACE_DEFAULT_VARIANT = 360000;   // one pop site per trip (3.5 % over the two-site loop) + 256-bit node loads (2 %): profiles/r2_wave_scheduling.txt
+constexpr int TRACE_DEFAULT_VARIANT = 360200;   // one pop site per trip (3.5 %) + 256-bit node loads (2 %) + 12 instead of 20 stack entries in shared memory, i.e. more L1 (1.6 %): profiles/r2_wave_scheduling.txt
 constexpr int SORT_MIN_RAYS = 1 << 17;   // below this a launch is too small for the sort to pay
 
 // count_ptr != nullptr: n is only an upper bound, the live count is read on the device (and added to the device-side ray total)
@@ -33,7 +33,7 @@ inline void launch_trace(gdpt_ctx *c, const RayF *rays, HitRec *hits, int n, con
     else if constexpr (EXACT) launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, st, rays, hits, n, order, count_ptr);
     else switch (c->trace_variant) {
 #define GD_V(v) case v: launch_trace_v<EXACT, false, v>(c, st, rays, hits, n, order, count_ptr); break;
-        GD_V(0) GD_V(40000) GD_V(120000) GD_V(200000) GD_V(360000)
+        GD_V(0) GD_V(40000) GD_V(120000) GD_V(200000) GD_V(360000) GD_V(360200) GD_V(360300) GD_V(1000200)
 #undef GD_V
         default: launch_trace_v<EXACT, false, TRACE_DEFAULT_VARIANT>(c, st, rays, hits, n, order, count_ptr);
     }

@@ -258,7 +258,8 @@ __global__ void __launch_bounds__(128) k_generate(DScene<R> sc, WaveParams wp, G
 //        bit 2: one pop site per trip (node misses and finished leaves pop together at the top of the next trip);
 //        bit 3 (with bit 2): leaf children are tested inside their parent's node step (no leaf trips);
 //        bit 4: streaming (evict-first) loads of rays / permutation and stores of hits;
-//        bit 5 (with bit 2): the node planes are fetched with three 256-bit loads (LDG.E.ENL2.256) instead of six 128-bit ones
+//        bit 5 (with bit 2): the node planes are fetched with three 256-bit loads (LDG.E.ENL2.256) instead of six 128-bit ones;
+//        bit 6 (with bits 2, 5): node loads carry the L1 eviction priority evict-last
 // COUNT=true additionally sums visited nodes / tested primitives into counters[0..1]
 // (bench.py derives the algorithmic bytes per ray from them; never in timed runs).
 constexpr int trace_variant_depth(int v) { return ((v / 100) % 10) == 0 ? 20 : ((v / 100) % 10) == 1 ? 16 : ((v / 100) % 10) == 2 ? 12 : 8; }
@@ -290,7 +291,7 @@ __global__ void __launch_bounds__(TRACE_BLOCK, trace_variant_blocks(V)) k_trace(
                     if (cur == TRACE_POP) { cur = trace_pop(st, sp, r.best); if (cur == TRACE_DONE) break; }
                     if (cur >= 0) {
                         if (COUNT) cn++;
-                        cur = trace_node<SORT, FMA, true, (LOOP & 8) ? 1 : 0, EXACT, (LOOP & 32) != 0>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
+                        cur = trace_node<SORT, FMA, true, (LOOP & 8) ? 1 : 0, EXACT, (LOOP & 64) ? 2 : (LOOP & 32) ? 1 : 0>(bvh, cur, r, st, sp, COUNT ? &cp : nullptr);
                         if ((LOOP & 8) && ANY && r.hit.shape_id >= 0) break;
                     } else {
                         int enc = ~cur, first = enc >> 3, cnt = enc & 7;
