@@ -60,6 +60,7 @@ template <typename R> struct DScene {
     const int *indices;           // [T][3] mesh-local vertex indices
     const R *normals;             // [Vn][3]
     const R *uvs;                 // [Vu][2]
+    const float4 *tri_recs;       // f32 mode only (else null): [T][6] = p0 p1 p2 n0 n1 n2 (3 floats each) uv0 uv1 uv2 — one 96-byte line per triangle
     const DMaterial *materials;
     const DTexture<R> *textures;
     const DImage *img3, *img1;
@@ -195,6 +196,34 @@ GD_D double sphere_hit_d(const double *sph, const float *o, const float *d, floa
     return -1.0;
 }
 
+// 256-bit global load (sm_100: LDG.E.ENL2.256)
+GD_D void scene_ld256(const float4 *p, float4 &a, float4 &b) {
+    unsigned long long x0, x1, x2, x3;           // (64-bit operands: the eight-float form of this asm crashes cicc 12.9 inside make_vertex_impl)
+    asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(x0), "=l"(x1), "=l"(x2), "=l"(x3) : "l"(p));
+    a.x = __uint_as_float((unsigned)x0); a.y = __uint_as_float((unsigned)(x0 >> 32)); a.z = __uint_as_float((unsigned)x1); a.w = __uint_as_float((unsigned)(x1 >> 32));
+    b.x = __uint_as_float((unsigned)x2); b.y = __uint_as_float((unsigned)(x2 >> 32)); b.z = __uint_as_float((unsigned)x3); b.w = __uint_as_float((unsigned)(x3 >> 32));
+}
+// One thread per triangle: the vertex data a hit needs, gathered once at scene creation into one 96-byte record, so that
+// make_vertex fetches it with three 256-bit loads instead of 3 index loads followed by 24 scalar gathers (two dependent
+// levels of long-scoreboard stalls in k_primary / k_bounce / k_tail).  Same float values as the vertex pools: same results.
+static __global__ void k_build_tri_recs(int n_shapes, const DShape *shapes, const int *indices, const float *positions, const float *normals, const float *uvs,
+                                        long long n_tris, float *out) {
+    const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (t >= n_tris) return;
+    int s = -1;                                                // the mesh that owns triangle t (a warp's triangles share it: uniform loop)
+    for (int i = 0; i < n_shapes; i++) { const DShape sh = shapes[i]; if (sh.kind == SHAPE_MESH && t >= sh.tri_off && t < (long long)sh.tri_off + sh.n_tris) { s = i; break; } }
+    float *o = out + 24 * t;
+    if (s < 0) { for (int k = 0; k < 24; k++) o[k] = 0.f; return; }
+    const DShape sh = shapes[s];
+    const int *ix = indices + 3 * t;
+    const float *P = positions + 3 * (size_t)sh.vtx_off;
+    for (int v = 0; v < 3; v++) for (int k = 0; k < 3; k++) o[3 * v + k] = P[3 * ix[v] + k];
+    if (sh.flags & 1) { const float *N = normals + 3 * (size_t)sh.nrm_off; for (int v = 0; v < 3; v++) for (int k = 0; k < 3; k++) o[9 + 3 * v + k] = N[3 * ix[v] + k]; }
+    else for (int k = 0; k < 9; k++) o[9 + k] = 0.f;
+    if (sh.flags & 2) { const float *U = uvs + 2 * (size_t)sh.uv_off; for (int v = 0; v < 3; v++) for (int k = 0; k < 2; k++) o[18 + 2 * v + k] = U[2 * ix[v] + k]; }
+    else for (int k = 0; k < 6; k++) o[18 + k] = 0.f;
+}
+
 // ---------------------------------------------------------------- vertex construction
 // org/dir: the ray in working precision (what lajolla holds in double); tnear/tfar_in: the
 // values that were handed to the traversal (needed to re-derive the double sphere root).
@@ -206,10 +235,23 @@ GD_D void make_vertex_impl(const DScene<R> &sc, const V3<R> &org, const V3<R> &d
     v.position = org + dir * R(hit.t);
     R inv_uv_size;
     if (sh.kind == SHAPE_MESH) {
-        const int *ix = sc.indices + 3 * (size_t)(sh.tri_off + hit.prim_id);
-        int i0 = ix[0], i1 = ix[1], i2 = ix[2];
-        const R *P = sc.positions + 3 * (size_t)sh.vtx_off;
-        V3<R> p0(P[3 * i0], P[3 * i0 + 1], P[3 * i0 + 2]), p1(P[3 * i1], P[3 * i1 + 1], P[3 * i1 + 2]), p2(P[3 * i2], P[3 * i2 + 1], P[3 * i2 + 2]);
+        int i0 = 0, i1 = 0, i2 = 0;
+        V3<R> p0, p1, p2, n0, n1, n2;
+        V2<R> uv0, uv1, uv2;
+        const bool packed = sizeof(R) == 4 && sc.tri_recs != nullptr;
+        if (packed) {
+            const float4 *tr = sc.tri_recs + 6 * (size_t)(sh.tri_off + hit.prim_id);
+            float4 q0, q1, q2, q3, q4, q5;
+            scene_ld256(tr, q0, q1); scene_ld256(tr + 2, q2, q3); scene_ld256(tr + 4, q4, q5);
+            p0 = V3<R>(q0.x, q0.y, q0.z); p1 = V3<R>(q0.w, q1.x, q1.y); p2 = V3<R>(q1.z, q1.w, q2.x);
+            n0 = V3<R>(q2.y, q2.z, q2.w); n1 = V3<R>(q3.x, q3.y, q3.z); n2 = V3<R>(q3.w, q4.x, q4.y);
+            uv0 = V2<R>(q4.z, q4.w); uv1 = V2<R>(q5.x, q5.y); uv2 = V2<R>(q5.z, q5.w);
+        } else {
+            const int *ix = sc.indices + 3 * (size_t)(sh.tri_off + hit.prim_id);
+            i0 = ix[0]; i1 = ix[1]; i2 = ix[2];
+            const R *P = sc.positions + 3 * (size_t)sh.vtx_off;
+            p0 = V3<R>(P[3 * i0], P[3 * i0 + 1], P[3 * i0 + 2]); p1 = V3<R>(P[3 * i1], P[3 * i1 + 1], P[3 * i1 + 2]); p2 = V3<R>(P[3 * i2], P[3 * i2 + 1], P[3 * i2 + 2]);
+        }
         // Embree's Ng: float vertices, result rounded to float (intersection.cpp:41)
         {
             V3<double> a((double)(float)p0.x, (double)(float)p0.y, (double)(float)p0.z);
@@ -219,10 +261,11 @@ GD_D void make_vertex_impl(const DScene<R> &sc, const V3<R> &org, const V3<R> &d
             v.gn = normalize(V3<R>((R)(float)ng.x, (R)(float)ng.y, (R)(float)ng.z));
         }
         v.st = V2<R>((R)hit.u, (R)hit.v);
-        V2<R> uv0, uv1, uv2;
         if (sh.flags & 2) {
-            const R *U = sc.uvs + 2 * (size_t)sh.uv_off;
-            uv0 = V2<R>(U[2 * i0], U[2 * i0 + 1]); uv1 = V2<R>(U[2 * i1], U[2 * i1 + 1]); uv2 = V2<R>(U[2 * i2], U[2 * i2 + 1]);
+            if (!packed) {
+                const R *U = sc.uvs + 2 * (size_t)sh.uv_off;
+                uv0 = V2<R>(U[2 * i0], U[2 * i0 + 1]); uv1 = V2<R>(U[2 * i1], U[2 * i1 + 1]); uv2 = V2<R>(U[2 * i2], U[2 * i2 + 1]);
+            }
         } else { uv0 = V2<R>(0, 0); uv1 = V2<R>(1, 0); uv2 = V2<R>(1, 1); }
         R b0 = R(1) - v.st.x - v.st.y;
         v.uv = V2<R>(b0 * uv0.x + v.st.x * uv1.x + v.st.y * uv2.x, b0 * uv0.y + v.st.x * uv1.y + v.st.y * uv2.y);
@@ -240,8 +283,10 @@ GD_D void make_vertex_impl(const DScene<R> &sc, const V3<R> &org, const V3<R> &d
         V3<R> sn = v.gn; R mc = R(0);
         V3<R> tangent, bitangent;
         if (sh.flags & 1) {
-            const R *N = sc.normals + 3 * (size_t)sh.nrm_off;
-            V3<R> n0(N[3 * i0], N[3 * i0 + 1], N[3 * i0 + 2]), n1(N[3 * i1], N[3 * i1 + 1], N[3 * i1 + 2]), n2(N[3 * i2], N[3 * i2 + 1], N[3 * i2 + 2]);
+            if (!packed) {
+                const R *N = sc.normals + 3 * (size_t)sh.nrm_off;
+                n0 = V3<R>(N[3 * i0], N[3 * i0 + 1], N[3 * i0 + 2]); n1 = V3<R>(N[3 * i1], N[3 * i1 + 1], N[3 * i1 + 2]); n2 = V3<R>(N[3 * i2], N[3 * i2 + 1], N[3 * i2 + 2]);
+            }
             sn = normalize(b0 * n0 + v.st.x * n1 + v.st.y * n2);
             tangent = normalize(dpdu - sn * dot(sn, dpdu));
             V3<R> dnds = n2 - n0, dndt = n2 - n1;

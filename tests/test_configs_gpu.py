@@ -262,3 +262,22 @@ def test_path_and_shift_mode_images_are_bit_reproducible_and_equal_the_atomic_ac
         for n in ("primal", "dx", "dy"):
             assert np.allclose(s1[n], sa[n], rtol=1e-11, atol=1e-14), n
     sc.close()
+
+
+def test_packed_triangle_records_give_the_same_bits_as_the_vertex_pools(g):
+    """f32 mode: a hit triangle's vertex data comes from one packed 96-byte record (three 256-bit loads) instead of the index and
+    vertex pools — the same float values, so the images are the same bits (textured mesh with normals and uvs, and the Cornell box)."""
+    for name in ("sponza_small", "cbox_gdpt_64", "veach_mi_small"):
+        sc = g.Scene.named(name)
+        a = g.gradient_path_render(sc, spp=4, precision="f32", seed=9)
+        sc.set_option("tri_records", 0)
+        b = g.gradient_path_render(sc, spp=4, precision="f32", seed=9)
+        sc.set_option("tri_records", 1)
+        p = g.path_render(sc, spp=2, precision="f32", seed=1) if name != "sponza_small" else None
+        sc.set_option("tri_records", 0)
+        q = g.path_render(sc, spp=2, precision="f32", seed=1) if name != "sponza_small" else None
+        sc.close()
+        for n in ("primal", "dx", "dy", "poisson"):
+            assert np.array_equal(a[n], b[n]), (name, n)
+        if p is not None:
+            assert np.array_equal(p, q), name

@@ -20,11 +20,9 @@ if "sched" in what:
         print("%-44s %7.1f ms  %7.1f Mpaths/s   mean %.6f  launches %d" % (tag, dt * 1e3, 5 * 1920 * 1080 * spp / dt / 1e6, r.primal.mean(), r.stats["kernel_launches"]), flush=True)
         sc.close()
     run("default", {})
-    vs = ((360000, "20-entry shared stack"), (1000200, "12 entries + evict-last node loads"))
     for rep in range(3):
-        run("default", {})
-        for v, tag in vs:
-            run("trace variant %d (%s)" % (v, tag), {"trace_variant": v})
+        run("default (packed triangle records)", {})
+        run("tri_records = 0 (index + vertex pools)", {"tri_records": 0})
 if "records" in what:
     for name in ["cbox_gdpt_64", "cbox_gdpt_d2", "veach_mi_small", "sponza_small", "disney_small"]:
         z = np.load("tests/golden/records_%s.npz" % name)
