@@ -283,7 +283,8 @@ int gdpt_set_option(gdpt_ctx *ctx, const char *name, int value) {
     else if (n == "deterministic") ctx->deterministic = value != 0;
     else if (n == "shade_sorted") ctx->shade_sorted = value != 0;
     else if (n == "sort_rays") ctx->sort_rays = value != 0;
-    else if (n == "tri_records") { ctx->use_tri_recs = value != 0; ctx->sc_f.tri_recs = (ctx->use_tri_recs && ctx->tri_recs.p) ? ctx->tri_recs.as<float4>() : nullptr; }
+    else if (n == "tri_records") { ctx->use_tri_recs = value != 0; ctx->sc_f.tri_recs = (ctx->use_tri_recs && ctx->tri_recs.p) ? ctx->tri_recs.as<float>() : nullptr;
+                                    ctx->sc_d.tri_recs = (ctx->use_tri_recs && ctx->tri_recs_d.p) ? ctx->tri_recs_d.as<double>() : nullptr; }
     else if (n == "trace_variant") ctx->trace_variant = value;
     else if (n == "shade_variant") ctx->shade_variant = value;
     else return fail(GDPT_ERR_ARG, "unknown option '%s'", name);

@@ -117,7 +117,7 @@ struct gdpt_ctx {
     gdpt::DevBuf shapes, spheres, indices, materials, img3, img1;
     gdpt::DevBuf pos_d, nrm_d, uv_d, tex_d, texels3_d, texels1_d, light_d;   // exact mode
     gdpt::DevBuf pos_f, nrm_f, uv_f, tex_f, texels3_f, texels1_f, light_f;   // fast mode
-    gdpt::DevBuf tri_recs;                  // fast mode: packed per-triangle vertex records (k_build_tri_recs)
+    gdpt::DevBuf tri_recs, tri_recs_d;      // packed per-triangle vertex records (k_build_tri_recs), f32 and f64
     bool use_tri_recs = true;               // "tri_records" option
     gdpt::DevBuf lcdf_d, lcdf_f, lpmf_d, lpmf_f, tcdf_d, tcdf_f, area_d, area_f, lshape;   // light sampling tables (path integrator)
     bool has_envmap = false, envmap_ready = false;   // the scene has an environment map / its image and transforms were provided
@@ -505,13 +505,17 @@ inline int create_context(const gdpt_scene_desc *d, int device, int flags, gdpt_
     c->sc_d.positions = c->pos_d.as<double>(); c->sc_d.normals = c->nrm_d.as<double>(); c->sc_d.uvs = c->uv_d.as<double>();
     c->sc_f.positions = c->pos_f.as<float>(); c->sc_f.normals = c->nrm_f.as<float>(); c->sc_f.uvs = c->uv_f.as<float>();
     c->sc_d.tri_recs = nullptr; c->sc_f.tri_recs = nullptr;
-    if (d->n_triangles > 0) {           // the f32 mode reads a hit triangle's vertex data from one packed 96-byte record
+    if (d->n_triangles > 0) {           // a hit triangle's vertex data is read from one packed record (96 B in f32, 192 B in f64)
         if (int r = c->tri_recs.ensure((size_t)d->n_triangles * 24 * sizeof(float))) return r;
-        k_build_tri_recs<<<(unsigned)((d->n_triangles + 255) / 256), 256, 0, c->stream>>>(d->n_shapes, c->shapes.as<DShape>(), c->indices.as<int>(), c->pos_f.as<float>(),
-                                                                                         c->nrm_f.as<float>(), c->uv_f.as<float>(), (long long)d->n_triangles, c->tri_recs.as<float>());
+        if (int r = c->tri_recs_d.ensure((size_t)d->n_triangles * 24 * sizeof(double))) return r;
+        const unsigned nb = (unsigned)((d->n_triangles + 255) / 256);
+        k_build_tri_recs<float><<<nb, 256, 0, c->stream>>>(d->n_shapes, c->shapes.as<DShape>(), c->indices.as<int>(), c->pos_f.as<float>(), c->nrm_f.as<float>(),
+                                                          c->uv_f.as<float>(), (long long)d->n_triangles, c->tri_recs.as<float>());
+        k_build_tri_recs<double><<<nb, 256, 0, c->stream>>>(d->n_shapes, c->shapes.as<DShape>(), c->indices.as<int>(), c->pos_d.as<double>(), c->nrm_d.as<double>(),
+                                                           c->uv_d.as<double>(), (long long)d->n_triangles, c->tri_recs_d.as<double>());
         GD_CUDA(cudaGetLastError());
-        c->stats.kernel_launches++;
-        if (c->use_tri_recs) c->sc_f.tri_recs = c->tri_recs.as<float4>();
+        c->stats.kernel_launches += 2;
+        if (c->use_tri_recs) { c->sc_f.tri_recs = c->tri_recs.as<float>(); c->sc_d.tri_recs = c->tri_recs_d.as<double>(); }
     }
     c->sc_d.textures = c->tex_d.as<DTexture<double>>(); c->sc_f.textures = c->tex_f.as<DTexture<float>>();
     c->sc_d.texels3 = c->texels3_d.as<double>(); c->sc_d.texels1 = c->texels1_d.as<double>();
@@ -547,7 +551,7 @@ inline void destroy_context(gdpt_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     gdpt::DevBuf *all[] = {&c->shapes, &c->spheres, &c->indices, &c->materials, &c->img3, &c->img1, &c->pos_d, &c->nrm_d, &c->uv_d, &c->tex_d,
-                           &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tri_recs, &c->tex_f, &c->texels3_f, &c->texels1_f,
+                           &c->texels3_d, &c->texels1_d, &c->light_d, &c->pos_f, &c->nrm_f, &c->uv_f, &c->tri_recs, &c->tri_recs_d, &c->tex_f, &c->texels3_f, &c->texels1_f,
                            &c->light_f, &c->lcdf_d, &c->lcdf_f, &c->lpmf_d, &c->lpmf_f, &c->tcdf_d, &c->tcdf_f, &c->area_d, &c->area_f, &c->lshape, &c->ecr_d, &c->ecr_f, &c->epr_d, &c->epr_f, &c->ecm_d, &c->ecm_f, &c->epm_d, &c->epm_f, &c->shadow_rays, &c->shadow_hits, &c->prec_a, &c->prec_b, &c->bvh_nodes, &c->bvh_prims, &c->gen, &c->rays, &c->hits, &c->rec_a, &c->rec_b, &c->off, &c->counters,
                            &c->recout, &c->xs, &c->ys, &c->streams, &c->trav_counters, &c->sort_keys, &c->sort_order, &c->sort_hist, &c->dev_stats, &c->res0, &c->img, &c->cx0, &c->cy0, &c->cx1, &c->cy1, &c->cx, &c->cy, &c->out};
     for (auto *b : all) b->release();

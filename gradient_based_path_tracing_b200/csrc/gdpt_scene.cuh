@@ -60,7 +60,7 @@ template <typename R> struct DScene {
     const int *indices;           // [T][3] mesh-local vertex indices
     const R *normals;             // [Vn][3]
     const R *uvs;                 // [Vu][2]
-    const float4 *tri_recs;       // f32 mode only (else null): [T][6] = p0 p1 p2 n0 n1 n2 (3 floats each) uv0 uv1 uv2 — one 96-byte line per triangle
+    const R *tri_recs;            // (may be null) [T][24] = p0 p1 p2 n0 n1 n2 (3 each) uv0 uv1 uv2 (2 each): one 96-byte (f32) / 192-byte (f64) record per triangle
     const DMaterial *materials;
     const DTexture<R> *textures;
     const DImage *img3, *img1;
@@ -197,31 +197,51 @@ GD_D double sphere_hit_d(const double *sph, const float *o, const float *d, floa
 }
 
 // 256-bit global load (sm_100: LDG.E.ENL2.256)
-GD_D void scene_ld256(const float4 *p, float4 &a, float4 &b) {
-    unsigned long long x0, x1, x2, x3;           // (64-bit operands: the eight-float form of this asm crashes cicc 12.9 inside make_vertex_impl)
+// eight floats / four doubles of a 32-byte aligned address, into scalars (an array filled through a pointer stays in local memory)
+// (64-bit operands: the eight-float form of this asm crashes cicc 12.9 inside make_vertex_impl)
+GD_D void scene_ld256(const float *p, float4 &a, float4 &b) {
+    unsigned long long x0, x1, x2, x3;
     asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(x0), "=l"(x1), "=l"(x2), "=l"(x3) : "l"(p));
     a.x = __uint_as_float((unsigned)x0); a.y = __uint_as_float((unsigned)(x0 >> 32)); a.z = __uint_as_float((unsigned)x1); a.w = __uint_as_float((unsigned)(x1 >> 32));
     b.x = __uint_as_float((unsigned)x2); b.y = __uint_as_float((unsigned)(x2 >> 32)); b.z = __uint_as_float((unsigned)x3); b.w = __uint_as_float((unsigned)(x3 >> 32));
 }
+GD_D void scene_ld256(const double *p, double &a, double &b, double &c, double &d) {
+    unsigned long long x0, x1, x2, x3;
+    asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(x0), "=l"(x1), "=l"(x2), "=l"(x3) : "l"(p));
+    a = __longlong_as_double((long long)x0); b = __longlong_as_double((long long)x1); c = __longlong_as_double((long long)x2); d = __longlong_as_double((long long)x3);
+}
+// one triangle record -> its nine vectors
+GD_D void load_tri_rec(const float *r, V3<float> &p0, V3<float> &p1, V3<float> &p2, V3<float> &n0, V3<float> &n1, V3<float> &n2, V2<float> &uv0, V2<float> &uv1, V2<float> &uv2) {
+    float4 q0, q1, q2, q3, q4, q5;
+    scene_ld256(r, q0, q1); scene_ld256(r + 8, q2, q3); scene_ld256(r + 16, q4, q5);
+    p0 = V3<float>(q0.x, q0.y, q0.z); p1 = V3<float>(q0.w, q1.x, q1.y); p2 = V3<float>(q1.z, q1.w, q2.x);
+    n0 = V3<float>(q2.y, q2.z, q2.w); n1 = V3<float>(q3.x, q3.y, q3.z); n2 = V3<float>(q3.w, q4.x, q4.y);
+    uv0 = V2<float>(q4.z, q4.w); uv1 = V2<float>(q5.x, q5.y); uv2 = V2<float>(q5.z, q5.w);
+}
+GD_D void load_tri_rec(const double *r, V3<double> &p0, V3<double> &p1, V3<double> &p2, V3<double> &n0, V3<double> &n1, V3<double> &n2, V2<double> &uv0, V2<double> &uv1, V2<double> &uv2) {
+    scene_ld256(r, p0.x, p0.y, p0.z, p1.x); scene_ld256(r + 4, p1.y, p1.z, p2.x, p2.y); scene_ld256(r + 8, p2.z, n0.x, n0.y, n0.z);
+    scene_ld256(r + 12, n1.x, n1.y, n1.z, n2.x); scene_ld256(r + 16, n2.y, n2.z, uv0.x, uv0.y); scene_ld256(r + 20, uv1.x, uv1.y, uv2.x, uv2.y);
+}
 // One thread per triangle: the vertex data a hit needs, gathered once at scene creation into one 96-byte record, so that
-// make_vertex fetches it with three 256-bit loads instead of 3 index loads followed by 24 scalar gathers (two dependent
+// make_vertex fetches it with three (f32) or six (f64) 256-bit loads instead of 3 index loads followed by 24 scalar gathers (two dependent
 // levels of long-scoreboard stalls in k_primary / k_bounce / k_tail).  Same float values as the vertex pools: same results.
-static __global__ void k_build_tri_recs(int n_shapes, const DShape *shapes, const int *indices, const float *positions, const float *normals, const float *uvs,
-                                        long long n_tris, float *out) {
+template <typename T>
+static __global__ void k_build_tri_recs(int n_shapes, const DShape *shapes, const int *indices, const T *positions, const T *normals, const T *uvs,
+                                        long long n_tris, T *out) {
     const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (t >= n_tris) return;
     int s = -1;                                                // the mesh that owns triangle t (a warp's triangles share it: uniform loop)
     for (int i = 0; i < n_shapes; i++) { const DShape sh = shapes[i]; if (sh.kind == SHAPE_MESH && t >= sh.tri_off && t < (long long)sh.tri_off + sh.n_tris) { s = i; break; } }
-    float *o = out + 24 * t;
-    if (s < 0) { for (int k = 0; k < 24; k++) o[k] = 0.f; return; }
+    T *o = out + 24 * t;
+    if (s < 0) { for (int k = 0; k < 24; k++) o[k] = T(0); return; }
     const DShape sh = shapes[s];
     const int *ix = indices + 3 * t;
-    const float *P = positions + 3 * (size_t)sh.vtx_off;
+    const T *P = positions + 3 * (size_t)sh.vtx_off;
     for (int v = 0; v < 3; v++) for (int k = 0; k < 3; k++) o[3 * v + k] = P[3 * ix[v] + k];
-    if (sh.flags & 1) { const float *N = normals + 3 * (size_t)sh.nrm_off; for (int v = 0; v < 3; v++) for (int k = 0; k < 3; k++) o[9 + 3 * v + k] = N[3 * ix[v] + k]; }
-    else for (int k = 0; k < 9; k++) o[9 + k] = 0.f;
-    if (sh.flags & 2) { const float *U = uvs + 2 * (size_t)sh.uv_off; for (int v = 0; v < 3; v++) for (int k = 0; k < 2; k++) o[18 + 2 * v + k] = U[2 * ix[v] + k]; }
-    else for (int k = 0; k < 6; k++) o[18 + k] = 0.f;
+    if (sh.flags & 1) { const T *N = normals + 3 * (size_t)sh.nrm_off; for (int v = 0; v < 3; v++) for (int k = 0; k < 3; k++) o[9 + 3 * v + k] = N[3 * ix[v] + k]; }
+    else for (int k = 0; k < 9; k++) o[9 + k] = T(0);
+    if (sh.flags & 2) { const T *U = uvs + 2 * (size_t)sh.uv_off; for (int v = 0; v < 3; v++) for (int k = 0; k < 2; k++) o[18 + 2 * v + k] = U[2 * ix[v] + k]; }
+    else for (int k = 0; k < 6; k++) o[18 + k] = T(0);
 }
 
 // ---------------------------------------------------------------- vertex construction
@@ -238,14 +258,9 @@ GD_D void make_vertex_impl(const DScene<R> &sc, const V3<R> &org, const V3<R> &d
         int i0 = 0, i1 = 0, i2 = 0;
         V3<R> p0, p1, p2, n0, n1, n2;
         V2<R> uv0, uv1, uv2;
-        const bool packed = sizeof(R) == 4 && sc.tri_recs != nullptr;
+        const bool packed = sc.tri_recs != nullptr;
         if (packed) {
-            const float4 *tr = sc.tri_recs + 6 * (size_t)(sh.tri_off + hit.prim_id);
-            float4 q0, q1, q2, q3, q4, q5;
-            scene_ld256(tr, q0, q1); scene_ld256(tr + 2, q2, q3); scene_ld256(tr + 4, q4, q5);
-            p0 = V3<R>(q0.x, q0.y, q0.z); p1 = V3<R>(q0.w, q1.x, q1.y); p2 = V3<R>(q1.z, q1.w, q2.x);
-            n0 = V3<R>(q2.y, q2.z, q2.w); n1 = V3<R>(q3.x, q3.y, q3.z); n2 = V3<R>(q3.w, q4.x, q4.y);
-            uv0 = V2<R>(q4.z, q4.w); uv1 = V2<R>(q5.x, q5.y); uv2 = V2<R>(q5.z, q5.w);
+            load_tri_rec(sc.tri_recs + 24 * (size_t)(sh.tri_off + hit.prim_id), p0, p1, p2, n0, n1, n2, uv0, uv1, uv2);
         } else {
             const int *ix = sc.indices + 3 * (size_t)(sh.tri_off + hit.prim_id);
             i0 = ix[0]; i1 = ix[1]; i2 = ix[2];

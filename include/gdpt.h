@@ -250,7 +250,7 @@ int gdpt_get_stats(gdpt_ctx *ctx, gdpt_stats *out);
  * fields stay 0); "deterministic" 1|0: gradpath accumulates through per-path
  * result records that are added to the images in sample order (bit-reproducible images, the summation order of render.cpp:303-327;
  * default 1) or with atomicAdd(double) straight into the images; "poisson_fft" 1|0: the O(N log N) form of the DCT-I in fourierSolve's
- * replacement or the dense-matrix form (default 1; films under 16 pixels a side always take the matrix form); "tail_paths" n; "sort_rays" 1|0; "trace_variant" v; "shade_variant" v; "tri_records" 1|0: the f32 mode reads a hit triangle's vertex data from one packed 96-byte record built at creation (three 256-bit loads) or from the index / vertex pools (default 1; same values, same results). */
+ * replacement or the dense-matrix form (default 1; films under 16 pixels a side always take the matrix form); "tail_paths" n; "sort_rays" 1|0; "trace_variant" v; "shade_variant" v; "tri_records" 1|0: a hit triangle's vertex data is read from one packed record built at creation (96 bytes / three 256-bit loads in f32, 192 / six in f64) or from the index / vertex pools (default 1; same values, same results). */
 int gdpt_set_option(gdpt_ctx *ctx, const char *name, int value);
 /* Run all of the context's work on the caller's CUDA stream (a cudaStream_t; NULL restores the context's own). */
 int gdpt_set_stream(gdpt_ctx *ctx, void *cuda_stream);

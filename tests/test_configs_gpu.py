@@ -265,8 +265,9 @@ def test_path_and_shift_mode_images_are_bit_reproducible_and_equal_the_atomic_ac
 
 
 def test_packed_triangle_records_give_the_same_bits_as_the_vertex_pools(g):
-    """f32 mode: a hit triangle's vertex data comes from one packed 96-byte record (three 256-bit loads) instead of the index and
-    vertex pools — the same float values, so the images are the same bits (textured mesh with normals and uvs, and the Cornell box)."""
+    """A hit triangle's vertex data comes from one packed record (96 bytes / three 256-bit loads in f32, 192 / six in f64) instead
+    of the index and vertex pools — the same values, so the images are the same bits (textured mesh with normals and uvs, the
+    Cornell box, sphere lights + rough plastic)."""
     for name in ("sponza_small", "cbox_gdpt_64", "veach_mi_small"):
         sc = g.Scene.named(name)
         a = g.gradient_path_render(sc, spp=4, precision="f32", seed=9)
@@ -281,3 +282,11 @@ def test_packed_triangle_records_give_the_same_bits_as_the_vertex_pools(g):
             assert np.array_equal(a[n], b[n]), (name, n)
         if p is not None:
             assert np.array_equal(p, q), name
+    # the f64 mode has its own records (192 bytes, six loads)
+    sc = g.Scene.named("sponza_small")
+    a = g.gradient_path_render(sc, spp=2, precision="f64", seed=4)
+    sc.set_option("tri_records", 0)
+    b = g.gradient_path_render(sc, spp=2, precision="f64", seed=4)
+    sc.close()
+    for n in ("primal", "dx", "dy", "poisson"):
+        assert np.array_equal(a[n], b[n]), ("f64", n)

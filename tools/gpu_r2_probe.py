@@ -21,8 +21,8 @@ if "sched" in what:
         sc.close()
     run("default", {})
     for rep in range(3):
-        run("default (packed triangle records)", {})
-        run("tri_records = 0 (index + vertex pools)", {"tri_records": 0})
+        run("f64, default (packed triangle records)", {}, prec="f64")
+        run("f64, tri_records = 0 (index + vertex pools)", {"tri_records": 0}, prec="f64")
 if "records" in what:
     for name in ["cbox_gdpt_64", "cbox_gdpt_d2", "veach_mi_small", "sponza_small", "disney_small"]:
         z = np.load("tests/golden/records_%s.npz" % name)
