@@ -110,6 +110,14 @@ static __global__ void __launch_bounds__(256) k_shift_reduce(WaveParams wp, cons
             if (nb_y) a[6 + c] += -r[15 * 8 + 6 + c];           // pixel (x, 1): next row of the tile
         }
     }
+    if (y == 1 && wp.y0 == 1) {          // a row band that starts at row 1: row 0 belongs to another call, so this thread carries the border term there
+        double b[3] = {cy0[pix - (size_t)wp.width * 3], cy0[pix - (size_t)wp.width * 3 + 1], cy0[pix - (size_t)wp.width * 3 + 2]};
+        for (int s = 0; s < wp.n_samples; s++) {
+            const double *r = res + ((size_t)s * wp.npix_pad + p) * 15;
+            for (int c = 0; c < 3; c++) b[c] += -r[6 + c];
+        }
+        for (int c = 0; c < 3; c++) cy0[pix - (size_t)wp.width * 3 + c] = b[c];
+    }
 #pragma unroll
     for (int k = 0; k < 15; k++) bufs[k / 3][pix + k % 3] = a[k];
 }

@@ -101,6 +101,15 @@ def test_row_bands_compose_to_the_full_image(g):
         acc_dx[y0:y1] += part.dx[y0:y1]
     assert np.allclose(acc_p, full.primal, rtol=1e-12, atol=1e-15)
     assert np.allclose(acc_dx, full.dx, rtol=1e-9, atol=1e-13)
+    # the merge is linear, so whole merged images add up too — also for a band edge between rows 0 and 1, where the border rule
+    # of row 0 (minus the row-1 estimate) has to be carried by the band that owns row 1
+    acc = {n: np.zeros_like(full.primal) for n in ("primal", "dx", "dy")}
+    for y0, y1 in ((0, 1), (1, 20), (20, 44), (44, 64)):
+        part = g.gradient_path_render(sc, spp=3, precision="f64", offsets="shift", rows=(y0, y1), outputs=("primal", "dx", "dy"))
+        for n in acc:
+            acc[n] += part[n]
+    for n in acc:
+        assert np.allclose(acc[n], full[n], rtol=1e-9, atol=1e-13), n
 
 
 def test_glossy_and_textured_scenes_render(g):
