@@ -186,6 +186,7 @@ int run_l1(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, con
     L1Geom g; g.w = w; g.h = h; g.n = (long long)w * h * 3; g.alpha = alpha;
     const size_t img = (size_t)g.n * sizeof(double), plane = (size_t)w * h * sizeof(double);
     L1Buffers B;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
     auto release = [&]() { DevBuf *all[] = {&B.wU, &B.wX, &B.wY, &B.r, &B.z, &B.p, &B.q, &B.partial, &B.partial2, &B.sc}; for (auto *b : all) b->release(); };
     auto body = [&]() -> int {
         { DevBuf *planes[] = {&B.wU, &B.wX, &B.wY}; for (auto *b : planes) if (int r = b->ensure(plane)) return r; }
@@ -196,7 +197,6 @@ int run_l1(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, con
         L1Scalars *sc = B.sc.as<L1Scalars>();
         double *part = B.partial.as<double>(), *part2 = B.partial2.as<double>();
         GD_CUDA(cudaMemsetAsync(sc, 0, sizeof(L1Scalars), st));
-        cudaEvent_t e0, e1;
         GD_CUDA(cudaEventCreate(&e0)); GD_CUDA(cudaEventCreate(&e1));
         GD_CUDA(cudaEventRecord(e0, st));
         // the starting image
@@ -227,12 +227,13 @@ int run_l1(gdpt_ctx *c, int w, int h, const double *d_u, const double *d_gx, con
         GD_CUDA(cudaMemcpyAsync(&hs, sc, sizeof(hs), cudaMemcpyDeviceToHost, st));
         GD_CUDA(cudaStreamSynchronize(st));
         float ms = 0.f; cudaEventElapsedTime(&ms, e0, e1);
-        cudaEventDestroy(e0); cudaEventDestroy(e1);
         c->stats.kernel_launches += launches;
         if (info) { info[0] = hs.bb > 0 ? sqrt(hs.rr / hs.bb) : 0.0; info[1] = (double)hs.iterations; info[2] = ms; info[3] = hs.eps; }
         return 0;
     };
     const int rc = body();
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
     release();
     return rc;
 }
