@@ -449,11 +449,11 @@ def run_native(args):
             check(lib.gdpt_measure_l2_read(local, 48, 40, _capi.as_dp(l2)))     # 48 MB buffer, L2-resident
         except Exception:
             l2[0] = 0.0
-        # committed ncu evidence for the same kernel (profiles/r2v_k_trace_*.json, captured at the final state of the kernel; one --set full capture per launch type)
+        # committed ncu evidence for the same kernel (profiles/r2y_k_trace_bounce.json (final state of the kernel) and r2v_k_trace_primary.json; one --set full capture per launch type)
         ncu = {}
         for tag in ("bounce", "primary"):
             try:
-                ncu[tag] = json.load(open(os.path.join(ROOT, "profiles", "r2v_k_trace_%s.json" % tag)))
+                ncu[tag] = json.load(open(os.path.join(ROOT, "profiles", ("r2y_k_trace_%s.json" if tag == "bounce" else "r2v_k_trace_%s.json") % tag)))
             except Exception:
                 pass
         nb = ncu.get("bounce")
