@@ -308,6 +308,24 @@ def test_fft_dct1_device_functions_on_the_host(tmp_path):
         assert r[str(n)]["roundtrip"] < 1e-14 and r[str(n)]["dct_rel_err"] < 1e-13, (n, r[str(n)])
 
 
+def test_fft_line_buffer_swizzle_is_conflict_free_in_the_bank_model():
+    """fft_sw (csrc/gdpt_poisson_fft.cuh) in the 8-bank / quarter-warp model of 16-byte shared-memory accesses: every access
+    pattern of both FFT directions at P = 2048 / 4096 / 8192 costs the ideal number of wavefronts, where the natural layout
+    costs 1.5-1.6 x (ncu measured 1.52 x on B200: profiles/r2_k_dct_cols_swizzled.txt).  The Python map is the header's."""
+    import re
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import fft_swizzle_search as F
+    src = open(os.path.join(ROOT, "gradient_based_path_tracing_b200", "csrc", "gdpt_poisson_fft.cuh")).read()
+    assert re.search(r"fft_sw\(int e\) \{ const int x = \(e >> 3\) & 3; return e \^ \(x \^ \(x << 1\)\); \}", src)
+    for P, logP in F.SIZES:
+        natural, _ = F.cost(lambda e: e, P, logP)
+        swizzled, worst = F.cost(F.fft_sw, P, logP)
+        assert swizzled == 1.0, (P, worst)
+        assert natural > 1.45
+        assert sorted(F.fft_sw(e) for e in range(P)) == list(range(P))          # a permutation of the line
+
+
 # ------------------------------------------------------------------ bench.py: the reference arm and the helpers that need no GPU
 def test_bench_reference_arm_line_and_affine_cost_model():
     """`bench.py --impl reference` on a small film: one JSON line with the contract's keys, the affine cost model
