@@ -36,3 +36,9 @@ if [ ! -f "$CLI" ] || [ "$OUT" -nt "$CLI" ] || [ -n "$(find "$HERE/host" -newer 
       -L "$HERE/.." -lgdpt -lz -Wl,-rpath,'$ORIGIN'
   echo "built $CLI"
 fi
+# the reference's second program as a host over the C ABI (same command line and output files as small_gdpt.cpp)
+SG="$HERE/../smallgdpt_b200"
+if [ ! -f "$SG" ] || [ "$OUT" -nt "$SG" ] || [ "$HERE/host/smallgdpt_b200.cpp" -nt "$SG" ]; then
+  g++ -O2 -std=c++17 -I "$HERE/../../include" "$HERE/host/smallgdpt_b200.cpp" -o "$SG" -L "$HERE/.." -lgdpt -Wl,-rpath,'$ORIGIN'
+  echo "built $SG"
+fi

@@ -101,3 +101,19 @@ def test_the_header_s_two_stated_choices_matter(tmp_path):
     c = np.fromfile(out).reshape(5, h, w, 3)[0].astype(np.float32)
     assert not np.array_equal(c, g["image"])
     assert np.abs(c - g["image"]).max() < 1e-2            # a last-digits difference, not another image
+
+
+def test_cli_host_fails_loudly_without_a_device(tmp_path):
+    """smallgdpt_b200 has no CPU path: without a CUDA device it says so and exits non-zero (no files written)."""
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "smallgdpt_b200")
+    if not os.path.exists(exe):
+        pytest.skip("smallgdpt_b200 not built")
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("a CUDA device is present")
+    except ImportError:
+        pass
+    r = subprocess.run([exe, "1", "-size", "16", "12"], cwd=tmp_path, capture_output=True, timeout=60)
+    assert r.returncode != 0 and b"no CUDA device" in r.stderr
+    assert not list(tmp_path.glob("*.pfm"))

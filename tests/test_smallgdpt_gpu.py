@@ -90,3 +90,18 @@ def test_argument_errors(g):
             smallgdpt.render(**kw)
     with pytest.raises(ValueError):
         smallgdpt.render(64, 48, 1, rng="columns")
+
+
+def test_cli_host_writes_the_reference_program_s_files(g, tmp_path):
+    """smallgdpt_b200 (C++ over the C ABI): small_gdpt.cpp's command line and its four PFM files, compared with the fixture of
+    the reference program at the same film and sample count."""
+    import subprocess
+    from oracle import smallgdpt as ref
+    exe = os.path.join(ROOT, "gradient_based_path_tracing_b200", "smallgdpt_b200")
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "smallgdpt_128x96_4spp.npz"))
+    r = subprocess.run([exe, "4", "-size", "128", "96"], cwd=tmp_path, capture_output=True, timeout=300)
+    assert r.returncode == 0, r.stderr.decode()
+    for n in NAMES:
+        got = ref.read_pfm(str(tmp_path / (n + ".pfm")))
+        same, worst = closeness(got, gold[n])
+        assert same > 0.99 and worst < 2e-5, (n, same, worst)
