@@ -42,6 +42,29 @@ def test_no_cpu_fallback_without_device(g):
     sc = g.Scene.named("cbox_gdpt_64")
     with pytest.raises(g._capi.GdptError, match="no CUDA device"):
         g.render(sc)
+    # the entry points added in round 2 have no CPU path either; their argument checks answer before the device is looked for
+    from gradient_based_path_tracing_b200 import smallgdpt
+    with pytest.raises(g._capi.GdptError, match="no CUDA device"):
+        g.reconstruct_l1(u, u, u)
+    with pytest.raises(g._capi.GdptError, match="no CUDA device"):
+        smallgdpt.render(64, 48, 1)
+    with pytest.raises(g._capi.GdptError, match="outside 2..16384"):
+        smallgdpt.render(1, 48, 1)
+    with pytest.raises(g._capi.GdptError, match="2x2"):
+        g.reconstruct_l1(u[:1], u[:1], u[:1])
+
+
+def test_struct_layout_of_the_l1_parameters_matches_the_header(g, tmp_path):
+    import ctypes
+    import subprocess
+    src = tmp_path / "l1.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "gdpt.h"\nint main(void){printf("%zu %zu %zu %zu\\n", sizeof(gdpt_l1_params),'
+                   ' offsetof(gdpt_l1_params, reweight_primal), offsetof(gdpt_l1_params, alpha), offsetof(gdpt_l1_params, cg_tolerance));return 0;}\n')
+    exe = tmp_path / "l1"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = [int(v) for v in subprocess.check_output([str(exe)]).split()]
+    P = g._capi.GdptL1Params
+    assert got == [ctypes.sizeof(P), P.reweight_primal.offset, P.alpha.offset, P.cg_tolerance.offset]
 
 
 def test_product_never_imports_the_oracle():
